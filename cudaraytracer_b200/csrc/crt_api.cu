@@ -1,0 +1,595 @@
+// crt_api.cu — the C ABI of include/crt.h: context, scene upload, camera, framebuffer, render, resolve.
+// Everything here runs on the GPU or fails with an error code; there is no CPU rendering path.
+
+#include "crt.h"
+#include "crt_internal.h"
+
+#include "kernels.cuh"
+#include "wavefront.cuh"
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+struct crt_context
+{
+    int device = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    int sm_count = 0;
+    int smem_optin = 0, smem_per_sm = 0;
+    int smem_budget_override = -1;
+
+    // scene
+    float4* d_nodes = nullptr;
+    float4* d_prims = nullptr;
+    float* d_prim_k = nullptr;
+    float4* d_mats = nullptr;
+    int* d_prim_id = nullptr;
+    DevImage* d_images = nullptr;
+    std::vector<uchar4*> d_texels;
+    DevScene scene{};
+    bool have_scene = false;
+    crt_bvh_stats stats{};
+    uint64_t scene_h2d_bytes = 0;
+
+    // camera
+    crt_input_struct inputs{};
+    DevCamera cam{};
+    bool have_cam = false;
+    float aperture = 0.f, focus_dist = 1.f;
+
+    // framebuffer
+    uint32_t width = 0, height = 0;
+    float4* d_accum_own = nullptr;
+    float4* d_accum = nullptr;
+    uint32_t* d_rgba = nullptr;
+    int* d_ids = nullptr;
+
+    DevCounters* d_counters = nullptr;
+    uint64_t launches = 0;
+
+    WavefrontState wf;
+
+    std::string err;
+};
+
+static std::mutex g_err_mu;
+static std::string g_err;
+
+crt_status crt_set_error(crt_context* ctx, crt_status st, const char* msg)
+{
+    if (ctx) ctx->err = msg ? msg : "";
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    g_err = msg ? msg : "";
+    return st;
+}
+
+static crt_status cuda_fail(crt_context* ctx, cudaError_t e, const char* what)
+{
+    char buf[512];
+    snprintf(buf, sizeof(buf), "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+    return crt_set_error(ctx, CRT_ERR_CUDA, buf);
+}
+
+#define CU(call)                                                   \
+    do {                                                           \
+        cudaError_t e__ = (call);                                  \
+        if (e__ != cudaSuccess) return cuda_fail(ctx, e__, #call); \
+    } while (0)
+
+static void free_scene(crt_context* ctx)
+{
+    cudaFree(ctx->d_nodes); ctx->d_nodes = nullptr;
+    cudaFree(ctx->d_prims); ctx->d_prims = nullptr;
+    cudaFree(ctx->d_prim_k); ctx->d_prim_k = nullptr;
+    cudaFree(ctx->d_mats); ctx->d_mats = nullptr;
+    cudaFree(ctx->d_prim_id); ctx->d_prim_id = nullptr;
+    cudaFree(ctx->d_images); ctx->d_images = nullptr;
+    for (uchar4* p : ctx->d_texels) cudaFree(p);
+    ctx->d_texels.clear();
+    ctx->have_scene = false;
+}
+
+extern "C" {
+
+int crt_abi_version(void)
+{
+    return CRT_ABI_VERSION;
+}
+
+const char* crt_last_error_string(const crt_context* ctx)
+{
+    if (ctx) return ctx->err.c_str();
+    static thread_local std::string copy;
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    copy = g_err;
+    return copy.c_str();
+}
+
+crt_status crt_context_create(int device, crt_context** out)
+{
+    if (!out) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_context_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        // Loud failure: this library has no CPU path.
+        return crt_set_error(nullptr, CRT_ERR_CUDA, "crt_context_create: no CUDA device available (this library has no CPU fallback)");
+    }
+    if (device < 0 || device >= n) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_context_create: device index out of range");
+    crt_context* ctx = new (std::nothrow) crt_context();
+    if (!ctx) return crt_set_error(nullptr, CRT_ERR_NOMEM, "crt_context_create: out of memory");
+    ctx->device = device;
+    if ((e = cudaSetDevice(device)) != cudaSuccess) { crt_status s = cuda_fail(nullptr, e, "cudaSetDevice"); delete ctx; return s; }
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) { crt_status s = cuda_fail(nullptr, e, "cudaGetDeviceProperties"); delete ctx; return s; }
+    if (prop.major != 10) {
+        delete ctx;
+        return crt_set_error(nullptr, CRT_ERR_UNSUPPORTED, "crt_context_create: kernels are built for sm_100a (B200) only");
+    }
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    ctx->smem_per_sm = (int)prop.sharedMemPerMultiprocessor;
+    const char* env = getenv("CRT_SMEM_KB");
+    if (env) ctx->smem_budget_override = atoi(env) * 1024;
+    if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->d_counters, sizeof(DevCounters))) != cudaSuccess ||
+        (e = cudaMemset(ctx->d_counters, 0, sizeof(DevCounters))) != cudaSuccess) {
+        crt_status s = cuda_fail(nullptr, e, "crt_context_create");
+        crt_context_destroy(ctx);
+        return s;
+    }
+    ctx->stream = ctx->own_stream;
+    *out = ctx;
+    return CRT_OK;
+}
+
+void crt_context_destroy(crt_context* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    free_scene(ctx);
+    wavefront_free(ctx->wf);
+    cudaFree(ctx->d_accum_own);
+    cudaFree(ctx->d_rgba);
+    cudaFree(ctx->d_ids);
+    cudaFree(ctx->d_counters);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+}
+
+crt_status crt_set_stream(crt_context* ctx, void* cuda_stream)
+{
+    if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_set_stream: ctx is NULL");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    return CRT_OK;
+}
+
+crt_status crt_synchronize(crt_context* ctx)
+{
+    if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_synchronize: ctx is NULL");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return CRT_OK;
+}
+
+} // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// scene
+// ------------------------------------------------------------------------------------------
+static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, const CrtPackedScene& P)
+{
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    free_scene(ctx);
+    const size_t nn = P.nodes.size(), np = P.prim_id.size();
+    uint64_t h2d = 0;
+    CU(cudaMalloc(&ctx->d_nodes, std::max<size_t>(nn, 1) * 64));
+    CU(cudaMemcpyAsync(ctx->d_nodes, P.nodes.data(), nn * 64, cudaMemcpyHostToDevice, ctx->stream));
+    h2d += nn * 64;
+    CU(cudaMalloc(&ctx->d_prims, std::max<size_t>(np, 1) * 16));
+    CU(cudaMalloc(&ctx->d_prim_k, std::max<size_t>(np, 1) * 4));
+    CU(cudaMalloc(&ctx->d_mats, std::max<size_t>(np, 1) * 32));
+    CU(cudaMalloc(&ctx->d_prim_id, std::max<size_t>(np, 1) * 4));
+    if (np) {
+        CU(cudaMemcpyAsync(ctx->d_prims, P.prims.data(), np * 16, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->d_prim_k, P.prim_k.data(), np * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->d_mats, P.mats.data(), np * 32, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->d_prim_id, P.prim_id.data(), np * 4, cudaMemcpyHostToDevice, ctx->stream));
+        h2d += np * (16 + 4 + 32 + 4);
+    }
+    // images: RGB8 -> RGBA8 so a texel is one aligned 32-bit load
+    std::vector<DevImage> himg(sd->n_images);
+    for (uint64_t i = 0; i < sd->n_images; i++) {
+        const crt_image& im = sd->images[i];
+        himg[i].texels = nullptr;
+        himg[i].width = im.width;
+        himg[i].height = im.height;
+        if (!im.pixels || im.width <= 0 || im.height <= 0) continue;
+        size_t npx = (size_t)im.width * im.height;
+        std::vector<uchar4> rgba(npx);
+        for (size_t k = 0; k < npx; k++) rgba[k] = make_uchar4(im.pixels[3 * k], im.pixels[3 * k + 1], im.pixels[3 * k + 2], 255);
+        uchar4* d = nullptr;
+        CU(cudaMalloc(&d, npx * 4));
+        ctx->d_texels.push_back(d);
+        CU(cudaMemcpy(d, rgba.data(), npx * 4, cudaMemcpyHostToDevice));
+        h2d += npx * 4;
+        himg[i].texels = d;
+    }
+    CU(cudaMalloc(&ctx->d_images, std::max<size_t>(himg.size(), 1) * sizeof(DevImage)));
+    if (!himg.empty()) CU(cudaMemcpy(ctx->d_images, himg.data(), himg.size() * sizeof(DevImage), cudaMemcpyHostToDevice));
+    CU(cudaStreamSynchronize(ctx->stream));
+
+    DevScene& S = ctx->scene;
+    S.nodes = ctx->d_nodes; S.prims = ctx->d_prims; S.prim_k = ctx->d_prim_k; S.mats = ctx->d_mats;
+    S.prim_id = ctx->d_prim_id; S.images = ctx->d_images;
+    S.n_nodes = (int)nn; S.n_prims = (int)np;
+    S.smem_nodes = S.smem_prims = S.smem_mats = 0;
+    ctx->stats = P.stats;
+    ctx->scene_h2d_bytes = h2d;
+    ctx->have_scene = true;
+    return CRT_OK;
+}
+
+extern "C" {
+
+crt_status crt_scene_upload(crt_context* ctx, const crt_scene_desc* scene)
+{
+    if (!ctx || !scene) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_upload: NULL argument");
+    CrtPackedScene P;
+    std::string err;
+    if (!crt_pack_scene(scene, &P, &err)) return crt_set_error(ctx, CRT_ERR_INVALID, err.c_str());
+    if (P.stats.max_depth >= CRT_STACK_SIZE)
+        return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, "crt_scene_upload: BVH deeper than the traversal stack");
+    return upload_packed(ctx, scene, P);
+}
+
+crt_status crt_scene_from_reference(crt_context* ctx, const void* world)
+{
+    if (!ctx || !world) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_from_reference: NULL argument");
+    CrtFlatScene flat;
+    std::string err;
+    if (!crt_flatten_reference_world(world, &flat, &err)) return crt_set_error(ctx, CRT_ERR_INVALID, err.c_str());
+    crt_scene_desc d = flat.desc();
+    return crt_scene_upload(ctx, &d);
+}
+
+crt_status crt_bvh_get_stats(const crt_context* ctx, crt_bvh_stats* out)
+{
+    if (!ctx || !out) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_bvh_get_stats: NULL argument");
+    if (!ctx->have_scene) return crt_set_error(nullptr, CRT_ERR_STATE, "crt_bvh_get_stats: no scene uploaded");
+    *out = ctx->stats;
+    return CRT_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// camera
+// ------------------------------------------------------------------------------------------
+static void derive_camera(crt_context* ctx)
+{
+    const crt_input_struct& in = ctx->inputs;
+    DevCamera& C = ctx->cam;
+    C.ox = in.origin_x; C.oy = in.origin_y; C.oz = in.origin_z;
+    C.fx = in.orientation_x; C.fy = in.orientation_y; C.fz = in.orientation_z;
+    C.ux = in.up_x; C.uy = in.up_y; C.uz = in.up_z;
+    // rightV = Normalize(Cross(upV, forwardV)), Kernel.cu:133 with Math.cuh:157-161,225-229; host IEEE binary32
+    volatile float cx = C.uy * C.fz - C.uz * C.fy;
+    volatile float cy = -(C.ux * C.fz - C.uz * C.fx);
+    volatile float cz = C.ux * C.fy - C.uy * C.fx;
+    volatile float dd = cx * cx + cy * cy + cz * cz;
+    volatile float inv = 1 / sqrtf(dd);
+    C.rx = inv * cx; C.ry = inv * cy; C.rz = inv * cz;
+    C.far_plane = in.far_plane; C.near_plane = in.near_plane; C.fov = in.fov;
+    volatile float k = 1.0f / in.fov;
+    C.far_k = k * 10.0f;
+    for (int i = 0; i < 3; i++) { C.bg0[i] = in.background_start[i]; C.bg1[i] = in.background_end[i]; }
+    C.lens_radius = ctx->aperture * 0.5f;
+    C.focus_dist = ctx->focus_dist;
+}
+
+crt_status crt_set_camera(crt_context* ctx, const crt_input_struct* inputs)
+{
+    if (!ctx || !inputs) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_set_camera: NULL argument");
+    ctx->inputs = *inputs;
+    derive_camera(ctx);
+    ctx->have_cam = true;
+    return CRT_OK;
+}
+
+crt_status crt_set_lens(crt_context* ctx, float aperture, float focus_dist)
+{
+    if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_set_lens: ctx is NULL");
+    if (!(aperture >= 0.f) || !(focus_dist > 0.f)) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_set_lens: aperture must be >= 0 and focus_dist > 0");
+    ctx->aperture = aperture;
+    ctx->focus_dist = focus_dist;
+    if (ctx->have_cam) derive_camera(ctx);
+    return CRT_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// framebuffer
+// ------------------------------------------------------------------------------------------
+crt_status crt_framebuffer_resize(crt_context* ctx, uint32_t width, uint32_t height)
+{
+    if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_framebuffer_resize: ctx is NULL");
+    if (width == 0 || height == 0 || (uint64_t)width * height > 0x7FFFFFFFull)
+        return crt_set_error(ctx, CRT_ERR_INVALID, "crt_framebuffer_resize: bad size");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    const bool external = ctx->d_accum && ctx->d_accum != ctx->d_accum_own;
+    if (width != ctx->width || height != ctx->height || !ctx->d_rgba) {
+        cudaFree(ctx->d_accum_own); ctx->d_accum_own = nullptr;
+        cudaFree(ctx->d_rgba); ctx->d_rgba = nullptr;
+        cudaFree(ctx->d_ids); ctx->d_ids = nullptr;
+        size_t n = (size_t)width * height;
+        CU(cudaMalloc(&ctx->d_accum_own, n * sizeof(float4)));
+        CU(cudaMalloc(&ctx->d_rgba, n * 4));
+        CU(cudaMalloc(&ctx->d_ids, n * 4));
+        ctx->width = width;
+        ctx->height = height;
+        if (!external) ctx->d_accum = ctx->d_accum_own;
+        else ctx->d_accum = ctx->d_accum_own; // an external buffer of the old size is no longer valid
+    }
+    return crt_accum_clear(ctx);
+}
+
+crt_status crt_accum_clear(crt_context* ctx)
+{
+    if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_accum_clear: ctx is NULL");
+    if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_accum_clear: no framebuffer");
+    CU(cudaSetDevice(ctx->device));
+    uint32_t n = ctx->width * ctx->height;
+    k_clear<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_accum, n);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return CRT_OK;
+}
+
+crt_status crt_set_accum_device_buffer(crt_context* ctx, void* device_float4)
+{
+    if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_set_accum_device_buffer: ctx is NULL");
+    if (!ctx->d_accum_own) return crt_set_error(ctx, CRT_ERR_STATE, "crt_set_accum_device_buffer: call crt_framebuffer_resize first");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->d_accum = device_float4 ? (float4*)device_float4 : ctx->d_accum_own;
+    return CRT_OK;
+}
+
+void* crt_accum_device_ptr(crt_context* ctx)
+{
+    return ctx ? (void*)ctx->d_accum : nullptr;
+}
+
+} // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// render
+// ------------------------------------------------------------------------------------------
+// Decides how much of the scene each CTA stages in shared memory. Everything if it fits next to
+// `blocks_per_sm` resident CTAs; otherwise the breadth-first prefix of the node array (the hot top levels).
+static size_t plan_smem(const crt_context* ctx, int blocks_per_sm, DevScene& S, bool& all)
+{
+    long budget = ctx->smem_per_sm / std::max(blocks_per_sm, 1) - 1024;
+    budget = std::min<long>(budget, ctx->smem_optin);
+    if (ctx->smem_budget_override >= 0) budget = std::min<long>(ctx->smem_budget_override, ctx->smem_optin);
+    budget = std::max<long>(budget, 0);
+    const long full = (long)S.n_nodes * 64 + (long)S.n_prims * 48;
+    if (full <= budget) {
+        S.smem_nodes = S.n_nodes; S.smem_prims = S.n_prims; S.smem_mats = S.n_prims;
+        all = true;
+        return (size_t)full;
+    }
+    all = false;
+    long rem = budget;
+    S.smem_nodes = (int)std::min<long>(S.n_nodes, rem / 64); rem -= (long)S.smem_nodes * 64;
+    S.smem_prims = (int)std::min<long>(S.n_prims, rem / 16); rem -= (long)S.smem_prims * 16;
+    S.smem_mats = (int)std::min<long>(S.n_prims, rem / 32); rem -= (long)S.smem_mats * 32;
+    return (size_t)(budget - rem);
+}
+
+template <bool EXACT, bool COUNT, bool ALL>
+static cudaError_t launch_mega(const RenderArgs& A, dim3 grid, size_t smem, cudaStream_t st)
+{
+    cudaError_t e = cudaFuncSetAttribute(k_render_mega<EXACT, COUNT, ALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_render_mega<EXACT, COUNT, ALL><<<grid, CRT_BLOCK_THREADS, smem, st>>>(A);
+    return cudaGetLastError();
+}
+
+static cudaError_t dispatch_mega(const RenderArgs& A, dim3 grid, size_t smem, cudaStream_t st, bool exact, bool count, bool all)
+{
+    if (exact) {
+        if (count) return all ? launch_mega<true, true, true>(A, grid, smem, st) : launch_mega<true, true, false>(A, grid, smem, st);
+        return all ? launch_mega<true, false, true>(A, grid, smem, st) : launch_mega<true, false, false>(A, grid, smem, st);
+    }
+    if (count) return all ? launch_mega<false, true, true>(A, grid, smem, st) : launch_mega<false, true, false>(A, grid, smem, st);
+    return all ? launch_mega<false, false, true>(A, grid, smem, st) : launch_mega<false, false, false>(A, grid, smem, st);
+}
+
+static int mega_blocks_per_sm(bool exact, bool count)
+{
+    // occupancy of the variant with no dynamic shared memory; used only to size the smem budget
+    int n = 0;
+    cudaError_t e;
+    if (exact) e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render_mega<true, true, true>, CRT_BLOCK_THREADS, 0)
+                         : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render_mega<true, false, true>, CRT_BLOCK_THREADS, 0);
+    else e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render_mega<false, true, true>, CRT_BLOCK_THREADS, 0)
+                   : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render_mega<false, false, true>, CRT_BLOCK_THREADS, 0);
+    if (e != cudaSuccess || n < 1) n = 4;
+    return n;
+}
+
+extern "C" {
+
+crt_status crt_render(crt_context* ctx, const crt_render_params* p)
+{
+    if (!ctx || !p) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_render: NULL argument");
+    if (!ctx->have_scene) return crt_set_error(ctx, CRT_ERR_STATE, "crt_render: no scene uploaded");
+    if (!ctx->have_cam) return crt_set_error(ctx, CRT_ERR_STATE, "crt_render: no camera set");
+    if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_render: no framebuffer (crt_framebuffer_resize)");
+    if (p->variant < CRT_VARIANT_AUTO || p->variant > CRT_VARIANT_WAVEFRONT) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_render: bad variant");
+    if (p->jitter != CRT_JITTER_RANDOM && p->jitter != CRT_JITTER_CENTER) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_render: bad jitter mode");
+    CU(cudaSetDevice(ctx->device));
+
+    RenderArgs A;
+    memset(&A, 0, sizeof(A));
+    A.scene = ctx->scene;
+    A.cam = ctx->cam;
+    A.accum = ctx->d_accum;
+    A.counters = ctx->d_counters;
+    A.width = ctx->width; A.height = ctx->height;
+    A.cover_w = ctx->width; A.cover_h = ctx->height;
+    if (p->flags & CRT_FLAG_TRUNCATED_GRID) { A.cover_w = ctx->width / 16 * 16; A.cover_h = ctx->height / 16 * 16; }
+    A.spp_begin = p->spp_begin; A.spp_count = p->spp_count; A.spp_stride = p->spp_stride ? p->spp_stride : 1;
+    A.max_depth = p->max_depth;
+    A.seed_lo = (uint32_t)p->seed; A.seed_hi = (uint32_t)(p->seed >> 32);
+    A.jitter = p->jitter;
+    const bool exact = (p->flags & CRT_FLAG_EXACT_MATH) != 0, count = (p->flags & CRT_FLAG_COUNT_TESTS) != 0;
+
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    if (p->spp_count > 0 && A.cover_w > 0 && A.cover_h > 0) {
+        int variant = p->variant == CRT_VARIANT_AUTO ? CRT_VARIANT_MEGAKERNEL : p->variant;
+        if (variant == CRT_VARIANT_WAVEFRONT) {
+            return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, "crt_render: wavefront variant not built yet");
+        }
+        bool all = false;
+        size_t smem = plan_smem(ctx, mega_blocks_per_sm(exact, count), A.scene, all);
+        dim3 grid(((A.cover_w + 15) / 16) * ((A.cover_h + 15) / 16));
+        CU(dispatch_mega(A, grid, smem, ctx->stream, exact, count, all));
+        ctx->launches++;
+    }
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->timed = true;
+    return CRT_OK;
+}
+
+crt_status crt_last_render_ms(crt_context* ctx, float* out_ms)
+{
+    if (!ctx || !out_ms) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_last_render_ms: NULL argument");
+    if (!ctx->timed) return crt_set_error(ctx, CRT_ERR_STATE, "crt_last_render_ms: nothing rendered yet");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventSynchronize(ctx->ev1));
+    CU(cudaEventElapsedTime(out_ms, ctx->ev0, ctx->ev1));
+    return CRT_OK;
+}
+
+crt_status crt_resolve_device(crt_context* ctx, void* device_out_rgba8)
+{
+    if (!ctx || !device_out_rgba8) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_device: NULL argument");
+    if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_resolve_device: no framebuffer");
+    CU(cudaSetDevice(ctx->device));
+    uint32_t n = ctx->width * ctx->height;
+    k_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_accum, (uint32_t*)device_out_rgba8, ctx->width, ctx->width, ctx->height);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return CRT_OK;
+}
+
+crt_status crt_resolve(crt_context* ctx, uint32_t* out_rgba8)
+{
+    if (!ctx || !out_rgba8) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve: NULL argument");
+    crt_status s = crt_resolve_device(ctx, ctx->d_rgba);
+    if (s != CRT_OK) return s;
+    CU(cudaMemcpyAsync(out_rgba8, ctx->d_rgba, (size_t)ctx->width * ctx->height * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return CRT_OK;
+}
+
+crt_status crt_read_accum(crt_context* ctx, float* out_float4)
+{
+    if (!ctx || !out_float4) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_read_accum: NULL argument");
+    if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_read_accum: no framebuffer");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(out_float4, ctx->d_accum, (size_t)ctx->width * ctx->height * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return CRT_OK;
+}
+
+crt_status crt_primary_ids(crt_context* ctx, int32_t jitter, uint64_t seed, int32_t* out_ids)
+{
+    if (!ctx || !out_ids) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_primary_ids: NULL argument");
+    if (!ctx->have_scene) return crt_set_error(ctx, CRT_ERR_STATE, "crt_primary_ids: no scene uploaded");
+    if (!ctx->have_cam) return crt_set_error(ctx, CRT_ERR_STATE, "crt_primary_ids: no camera set");
+    if (!ctx->d_ids) return crt_set_error(ctx, CRT_ERR_STATE, "crt_primary_ids: no framebuffer (crt_framebuffer_resize)");
+    if (jitter != CRT_JITTER_RANDOM && jitter != CRT_JITTER_CENTER) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_primary_ids: bad jitter mode");
+    CU(cudaSetDevice(ctx->device));
+    IdArgs A;
+    memset(&A, 0, sizeof(A));
+    A.scene = ctx->scene;
+    A.cam = ctx->cam;
+    A.out_ids = ctx->d_ids;
+    A.width = ctx->width; A.height = ctx->height;
+    A.seed_lo = (uint32_t)seed; A.seed_hi = (uint32_t)(seed >> 32);
+    A.jitter = jitter;
+    bool all = false;
+    size_t smem = plan_smem(ctx, 4, A.scene, all);
+    dim3 grid(((A.width + 15) / 16) * ((A.height + 15) / 16));
+    if (all) {
+        CU(cudaFuncSetAttribute(k_primary_ids<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_primary_ids<true><<<grid, CRT_BLOCK_THREADS, smem, ctx->stream>>>(A);
+    }
+    else {
+        CU(cudaFuncSetAttribute(k_primary_ids<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_primary_ids<false><<<grid, CRT_BLOCK_THREADS, smem, ctx->stream>>>(A);
+    }
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(out_ids, ctx->d_ids, (size_t)ctx->width * ctx->height * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return CRT_OK;
+}
+
+crt_status crt_get_counters(crt_context* ctx, crt_counters* out)
+{
+    if (!ctx || !out) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_get_counters: NULL argument");
+    CU(cudaSetDevice(ctx->device));
+    DevCounters h;
+    CU(cudaMemcpyAsync(&h, ctx->d_counters, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    out->paths = h.paths; out->rays = h.rays; out->box_tests = h.box_tests; out->prim_tests = h.prim_tests;
+    out->kernel_launches = ctx->launches;
+    return CRT_OK;
+}
+
+crt_status crt_reset_counters(crt_context* ctx)
+{
+    if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_reset_counters: ctx is NULL");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemsetAsync(ctx->d_counters, 0, sizeof(DevCounters), ctx->stream));
+    ctx->launches = 0;
+    return CRT_OK;
+}
+
+crt_status crt_write_ppm(const char* path, const uint32_t* rgba8, uint32_t width, uint32_t height, int flip_rows)
+{
+    if (!path || !rgba8 || !width || !height) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_write_ppm: bad argument");
+    FILE* f = fopen(path, "wb");
+    if (!f) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_write_ppm: cannot open output file");
+    fprintf(f, "P6\n%u %u\n255\n", width, height);
+    std::vector<unsigned char> row((size_t)width * 3);
+    for (uint32_t r = 0; r < height; r++) {
+        const uint32_t* src = rgba8 + (size_t)(flip_rows ? height - 1 - r : r) * width;
+        for (uint32_t x = 0; x < width; x++) {
+            row[3 * x] = src[x] & 255; row[3 * x + 1] = (src[x] >> 8) & 255; row[3 * x + 2] = (src[x] >> 16) & 255;
+        }
+        fwrite(row.data(), 1, row.size(), f);
+    }
+    fclose(f);
+    return CRT_OK;
+}
+
+} // extern "C"

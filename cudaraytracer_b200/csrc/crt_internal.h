@@ -1,0 +1,73 @@
+// crt_internal.h — shared between the host-side translation units of libcrt.so (not installed).
+#pragma once
+
+#include "crt.h"
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+// Records `msg` as the last error of `ctx` (and process-wide when ctx is NULL) and returns `st`.
+crt_status crt_set_error(crt_context* ctx, crt_status st, const char* msg);
+
+// ---------------------------------------------------------------------------------------------
+// Packed device scene (what the kernels read). Built on the host by scene_pack.cpp.
+//
+// BVH2, one primitive per leaf. Node = 64 bytes = 4 x 128-bit words:
+//   w0 = {c0.lo.x, c0.lo.y, c0.lo.z, c0.hi.x}
+//   w1 = {c0.hi.y, c0.hi.z, c1.lo.x, c1.lo.y}
+//   w2 = {c1.lo.z, c1.hi.x, c1.hi.y, c1.hi.z}
+//   w3 = {child0, child1, 0, 0} (int bits)
+// child >= 0: index of an inner node. child < 0: leaf, ~child = (type << 28) | prim index.
+// Nodes are stored breadth-first so the first K nodes are the hottest (they are staged in shared memory).
+//
+// Primitive i (leaf order): prim[i] = sphere {cx, cy, cz, r}
+//                                    | rect {a0, a1, b0, b1} (bounds on the two in-plane axes) with prim_k[i] = plane offset
+// Material record i (leaf order, one per primitive, 32 bytes = 2 words):
+//   m0 = {r, g, b, param}      constant colour | checker odd colour; param = fuzz | ir | (float)light_intensity
+//   m1 = {er, eg, eb, bits}    checker even colour; bits = mat_type | tex_type << 4 | (image + 1) << 8
+// prim_id[i] = index of the hittable in the list the caller uploaded.
+// ---------------------------------------------------------------------------------------------
+struct CrtPackedNode
+{
+    float w[12];
+    int32_t child[2];
+    int32_t pad[2];
+};
+static_assert(sizeof(CrtPackedNode) == 64, "node is 64 bytes");
+
+#define CRT_LEAF_TYPE_SHIFT 28
+#define CRT_LEAF_INDEX_MASK 0x0FFFFFFF
+
+struct CrtPackedScene
+{
+    std::vector<CrtPackedNode> nodes;
+    std::vector<float> prims;    // 4 floats per primitive
+    std::vector<float> prim_k;   // 1 float per primitive (rect plane offset; 0 for spheres)
+    std::vector<float> mats;     // 8 floats per primitive
+    std::vector<int32_t> prim_id;
+    crt_bvh_stats stats;
+};
+
+// Builds the BVH over the ACTIVE hittables (Hittable.cuh:311-320 filters inactive ones) and packs everything.
+// Returns false and fills err on invalid input.
+bool crt_pack_scene(const crt_scene_desc* scene, CrtPackedScene* out, std::string* err);
+
+// Host-side layout mirror of the reference scene graph (ref_abi.h) -> flat description.
+struct CrtFlatScene
+{
+    std::vector<crt_hittable> hittables;
+    std::vector<crt_material> materials;
+    std::vector<crt_texture> textures;
+    std::vector<crt_image> images;
+    crt_scene_desc desc() const
+    {
+        crt_scene_desc d;
+        d.hittables = hittables.data(); d.n_hittables = hittables.size();
+        d.materials = materials.data(); d.n_materials = materials.size();
+        d.textures = textures.data();   d.n_textures = textures.size();
+        d.images = images.data();       d.n_images = images.size();
+        return d;
+    }
+};
+bool crt_flatten_reference_world(const void* world, CrtFlatScene* out, std::string* err);

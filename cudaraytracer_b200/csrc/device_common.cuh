@@ -1,0 +1,127 @@
+// device_common.cuh — device-side scene view, Philox4x32-10, small vector helpers.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define CRT_STACK_SIZE 64
+#define CRT_BLOCK_THREADS 256
+
+struct DevImage
+{
+    const uchar4* texels; // RGB8 of the reference (Texture.cuh:76) padded to RGBA8 so one 32-bit load fetches a texel
+    int width, height;
+};
+
+struct DevScene
+{
+    const float4* nodes;   // 4 x float4 per node
+    const float4* prims;   // 1 x float4 per primitive
+    const float* prim_k;   // rect plane offsets
+    const float4* mats;    // 2 x float4 per primitive
+    const int* prim_id;    // leaf slot -> index in the uploaded hittable list
+    const DevImage* images;
+    int n_nodes, n_prims;
+    int smem_nodes, smem_prims, smem_mats; // how many of each the kernels stage in shared memory
+};
+
+struct DevCamera
+{
+    // InputStruct (SharedStructs.h:3-24) + the derived rightV of Kernel.cu:133 computed on the host in IEEE binary32
+    float ox, oy, oz;
+    float fx, fy, fz; // forwardV = orientation
+    float ux, uy, uz; // upV
+    float rx, ry, rz; // rightV = Normalize(Cross(upV, forwardV))
+    float far_plane, near_plane, fov, far_k; // far_k = (1.0f / fov * 10.0f), Kernel.cu:145
+    float bg0[3], bg1[3];
+    float lens_radius, focus_dist; // thin-lens extension; lens_radius == 0 is the reference camera
+};
+
+struct DevCounters
+{
+    unsigned long long paths, rays, box_tests, prim_tests;
+};
+
+struct RenderArgs
+{
+    DevScene scene;
+    DevCamera cam;
+    float4* accum;       // width*height: xyz = radiance sum, w = samples accumulated
+    DevCounters* counters;
+    uint32_t width, height;       // image size
+    uint32_t cover_w, cover_h;    // pixels actually rendered (== width/height unless CRT_FLAG_TRUNCATED_GRID)
+    uint32_t spp_begin, spp_count, spp_stride, max_depth;
+    uint32_t seed_lo, seed_hi;
+    int jitter;
+};
+
+// ------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al., SC'11). Stateless: counter = (pixel, sample, bounce, stream), key = seed.
+// ------------------------------------------------------------------------------------------
+#define CRT_PHILOX_M0 0xD2511F53u
+#define CRT_PHILOX_M1 0xCD9E8D57u
+#define CRT_PHILOX_W0 0x9E3779B9u
+#define CRT_PHILOX_W1 0xBB67AE85u
+
+__host__ __device__ __forceinline__ void crt_mulhilo(uint32_t a, uint32_t b, uint32_t& hi, uint32_t& lo)
+{
+#ifdef __CUDA_ARCH__
+    lo = a * b;
+    hi = __umulhi(a, b);
+#else
+    uint64_t p = (uint64_t)a * b;
+    lo = (uint32_t)p;
+    hi = (uint32_t)(p >> 32);
+#endif
+}
+
+__host__ __device__ __forceinline__ uint4 crt_philox4x32_10(uint4 c, uint32_t k0, uint32_t k1)
+{
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        uint32_t hi0, lo0, hi1, lo1;
+        crt_mulhilo(CRT_PHILOX_M0, c.x, hi0, lo0);
+        crt_mulhilo(CRT_PHILOX_M1, c.z, hi1, lo1);
+        c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
+        k0 += CRT_PHILOX_W0;
+        k1 += CRT_PHILOX_W1;
+    }
+    return c;
+}
+
+#define CRT_STREAM_CAMERA 0u
+#define CRT_STREAM_SCATTER 1u
+
+// Same mapping as curand_uniform (curand_uniform.h:69-72): (0, 1].
+__host__ __device__ __forceinline__ float crt_uniform(uint32_t x)
+{
+    return (float)x * 2.3283064e-10f + (2.3283064e-10f / 2.0f);
+}
+
+// ------------------------------------------------------------------------------------------
+// float3 helpers (operators kept minimal; contraction is left to the compiler in the fast path)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
+__device__ __forceinline__ float3 operator+(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ float3 operator-(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ float3 operator*(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ float3 operator*(float s, float3 a) { return f3(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ float3 operator-(float3 a) { return f3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ float dot3(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
+// Approximate single-instruction forms for the throughput path (MUFU.RCP / MUFU.SQRT; ~1-2 ulp).
+__device__ __forceinline__ float fast_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float fast_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float fast_div(float a, float b) { return __fdividef(a, b); }
+
+// IEEE, never-contracted versions used by the exact path (bit-for-bit the host oracle's arithmetic).
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub_rn(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float div_rn(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float sqrt_rn(float a) { return __fsqrt_rn(a); }
+// Dot (Math.cuh:152-155): ((x*x' + y*y') + z*z'), left to right, unfused.
+__device__ __forceinline__ float dot3_rn(float3 a, float3 b)
+{
+    return add_rn(add_rn(mul_rn(a.x, b.x), mul_rn(a.y, b.y)), mul_rn(a.z, b.z));
+}

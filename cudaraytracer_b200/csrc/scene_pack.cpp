@@ -1,0 +1,415 @@
+// scene_pack.cpp — host BVH build + packing of the scene into the device layout of crt_internal.h.
+//
+// Replaces the reference's BVHNode constructor (Hittable.cuh:303-385), which splits at the median of
+// the LIST ORDER and allocates one managed block per split. The closest hit does not depend on the
+// tree shape, so this builder is free to use a spatial binned-SAH split; only the
+// bounding boxes (Sphere::BoundingBox Hittable.cuh:112-116, *Rect::BoundingBox :171-181) and the
+// inactive-object filter (:311-320) follow the reference.
+
+#include "crt_internal.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <thread>
+
+namespace {
+
+struct Box
+{
+    float lo[3], hi[3];
+    void reset()
+    {
+        for (int i = 0; i < 3; i++) {
+            lo[i] = std::numeric_limits<float>::infinity();
+            hi[i] = -std::numeric_limits<float>::infinity();
+        }
+    }
+    void grow(const Box& b)
+    {
+        for (int i = 0; i < 3; i++) {
+            lo[i] = std::min(lo[i], b.lo[i]);
+            hi[i] = std::max(hi[i], b.hi[i]);
+        }
+    }
+    void grow(const float* p)
+    {
+        for (int i = 0; i < 3; i++) {
+            lo[i] = std::min(lo[i], p[i]);
+            hi[i] = std::max(hi[i], p[i]);
+        }
+    }
+    float half_area() const
+    {
+        float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+        if (!(dx >= 0.f) || !(dy >= 0.f) || !(dz >= 0.f))
+            return 0.f;
+        return dx * dy + dy * dz + dz * dx;
+    }
+};
+
+struct BuildNode
+{
+    Box box;
+    int32_t child[2]; // >= 0 build-node index, < 0: ~prim (index into the active list)
+};
+
+struct Builder
+{
+    std::vector<Box> pbox;
+    std::vector<float> cent; // 3 per prim
+    std::vector<uint32_t> idx;
+    std::vector<BuildNode> nodes;
+    int max_depth = 0;
+
+    static constexpr int kBins = 16;
+
+    Box range_box(uint32_t b, uint32_t e) const
+    {
+        Box r;
+        r.reset();
+        for (uint32_t i = b; i < e; i++)
+            r.grow(pbox[idx[i]]);
+        return r;
+    }
+
+    // Returns the child reference for the range [b, e).
+    int32_t build(uint32_t b, uint32_t e, const Box& bounds, int depth)
+    {
+        max_depth = std::max(max_depth, depth);
+        if (e - b == 1)
+            return ~(int32_t)idx[b];
+
+        Box cb;
+        cb.reset();
+        for (uint32_t i = b; i < e; i++)
+            cb.grow(&cent[3 * (size_t)idx[i]]);
+
+        int best_axis = -1, best_split = -1;
+        float best_cost = std::numeric_limits<float>::infinity();
+        const uint32_t n = e - b;
+        if (n > 2) {
+            for (int ax = 0; ax < 3; ax++) {
+                float ext = cb.hi[ax] - cb.lo[ax];
+                if (!(ext > 0.f))
+                    continue;
+                Box bins[kBins];
+                uint32_t cnt[kBins];
+                for (int k = 0; k < kBins; k++) {
+                    bins[k].reset();
+                    cnt[k] = 0;
+                }
+                float scale = (float)kBins / ext;
+                for (uint32_t i = b; i < e; i++) {
+                    uint32_t p = idx[i];
+                    int k = (int)((cent[3 * (size_t)p + ax] - cb.lo[ax]) * scale);
+                    k = std::min(std::max(k, 0), kBins - 1);
+                    bins[k].grow(pbox[p]);
+                    cnt[k]++;
+                }
+                float right_area[kBins];
+                uint32_t right_cnt[kBins];
+                Box acc;
+                acc.reset();
+                uint32_t c = 0;
+                for (int k = kBins - 1; k > 0; k--) {
+                    acc.grow(bins[k]);
+                    c += cnt[k];
+                    right_area[k] = acc.half_area();
+                    right_cnt[k] = c;
+                }
+                acc.reset();
+                c = 0;
+                for (int k = 0; k < kBins - 1; k++) {
+                    acc.grow(bins[k]);
+                    c += cnt[k];
+                    if (c == 0 || right_cnt[k + 1] == 0)
+                        continue;
+                    float cost = acc.half_area() * (float)c + right_area[k + 1] * (float)right_cnt[k + 1];
+                    if (cost < best_cost) {
+                        best_cost = cost;
+                        best_axis = ax;
+                        best_split = k;
+                    }
+                }
+            }
+        }
+
+        uint32_t mid;
+        if (best_axis >= 0) {
+            float ext = cb.hi[best_axis] - cb.lo[best_axis];
+            float scale = (float)kBins / ext;
+            float lo = cb.lo[best_axis];
+            int ax = best_axis, sp = best_split;
+            auto it = std::partition(idx.begin() + b, idx.begin() + e, [&](uint32_t p) {
+                int k = (int)((cent[3 * (size_t)p + ax] - lo) * scale);
+                k = std::min(std::max(k, 0), kBins - 1);
+                return k <= sp;
+            });
+            mid = (uint32_t)(it - idx.begin());
+        }
+        else {
+            // n == 2, or all centroids coincide: split the range in half along the widest centroid axis.
+            int ax = 0;
+            float e0 = cb.hi[0] - cb.lo[0], e1 = cb.hi[1] - cb.lo[1], e2 = cb.hi[2] - cb.lo[2];
+            if (e1 > e0 && e1 >= e2) ax = 1;
+            else if (e2 > e0 && e2 > e1) ax = 2;
+            mid = b + n / 2;
+            std::nth_element(idx.begin() + b, idx.begin() + mid, idx.begin() + e, [&](uint32_t p, uint32_t q) {
+                float cp = cent[3 * (size_t)p + ax], cq = cent[3 * (size_t)q + ax];
+                return cp < cq || (cp == cq && p < q);
+            });
+        }
+        if (mid == b || mid == e)
+            mid = b + n / 2;
+
+        int32_t me = (int32_t)nodes.size();
+        nodes.emplace_back();
+        Box lb = range_box(b, mid), rb = range_box(mid, e);
+        int32_t l = build(b, mid, lb, depth + 1);
+        int32_t r = build(mid, e, rb, depth + 1);
+        nodes[me].box = bounds;
+        nodes[me].child[0] = l;
+        nodes[me].child[1] = r;
+        return me;
+    }
+};
+
+// Conservative outward padding so that the fused/approximate slab test on the GPU never culls a
+// primitive whose exact test would hit: a few ulps relative to the coordinate, plus an absolute term
+// proportional to the scene extent (the error of lo*idir - o*idir grows with |o|, and ray origins
+// live inside the scene bounds after the first bounce).
+inline float pad_lo(float v, float abs_pad) { return v - (fabsf(v) * 4e-6f + abs_pad); }
+inline float pad_hi(float v, float abs_pad) { return v + (fabsf(v) * 4e-6f + abs_pad); }
+
+void store_box(float* w, int slot, const Box& b, bool empty, float abs_pad)
+{
+    float v[6];
+    if (empty) {
+        for (int i = 0; i < 3; i++) {
+            v[i] = std::numeric_limits<float>::infinity();
+            v[3 + i] = -std::numeric_limits<float>::infinity();
+        }
+    }
+    else {
+        for (int i = 0; i < 3; i++) {
+            v[i] = pad_lo(b.lo[i], abs_pad);
+            v[3 + i] = pad_hi(b.hi[i], abs_pad);
+        }
+    }
+    for (int i = 0; i < 6; i++)
+        w[slot * 6 + i] = v[i];
+}
+
+} // namespace
+
+bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* err)
+{
+    auto t0 = std::chrono::steady_clock::now();
+    if (!sd || (!sd->hittables && sd->n_hittables)) {
+        *err = "scene: NULL hittable list";
+        return false;
+    }
+    if (sd->n_hittables > (uint64_t)CRT_LEAF_INDEX_MASK) {
+        *err = "scene: too many hittables (limit 2^28 - 1)";
+        return false;
+    }
+    // 1. active filter + validation
+    std::vector<uint32_t> active;
+    active.reserve(sd->n_hittables);
+    for (uint64_t i = 0; i < sd->n_hittables; i++) {
+        const crt_hittable& h = sd->hittables[i];
+        if (!h.active)
+            continue;
+        if (h.type < CRT_SPHERE || h.type > CRT_YZRECT) {
+            *err = "scene: hittable " + std::to_string(i) + " has unknown type " + std::to_string(h.type);
+            return false;
+        }
+        if (h.material < 0 || (uint64_t)h.material >= sd->n_materials) {
+            *err = "scene: hittable " + std::to_string(i) + " has material index out of range";
+            return false;
+        }
+        const crt_material& m = sd->materials[h.material];
+        if (m.type < CRT_LAMBERTIAN || m.type > CRT_DIFFUSELIGHT) {
+            *err = "scene: material " + std::to_string(h.material) + " has unknown type";
+            return false;
+        }
+        if (m.type != CRT_DIELECTRIC) {
+            if (m.texture < 0 || (uint64_t)m.texture >= sd->n_textures) {
+                *err = "scene: material " + std::to_string(h.material) + " has texture index out of range";
+                return false;
+            }
+            const crt_texture& t = sd->textures[m.texture];
+            if (t.type < CRT_CONSTANT || t.type > CRT_IMAGE) {
+                *err = "scene: texture " + std::to_string(m.texture) + " has unknown type";
+                return false;
+            }
+            if (t.type == CRT_IMAGE && t.image >= 0 && (uint64_t)t.image >= sd->n_images) {
+                *err = "scene: texture " + std::to_string(m.texture) + " has image index out of range";
+                return false;
+            }
+        }
+        active.push_back((uint32_t)i);
+    }
+    const uint32_t n = (uint32_t)active.size();
+
+    // 2. primitive boxes
+    Builder B;
+    B.pbox.resize(n);
+    B.cent.resize(3 * (size_t)n);
+    B.idx.resize(n);
+    Box all;
+    all.reset();
+    for (uint32_t k = 0; k < n; k++) {
+        const crt_hittable& h = sd->hittables[active[k]];
+        Box& b = B.pbox[k];
+        float hw = h.a / 2, hh = h.b / 2; // the reference computes center -/+ (width / 2) (Hittable.cuh:142-146)
+        switch (h.type) {
+        case CRT_SPHERE:
+            b.lo[0] = h.cx - h.a; b.lo[1] = h.cy - h.a; b.lo[2] = h.cz - h.a;
+            b.hi[0] = h.cx + h.a; b.hi[1] = h.cy + h.a; b.hi[2] = h.cz + h.a;
+            if (h.a < 0.f) // negative radius (hollow-glass trick): box must still be ordered
+                for (int i = 0; i < 3; i++)
+                    std::swap(b.lo[i], b.hi[i]);
+            break;
+        case CRT_XYRECT:
+            b.lo[0] = h.cx - hw; b.hi[0] = h.cx + hw; b.lo[1] = h.cy - hh; b.hi[1] = h.cy + hh;
+            b.lo[2] = h.cz - 0.0001f; b.hi[2] = h.cz + 0.0001f;
+            break;
+        case CRT_XZRECT:
+            b.lo[0] = h.cx - hw; b.hi[0] = h.cx + hw; b.lo[2] = h.cz - hh; b.hi[2] = h.cz + hh;
+            b.lo[1] = h.cy - 0.0001f; b.hi[1] = h.cy + 0.0001f;
+            break;
+        default: // CRT_YZRECT: height spans y and width spans z (Hittable.cuh:253-257)
+            b.lo[1] = h.cy - hh; b.hi[1] = h.cy + hh; b.lo[2] = h.cz - hw; b.hi[2] = h.cz + hw;
+            b.lo[0] = h.cx - 0.0001f; b.hi[0] = h.cx + 0.0001f;
+            break;
+        }
+        for (int i = 0; i < 3; i++)
+            B.cent[3 * (size_t)k + i] = 0.5f * (b.lo[i] + b.hi[i]);
+        B.idx[k] = k;
+        all.grow(b);
+    }
+
+    // 3. build
+    B.nodes.reserve(n ? n : 1);
+    if (n >= 2) {
+        B.build(0, n, all, 1); // the root is always build-node 0
+    }
+    else {
+        B.nodes.emplace_back();
+        B.nodes[0].box = all;
+        B.nodes[0].child[0] = n == 1 ? ~0 : 0;
+        B.nodes[0].child[1] = 0; // marked empty below
+    }
+
+    // 4. breadth-first emission; leaves get their final primitive slot in BFS discovery order so that
+    //    primitives referenced by neighbouring nodes are neighbours in memory too.
+    const uint32_t nn = (uint32_t)B.nodes.size();
+    out->nodes.assign(nn, CrtPackedNode());
+    out->prims.assign(4 * (size_t)n, 0.f);
+    out->prim_k.assign(n, 0.f);
+    out->mats.assign(8 * (size_t)n, 0.f);
+    out->prim_id.assign(n, -1);
+    std::vector<int32_t> order;   // BFS order -> build node
+    std::vector<int32_t> newidx(nn, -1);
+    order.reserve(nn);
+    order.push_back(0);
+    newidx[0] = 0;
+    for (size_t q = 0; q < order.size(); q++) {
+        const BuildNode& bn = B.nodes[order[q]];
+        for (int c = 0; c < 2; c++) {
+            if (n >= 2 && bn.child[c] >= 0) {
+                newidx[bn.child[c]] = (int32_t)order.size();
+                order.push_back(bn.child[c]);
+            }
+        }
+    }
+    uint32_t next_prim = 0;
+    double sah = 0.0;
+    const float root_area = all.half_area();
+    float extent = 0.f;
+    if (n)
+        for (int i = 0; i < 3; i++) extent = std::max(extent, std::max(fabsf(all.lo[i]), fabsf(all.hi[i])));
+    const float abs_pad = 1e-7f + 4e-7f * extent;
+    for (uint32_t q = 0; q < nn; q++) {
+        const BuildNode& bn = B.nodes[order[q]];
+        CrtPackedNode& pn = out->nodes[q];
+        memset(&pn, 0, sizeof(pn));
+        if (root_area > 0.f)
+            sah += 1.0 * bn.box.half_area() / root_area;
+        for (int c = 0; c < 2; c++) {
+            bool empty = (n < 2) && (c == 1 || n == 0);
+            if (empty) {
+                store_box(pn.w, c, all, true, abs_pad);
+                pn.child[c] = ~0; // leaf 0 behind an empty box: never reached
+                continue;
+            }
+            int32_t ch = bn.child[c];
+            if (ch >= 0) {
+                store_box(pn.w, c, B.nodes[ch].box, false, abs_pad);
+                pn.child[c] = newidx[ch];
+            }
+            else {
+                uint32_t k = (uint32_t)~ch;          // index into the active list
+                uint32_t slot = next_prim++;
+                const crt_hittable& h = sd->hittables[active[k]];
+                store_box(pn.w, c, B.pbox[k], false, abs_pad);
+                if (root_area > 0.f)
+                    sah += 1.0 * B.pbox[k].half_area() / root_area;
+                pn.child[c] = ~(int32_t)(((uint32_t)h.type << CRT_LEAF_TYPE_SHIFT) | slot);
+                float* pr = &out->prims[4 * (size_t)slot];
+                float hw = h.a / 2, hh = h.b / 2;
+                switch (h.type) {
+                case CRT_SPHERE: pr[0] = h.cx; pr[1] = h.cy; pr[2] = h.cz; pr[3] = h.a; break;
+                case CRT_XYRECT: pr[0] = h.cx - hw; pr[1] = h.cx + hw; pr[2] = h.cy - hh; pr[3] = h.cy + hh; out->prim_k[slot] = h.cz; break;
+                case CRT_XZRECT: pr[0] = h.cx - hw; pr[1] = h.cx + hw; pr[2] = h.cz - hh; pr[3] = h.cz + hh; out->prim_k[slot] = h.cy; break;
+                default:         pr[0] = h.cy - hh; pr[1] = h.cy + hh; pr[2] = h.cz - hw; pr[3] = h.cz + hw; out->prim_k[slot] = h.cx; break;
+                }
+                out->prim_id[slot] = (int32_t)active[k];
+                // material record
+                const crt_material& m = sd->materials[h.material];
+                float* mr = &out->mats[8 * (size_t)slot];
+                uint32_t bits = (uint32_t)m.type;
+                float param = m.param;
+                if (m.type == CRT_METAL)
+                    param = m.param < 1 ? m.param : 1; // Material.cuh:71
+                if (m.type == CRT_DIFFUSELIGHT)
+                    param = (float)m.light_intensity;  // int * Vec3 in the reference (Material.cuh:168-172)
+                if (m.type != CRT_DIELECTRIC) {
+                    const crt_texture& t = sd->textures[m.texture];
+                    bits |= (uint32_t)t.type << 4;
+                    if (t.type == CRT_CONSTANT) {
+                        mr[0] = t.color[0]; mr[1] = t.color[1]; mr[2] = t.color[2];
+                    }
+                    else if (t.type == CRT_CHECKER) {
+                        mr[0] = t.odd[0]; mr[1] = t.odd[1]; mr[2] = t.odd[2];
+                        mr[4] = t.even[0]; mr[5] = t.even[1]; mr[6] = t.even[2];
+                    }
+                    else {
+                        bool has = t.image >= 0 && sd->images[t.image].pixels != nullptr;
+                        bits |= (uint32_t)(has ? t.image + 1 : 0) << 8;
+                    }
+                }
+                else {
+                    mr[0] = mr[1] = mr[2] = 1.0f; // attenuation (1,1,1), Material.cuh:112
+                }
+                mr[3] = param;
+                memcpy(&mr[7], &bits, 4);
+            }
+        }
+    }
+
+    auto t1 = std::chrono::steady_clock::now();
+    memset(&out->stats, 0, sizeof(out->stats));
+    out->stats.n_prims = n;
+    out->stats.n_nodes = nn;
+    out->stats.max_depth = (uint64_t)B.max_depth;
+    out->stats.sah_cost = sah;
+    out->stats.build_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    out->stats.node_bytes = (uint64_t)nn * sizeof(CrtPackedNode);
+    out->stats.prim_bytes = (uint64_t)n * (16 + 4 + 32 + 4);
+    return true;
+}

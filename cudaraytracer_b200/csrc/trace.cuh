@@ -1,0 +1,249 @@
+// trace.cuh — closest-hit query: BVH2 traversal + primitive tests.
+//
+// Replaces BVHNode::Hit / PerformHit (Hittable.cuh:387-439,470-485), AABB::Hit (AABB.cuh:30-50),
+// Sphere::Hit (Hittable.cuh:80-110) and XY/XZ/YZRect::Hit (Hittable.cuh:139-168,195-224,251-280).
+// Semantics kept from the reference: t_min = 0.001f in ray-parameter units (Kernel.cu:40), the ray
+// direction is NOT normalised, spheres accept a root iff t_min < t < t_max (strict), near root first;
+// rects accept iff !(t < t_min || t > t_max) and the point is inside the closed rectangle.
+// Only the hit distance and the leaf code are produced here; point, normal and UV are deferred to
+// shading (the reference recomputes them, with acos/atan2, for every accepted candidate).
+#pragma once
+
+#include "device_common.cuh"
+
+struct SceneView
+{
+    const float4* g_nodes;
+    const float4* g_prims;
+    const float* g_prim_k;
+    const float4* g_mats;
+    const float4* s_nodes;
+    const float4* s_prims;
+    const float4* s_mats;
+    const DevImage* images;
+    int smem_nodes, smem_prims, smem_mats;
+};
+
+template <bool SMEM_ALL> __device__ __forceinline__ void load_node(const SceneView& S, int i, float4& w0, float4& w1, float4& w2, int2& ch)
+{
+    if (SMEM_ALL || i < S.smem_nodes) {
+        const float4* p = S.s_nodes + 4 * i;
+        w0 = p[0]; w1 = p[1]; w2 = p[2];
+        float4 w3 = p[3];
+        ch = make_int2(__float_as_int(w3.x), __float_as_int(w3.y));
+    }
+    else {
+        const float4* p = S.g_nodes + 4 * (size_t)i;
+        w0 = __ldg(p); w1 = __ldg(p + 1); w2 = __ldg(p + 2);
+        float4 w3 = __ldg(p + 3);
+        ch = make_int2(__float_as_int(w3.x), __float_as_int(w3.y));
+    }
+}
+
+template <bool SMEM_ALL> __device__ __forceinline__ float4 load_prim(const SceneView& S, int i)
+{
+    if (SMEM_ALL || i < S.smem_prims)
+        return S.s_prims[i];
+    return __ldg(S.g_prims + i);
+}
+
+template <bool SMEM_ALL> __device__ __forceinline__ void load_mat(const SceneView& S, int i, float4& m0, float4& m1)
+{
+    if (SMEM_ALL || i < S.smem_mats) {
+        m0 = S.s_mats[2 * i];
+        m1 = S.s_mats[2 * i + 1];
+    }
+    else {
+        m0 = __ldg(S.g_mats + 2 * (size_t)i);
+        m1 = __ldg(S.g_mats + 2 * (size_t)i + 1);
+    }
+}
+
+// Stages the first smem_* entries of each table into dynamic shared memory. Call from every thread, then __syncthreads().
+__device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem)
+{
+    SceneView S;
+    S.g_nodes = D.nodes; S.g_prims = D.prims; S.g_prim_k = D.prim_k; S.g_mats = D.mats; S.images = D.images;
+    S.smem_nodes = D.smem_nodes; S.smem_prims = D.smem_prims; S.smem_mats = D.smem_mats;
+    float4* sn = smem;
+    float4* sp = sn + 4 * (size_t)D.smem_nodes;
+    float4* sm = sp + D.smem_prims;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    for (int i = tid; i < 4 * D.smem_nodes; i += nt) sn[i] = __ldg(D.nodes + i);
+    for (int i = tid; i < D.smem_prims; i += nt) sp[i] = __ldg(D.prims + i);
+    for (int i = tid; i < 2 * D.smem_mats; i += nt) sm[i] = __ldg(D.mats + i);
+    S.s_nodes = sn; S.s_prims = sp; S.s_mats = sm;
+    return S;
+}
+
+struct Hit
+{
+    float t;
+    int leaf; // (type << 28) | primitive slot; -1 = miss
+};
+
+// Sphere::Hit, Hittable.cuh:82-107. Returns the accepted root or a negative sentinel.
+template <bool EXACT>
+__device__ __forceinline__ bool sphere_test(float4 sph, float3 o, float3 d, float a, float inv_a, float t_min, float t_max, float& t_out)
+{
+    if (EXACT) {
+        float3 oc = f3(sub_rn(o.x, sph.x), sub_rn(o.y, sph.y), sub_rn(o.z, sph.z));
+        float b = dot3_rn(oc, d);
+        float c = sub_rn(dot3_rn(oc, oc), mul_rn(sph.w, sph.w));
+        float disc = sub_rn(mul_rn(b, b), mul_rn(a, c));
+        if (disc > 0.f) {
+            float sq = sqrt_rn(disc);
+            float t = div_rn(sub_rn(-b, sq), a);
+            if (t < t_max && t > t_min) { t_out = t; return true; }
+            t = div_rn(add_rn(-b, sq), a);
+            if (t < t_max && t > t_min) { t_out = t; return true; }
+        }
+        return false;
+    }
+    else {
+        float3 oc = o - f3(sph.x, sph.y, sph.z);
+        float b = dot3(oc, d);
+        float c = dot3(oc, oc) - sph.w * sph.w;
+        float disc = b * b - a * c;
+        if (disc > 0.f) {
+            float sq = fast_sqrt(disc);
+            float t = (-b - sq) * inv_a;
+            if (t < t_max && t > t_min) { t_out = t; return true; }
+            t = (-b + sq) * inv_a;
+            if (t < t_max && t > t_min) { t_out = t; return true; }
+        }
+        return false;
+    }
+}
+
+// XYRect/XZRect/YZRect::Hit. r = {a0, a1, b0, b1}, k = plane offset. (oa, ob, ok)/(da, db, dk) are the ray
+// components along the rect's two in-plane axes and its normal axis.
+template <bool EXACT>
+__device__ __forceinline__ bool rect_test(float4 r, float k, float oa, float ob, float ok, float da, float db, float dk, float t_min,
+                                          float t_max, float& t_out)
+{
+    float t, pa, pb;
+    if (EXACT) {
+        float inv = div_rn(1.0f, dk);
+        t = mul_rn(sub_rn(k, ok), inv);
+        if (t < t_min || t > t_max) return false;
+        pa = add_rn(oa, mul_rn(t, da));
+        pb = add_rn(ob, mul_rn(t, db));
+    }
+    else {
+        float inv = fast_rcp(dk);
+        t = (k - ok) * inv;
+        if (t < t_min || t > t_max) return false;
+        pa = oa + t * da;
+        pb = ob + t * db;
+    }
+    if (pa < r.x || pa > r.y || pb < r.z || pb > r.w) return false;
+    t_out = t;
+    return true;
+}
+
+template <bool EXACT, bool SMEM_ALL>
+__device__ __forceinline__ bool leaf_test(const SceneView& S, int code, float3 o, float3 d, float a, float inv_a, float t_min,
+                                          float t_max, float& t_out)
+{
+    const int slot = code & CRT_LEAF_INDEX_MASK;
+    const int type = code >> CRT_LEAF_TYPE_SHIFT;
+    float4 p = load_prim<SMEM_ALL>(S, slot);
+    if (type == CRT_SPHERE)
+        return sphere_test<EXACT>(p, o, d, a, inv_a, t_min, t_max, t_out);
+    float k = __ldg(S.g_prim_k + slot);
+    if (type == CRT_XYRECT) return rect_test<EXACT>(p, k, o.x, o.y, o.z, d.x, d.y, d.z, t_min, t_max, t_out);
+    if (type == CRT_XZRECT) return rect_test<EXACT>(p, k, o.x, o.z, o.y, d.x, d.z, d.y, t_min, t_max, t_out);
+    return rect_test<EXACT>(p, k, o.y, o.z, o.x, d.y, d.z, d.x, t_min, t_max, t_out);
+}
+
+// Closest hit in (t_min, t_max). Near-first ordered descent with a per-thread stack.
+template <bool EXACT, bool COUNT, bool SMEM_ALL>
+__device__ __forceinline__ Hit closest_hit(const SceneView& S, float3 o, float3 d, float t_min, float t_max, unsigned& n_box,
+                                           unsigned& n_prim)
+{
+    Hit h;
+    h.t = t_max;
+    h.leaf = -1;
+
+    // a = Dot(dir, dir), Hittable.cuh:83
+    float a, inv_a;
+    if (EXACT) { a = dot3_rn(d, d); inv_a = 0.f; }
+    else { a = dot3(d, d); inv_a = fast_rcp(a); }
+
+    // Reciprocal direction for the slab test. |d| is clamped away from zero so that 0 * inf never appears.
+    const float tiny = 1e-18f;
+    float3 dc = f3(fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x, fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y,
+                   fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
+    float3 id, ood;
+    if (EXACT) {
+        id = f3(div_rn(1.0f, dc.x), div_rn(1.0f, dc.y), div_rn(1.0f, dc.z));
+        ood = f3(0.f, 0.f, 0.f);
+    }
+    else {
+        id = f3(fast_rcp(dc.x), fast_rcp(dc.y), fast_rcp(dc.z));
+        ood = f3(o.x * id.x, o.y * id.y, o.z * id.z);
+    }
+
+    int stack[CRT_STACK_SIZE];
+    int sp = 0;
+    int node = 0;
+
+    while (true) {
+        float4 w0, w1, w2;
+        int2 ch;
+        load_node<SMEM_ALL>(S, node, w0, w1, w2, ch);
+        if (COUNT) n_box += 2;
+
+        float lx0, ly0, lz0, hx0, hy0, hz0, lx1, ly1, lz1, hx1, hy1, hz1;
+        if (EXACT) {
+            lx0 = (w0.x - o.x) * id.x; ly0 = (w0.y - o.y) * id.y; lz0 = (w0.z - o.z) * id.z;
+            hx0 = (w0.w - o.x) * id.x; hy0 = (w1.x - o.y) * id.y; hz0 = (w1.y - o.z) * id.z;
+            lx1 = (w1.z - o.x) * id.x; ly1 = (w1.w - o.y) * id.y; lz1 = (w2.x - o.z) * id.z;
+            hx1 = (w2.y - o.x) * id.x; hy1 = (w2.z - o.y) * id.y; hz1 = (w2.w - o.z) * id.z;
+        }
+        else {
+            lx0 = fmaf(w0.x, id.x, -ood.x); ly0 = fmaf(w0.y, id.y, -ood.y); lz0 = fmaf(w0.z, id.z, -ood.z);
+            hx0 = fmaf(w0.w, id.x, -ood.x); hy0 = fmaf(w1.x, id.y, -ood.y); hz0 = fmaf(w1.y, id.z, -ood.z);
+            lx1 = fmaf(w1.z, id.x, -ood.x); ly1 = fmaf(w1.w, id.y, -ood.y); lz1 = fmaf(w2.x, id.z, -ood.z);
+            hx1 = fmaf(w2.y, id.x, -ood.x); hy1 = fmaf(w2.z, id.y, -ood.y); hz1 = fmaf(w2.w, id.z, -ood.z);
+        }
+        float tn0 = fmaxf(fmaxf(fminf(lx0, hx0), fminf(ly0, hy0)), fmaxf(fminf(lz0, hz0), t_min));
+        float tf0 = fminf(fminf(fmaxf(lx0, hx0), fmaxf(ly0, hy0)), fminf(fmaxf(lz0, hz0), h.t));
+        float tn1 = fmaxf(fmaxf(fminf(lx1, hx1), fminf(ly1, hy1)), fmaxf(fminf(lz1, hz1), t_min));
+        float tf1 = fminf(fminf(fmaxf(lx1, hx1), fmaxf(ly1, hy1)), fminf(fmaxf(lz1, hz1), h.t));
+        // Slightly widened acceptance: the boxes are padded on the host, and <= keeps degenerate (flat) boxes alive.
+        const bool h0 = tn0 <= tf0 * 1.0000004f;
+        const bool h1 = tn1 <= tf1 * 1.0000004f;
+
+        int next;
+        if (h0 && h1) {
+            int c0 = ch.x, c1 = ch.y;
+            if (tn1 < tn0) { int t = c0; c0 = c1; c1 = t; }
+            next = c0;
+            stack[sp++] = c1;
+        }
+        else if (h0) next = ch.x;
+        else if (h1) next = ch.y;
+        else {
+            if (sp == 0) break;
+            next = stack[--sp];
+        }
+
+        bool done = false;
+        while (next < 0) {
+            const int code = ~next;
+            if (COUNT) n_prim++;
+            float t;
+            if (leaf_test<EXACT, SMEM_ALL>(S, code, o, d, a, inv_a, t_min, h.t, t)) {
+                h.t = t;
+                h.leaf = code;
+            }
+            if (sp == 0) { done = true; break; }
+            next = stack[--sp];
+        }
+        if (done) break;
+        node = next;
+    }
+    return h;
+}

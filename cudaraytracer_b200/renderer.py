@@ -1,0 +1,215 @@
+"""Thin Python host over the C ABI (include/crt.h) for tests and bench.py.
+
+Names follow the reference's domain: a Scene is the hittable list + materials + textures
+(CudaLayer::GenerateWorld, CudaLayer.cpp:103-256), the camera is its InputStruct
+(SharedStructs.h:3-24), Renderer.render() is LaunchKernel (Kernel.cu:178-191) with a progressive
+accumulation buffer. All rendering happens in libcrt.so on the GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+
+
+class CrtError(RuntimeError):
+    pass
+
+
+def _check(status: int, ctx=None):
+    if status != capi.CRT_OK:
+        lib = capi.load()
+        msg = lib.crt_last_error_string(ctx)
+        raise CrtError(f"crt status {status}: {msg.decode() if msg else '?'}")
+
+
+class Scene:
+    """Owns a crt_scene_builder (generated scene) or numpy-backed arrays (custom scene)."""
+
+    def __init__(self):
+        self._builder = None
+        self._keep = []
+        self.desc = None
+
+    @classmethod
+    def generate(cls, kind: int, seed: int = 1984, size_hint: int = 0) -> "Scene":
+        lib = capi.load()
+        s = cls()
+        b = C.c_void_p()
+        _check(lib.crt_scene_generate(kind, seed, size_hint, C.byref(b)))
+        s._builder = b
+        s.desc = lib.crt_scene_builder_desc(b).contents
+        return s
+
+    @classmethod
+    def from_arrays(cls, hittables, materials, textures, images=()) -> "Scene":
+        """hittables: list of dict(type, cx, cy, cz, a, b=0, material, active=1); materials: dict(type, texture, param,
+        light_intensity); textures: dict(type, image, color, odd, even); images: list of HxWx3 uint8 arrays or None."""
+        s = cls()
+        H = (capi.Hittable * max(len(hittables), 1))()
+        for i, h in enumerate(hittables):
+            H[i] = capi.Hittable(h["type"], h.get("active", 1), h["cx"], h["cy"], h["cz"], h["a"], h.get("b", 0.0), h["material"])
+        M = (capi.Material * max(len(materials), 1))()
+        for i, m in enumerate(materials):
+            M[i] = capi.Material(m["type"], m.get("texture", -1), m.get("param", 0.0), m.get("light_intensity", 0))
+        T = (capi.Texture * max(len(textures), 1))()
+        for i, t in enumerate(textures):
+            T[i] = capi.Texture(t["type"], t.get("image", -1), (C.c_float * 3)(*t.get("color", (0, 0, 0))),
+                                (C.c_float * 3)(*t.get("odd", (0, 0, 0))), (C.c_float * 3)(*t.get("even", (0, 0, 0))), 0)
+        I = (capi.Image * max(len(images), 1))()
+        for i, im in enumerate(images):
+            if im is None:
+                I[i] = capi.Image(None, 0, 0)
+            else:
+                arr = np.ascontiguousarray(im, dtype=np.uint8)
+                assert arr.ndim == 3 and arr.shape[2] == 3
+                s._keep.append(arr)
+                I[i] = capi.Image(arr.ctypes.data_as(C.POINTER(C.c_uint8)), arr.shape[1], arr.shape[0])
+        s._keep += [H, M, T, I]
+        s.desc = capi.SceneDesc(H, len(hittables), M, len(materials), T, len(textures), I, len(images))
+        return s
+
+    def default_camera(self, width: int, height: int) -> capi.InputStruct:
+        if self._builder is None:
+            raise CrtError("default_camera: only generated scenes carry a camera")
+        cam = capi.InputStruct()
+        _check(capi.load().crt_scene_builder_camera(self._builder, width, height, C.byref(cam)))
+        return cam
+
+    @property
+    def n_hittables(self) -> int:
+        return int(self.desc.n_hittables)
+
+    def hittable_array(self) -> np.ndarray:
+        """(n, 8) view: type, active, cx, cy, cz, a, b, material (floats reinterpreted per column by the caller)."""
+        n = self.n_hittables
+        buf = C.string_at(self.desc.hittables, n * C.sizeof(capi.Hittable))
+        return np.frombuffer(buf, dtype=np.dtype([("type", "<i4"), ("active", "<i4"), ("cx", "<f4"), ("cy", "<f4"), ("cz", "<f4"),
+                                                  ("a", "<f4"), ("b", "<f4"), ("material", "<i4")]))
+
+    def host_bytes(self) -> int:
+        d = self.desc
+        n = d.n_hittables * 32 + d.n_materials * 16 + d.n_textures * 48
+        for i in range(d.n_images):
+            if d.images[i].pixels:
+                n += d.images[i].width * d.images[i].height * 3
+        return int(n)
+
+    def __del__(self):
+        if self._builder is not None:
+            try:
+                capi.load().crt_scene_builder_free(self._builder)
+            except Exception:
+                pass
+            self._builder = None
+
+
+def look_camera(position, orientation, fov_deg=45.0, near=0.1, far=10.0, up=(0.0, 1.0, 0.0),
+                bg0=(1.0, 1.0, 1.0), bg1=(0.5, 0.7, 1.0)) -> capi.InputStruct:
+    """Camera fields -> InputStruct exactly as CudaLayer::OnAttach does (CudaLayer.cpp:45-62)."""
+    f3 = C.c_float * 3
+    cam = capi.InputStruct()
+    _check(capi.load().crt_camera_look(f3(*position), f3(*orientation), f3(*up), fov_deg, near, far, f3(*bg0), f3(*bg1), C.byref(cam)))
+    return cam
+
+
+class Renderer:
+    def __init__(self, device: int = 0):
+        self.lib = capi.load()
+        self.ctx = C.c_void_p()
+        _check(self.lib.crt_context_create(device, C.byref(self.ctx)))
+        self.width = self.height = 0
+
+    def close(self):
+        if self.ctx:
+            self.lib.crt_context_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, st):
+        _check(st, self.ctx)
+
+    def set_stream(self, cuda_stream: int):
+        self._ck(self.lib.crt_set_stream(self.ctx, C.c_void_p(cuda_stream)))
+
+    def upload(self, scene: Scene):
+        self._ck(self.lib.crt_scene_upload(self.ctx, C.byref(scene.desc)))
+
+    def bvh_stats(self) -> capi.BvhStats:
+        st = capi.BvhStats()
+        self._ck(self.lib.crt_bvh_get_stats(self.ctx, C.byref(st)))
+        return st
+
+    def set_camera(self, cam: capi.InputStruct):
+        self._ck(self.lib.crt_set_camera(self.ctx, C.byref(cam)))
+
+    def set_lens(self, aperture: float, focus_dist: float):
+        self._ck(self.lib.crt_set_lens(self.ctx, aperture, focus_dist))
+
+    def resize(self, width: int, height: int):
+        self._ck(self.lib.crt_framebuffer_resize(self.ctx, width, height))
+        self.width, self.height = width, height
+
+    def clear(self):
+        self._ck(self.lib.crt_accum_clear(self.ctx))
+
+    def set_accum_device_buffer(self, ptr: int):
+        self._ck(self.lib.crt_set_accum_device_buffer(self.ctx, C.c_void_p(ptr)))
+
+    def render(self, spp: int, max_depth: int, spp_begin: int = 0, spp_stride: int = 1, seed: int = 1984,
+               variant: int = capi.VARIANT_AUTO, jitter: int = capi.JITTER_RANDOM, flags: int = 0):
+        p = capi.RenderParams(spp_begin, spp, spp_stride, max_depth, seed, variant, jitter, flags, 0)
+        self._ck(self.lib.crt_render(self.ctx, C.byref(p)))
+
+    def synchronize(self):
+        self._ck(self.lib.crt_synchronize(self.ctx))
+
+    def last_render_ms(self) -> float:
+        ms = C.c_float()
+        self._ck(self.lib.crt_last_render_ms(self.ctx, C.byref(ms)))
+        return float(ms.value)
+
+    def resolve(self, out: np.ndarray | None = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.height, self.width), dtype=np.uint32)
+        assert out.dtype == np.uint32 and out.size == self.width * self.height and out.flags.c_contiguous
+        self._ck(self.lib.crt_resolve(self.ctx, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def resolve_device(self, ptr: int):
+        self._ck(self.lib.crt_resolve_device(self.ctx, C.c_void_p(ptr)))
+
+    def read_accum(self) -> np.ndarray:
+        out = np.empty((self.height, self.width, 4), dtype=np.float32)
+        self._ck(self.lib.crt_read_accum(self.ctx, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def primary_ids(self, jitter: int = capi.JITTER_CENTER, seed: int = 1984) -> np.ndarray:
+        out = np.empty((self.height, self.width), dtype=np.int32)
+        self._ck(self.lib.crt_primary_ids(self.ctx, jitter, seed, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def counters(self) -> capi.Counters:
+        c = capi.Counters()
+        self._ck(self.lib.crt_get_counters(self.ctx, C.byref(c)))
+        return c
+
+    def reset_counters(self):
+        self._ck(self.lib.crt_reset_counters(self.ctx))
+
+
+def unpack_rgba8(img: np.ndarray) -> np.ndarray:
+    """(H, W) packed A<<24|B<<16|G<<8|R -> (H, W, 3) uint8 RGB."""
+    return np.stack([img & 255, (img >> 8) & 255, (img >> 16) & 255], axis=-1).astype(np.uint8)
+
+
+def write_ppm(path: str, img: np.ndarray, flip_rows: bool = True):
+    img = np.ascontiguousarray(img, dtype=np.uint32)
+    _check(capi.load().crt_write_ppm(path.encode(), img.ctypes.data_as(C.c_void_p), img.shape[1], img.shape[0], int(flip_rows)))

@@ -1,0 +1,197 @@
+/*
+ * crt.h — C ABI of the B200-native path tracer that replaces CudaRayTracer's render path.
+ *
+ * Boundary being replaced (reference = Trippasch/CudaRayTracer, paths relative to CudaRayTracer/src):
+ *   - Cuda/Kernel.cu:178-204      extern "C" LaunchKernel / LaunchRandInit / LaunchRenderInit
+ *     (re-declared by the caller in Cuda/CudaLayer.cpp:12-19). Those three symbols are exported
+ *     unchanged by this library (see crt_legacy.h); everything in this header is the native
+ *     surface they are built on.
+ *   - Utils/SharedStructs.h:3-24  InputStruct (camera + background block passed by value)
+ *   - Hittables/Hittable.cuh:30-38, Material.cuh:6-12, Texture.cuh:7-12  the enum values
+ *
+ * Conventions: plain pointers and sizes, no C++ or torch types. Every entry point returns a
+ * crt_status (never exits the process; the reference's checkCudaErrors aborts, helper_cuda.h:599-612).
+ * Pointers are HOST pointers unless the name says "device". Framebuffer row 0 is the BOTTOM of the
+ * view, as in the reference (CudaLayer.cpp:402 draws it V-flipped).
+ */
+#ifndef CRT_H
+#define CRT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CRT_ABI_VERSION 1
+
+typedef enum crt_status {
+    CRT_OK = 0,
+    CRT_ERR_INVALID = 1,     /* bad argument */
+    CRT_ERR_CUDA = 2,        /* a CUDA runtime call failed; see crt_last_error_string */
+    CRT_ERR_NOMEM = 3,
+    CRT_ERR_UNSUPPORTED = 4,
+    CRT_ERR_STATE = 5        /* call order violated (e.g. render before scene upload) */
+} crt_status;
+
+/* Values equal the reference enums so a record can be copied across without translation. */
+enum { CRT_SPHERE = 0, CRT_XYRECT = 1, CRT_XZRECT = 2, CRT_YZRECT = 3 };            /* Hittable.cuh:30-38 */
+enum { CRT_LAMBERTIAN = 0, CRT_METAL = 1, CRT_DIELECTRIC = 2, CRT_DIFFUSELIGHT = 3 }; /* Material.cuh:6-12 */
+enum { CRT_CONSTANT = 0, CRT_CHECKER = 1, CRT_IMAGE = 2 };                           /* Texture.cuh:7-12 */
+
+/* One hittable of the scene list (reference: Hittable + Sphere / XYRect / XZRect / YZRect,
+ * Hittable.cuh:47-67,69-126,128-294). 32 bytes. */
+typedef struct crt_hittable {
+    int32_t type;      /* CRT_SPHERE ... CRT_YZRECT */
+    int32_t active;    /* Hittable::isActive; inactive entries are skipped by the BVH build (Hittable.cuh:311-320) */
+    float cx, cy, cz;  /* Sphere::center / *Rect::center */
+    float a;           /* Sphere::radius, or rect width  */
+    float b;           /* unused for spheres, or rect height */
+    int32_t material;  /* index into crt_scene_desc.materials */
+} crt_hittable;
+
+/* Material + Lambertian/Metal/Dielectric/DiffuseLight (Material.cuh:19-177). 16 bytes. */
+typedef struct crt_material {
+    int32_t type;            /* CRT_LAMBERTIAN ... */
+    int32_t texture;         /* albedo texture index (ignored for dielectric) */
+    float param;             /* Metal::fuzz (clamped to <=1 on upload, Material.cuh:71) | Dielectric::ir */
+    int32_t light_intensity; /* DiffuseLight::light_intensity (an int in the reference, Material.cuh:152) */
+} crt_material;
+
+/* Texture + Constant/Checker/Image (Texture.cuh:18-109). A Checker's two Constant children are
+ * folded into the record. 48 bytes. */
+typedef struct crt_texture {
+    int32_t type;     /* CRT_CONSTANT ... */
+    int32_t image;    /* index into crt_scene_desc.images for CRT_IMAGE, else -1 */
+    float color[3];   /* Constant::color */
+    float odd[3];     /* Checker::odd->color  (picked when the sine product is < 0) */
+    float even[3];    /* Checker::even->color */
+    int32_t pad_;
+} crt_texture;
+
+/* Image (Texture.cuh:70-109): tightly packed RGB8, bytes_per_pixel is always 3 in the reference.
+ * pixels == NULL reproduces the reference's "no data" cyan (Texture.cuh:85-86). */
+typedef struct crt_image {
+    const uint8_t* pixels;
+    int32_t width, height;
+} crt_image;
+
+typedef struct crt_scene_desc {
+    const crt_hittable* hittables; uint64_t n_hittables;
+    const crt_material* materials; uint64_t n_materials;
+    const crt_texture* textures;   uint64_t n_textures;
+    const crt_image* images;       uint64_t n_images;
+} crt_scene_desc;
+
+/* Field-for-field InputStruct (SharedStructs.h:3-24). 72 bytes. fov is in RADIANS and, as in the
+ * reference camera (Kernel.cu:130-146), slides the ray start along `orientation`. */
+typedef struct crt_input_struct {
+    float origin_x, origin_y, origin_z;
+    float orientation_x, orientation_y, orientation_z;
+    float up_x, up_y, up_z;   /* the caller passes normalize(cross(orientation, right)), CudaLayer.cpp:45-62 */
+    float far_plane, near_plane, fov;
+    float background_start[3];
+    float background_end[3];
+} crt_input_struct;
+
+enum { CRT_VARIANT_AUTO = 0, CRT_VARIANT_MEGAKERNEL = 1, CRT_VARIANT_WAVEFRONT = 2 };
+enum { CRT_JITTER_RANDOM = 0,   /* Philox jitter in (0,1], like curand_uniform (Kernel.cu:139-140) */
+       CRT_JITTER_CENTER = 1 }; /* xi1 = xi2 = 0.5: RNG-free ray generation for ID parity */
+enum { CRT_FLAG_EXACT_MATH = 1u,      /* IEEE, unfused arithmetic in ray generation + primitive tests */
+       CRT_FLAG_COUNT_TESTS = 2u,     /* also count box / primitive tests (slower; for the roofline figure) */
+       CRT_FLAG_TRUNCATED_GRID = 4u   /* reproduce the reference's W/16 x H/16 launch grid (Kernel.cu:183-184) */ };
+
+typedef struct crt_render_params {
+    uint32_t spp_begin;   /* first sample index of this call (Philox counter word) */
+    uint32_t spp_count;   /* samples per pixel added to the accumulation buffer by this call */
+    uint32_t spp_stride;  /* sample index step: rank g of G renders spp_begin=g, spp_stride=G. 0 means 1 */
+    uint32_t max_depth;   /* closest-hit queries per path at most (Kernel.cu:39) */
+    uint64_t seed;        /* Philox key */
+    int32_t variant;      /* CRT_VARIANT_* */
+    int32_t jitter;       /* CRT_JITTER_* */
+    uint32_t flags;       /* CRT_FLAG_* */
+    uint32_t reserved_;
+} crt_render_params;
+
+typedef struct crt_counters {
+    uint64_t paths;        /* camera paths started */
+    uint64_t rays;         /* closest-hit queries issued (primary + scattered, incl. the escaping one) */
+    uint64_t box_tests;    /* only with CRT_FLAG_COUNT_TESTS */
+    uint64_t prim_tests;   /* only with CRT_FLAG_COUNT_TESTS */
+    uint64_t kernel_launches; /* launches of this library's kernels since the last reset */
+} crt_counters;
+
+typedef struct crt_bvh_stats {
+    uint64_t n_prims, n_nodes, max_depth, smem_nodes;
+    double sah_cost;
+    double build_ms;
+    uint64_t node_bytes, prim_bytes;
+} crt_bvh_stats;
+
+typedef struct crt_context crt_context;
+
+/* ---- context ---- */
+crt_status crt_context_create(int device, crt_context** out);
+void       crt_context_destroy(crt_context* ctx);
+const char* crt_last_error_string(const crt_context* ctx); /* ctx may be NULL: process-wide last error */
+int        crt_abi_version(void);
+/* Run on an existing CUDA stream (cudaStream_t passed as void*); NULL = the context's own stream. */
+crt_status crt_set_stream(crt_context* ctx, void* cuda_stream);
+crt_status crt_synchronize(crt_context* ctx);
+
+/* ---- scene (replaces CudaLayer::GenerateWorld + BVHNode ctor, CudaLayer.cpp:103-256, Hittable.cuh:303-385) ---- */
+crt_status crt_scene_upload(crt_context* ctx, const crt_scene_desc* scene);
+/* Walk the reference's own pointer graph: `world` is the Hittable of type BVHNODE that
+ * LaunchKernel receives (Kernel.cu:178-181). Host-readable (managed or host) memory. */
+crt_status crt_scene_from_reference(crt_context* ctx, const void* world);
+crt_status crt_bvh_get_stats(const crt_context* ctx, crt_bvh_stats* out);
+
+/* ---- camera ---- */
+crt_status crt_set_camera(crt_context* ctx, const crt_input_struct* inputs);
+/* Thin-lens extension (not in the reference; north_star asks for defocus). aperture = lens DIAMETER;
+ * aperture 0 restores the reference camera bit for bit. */
+crt_status crt_set_lens(crt_context* ctx, float aperture, float focus_dist);
+
+/* ---- framebuffer: progressive FP32 accumulation (sum of radiance, RGBA float4 per pixel, .w = sample count) ---- */
+crt_status crt_framebuffer_resize(crt_context* ctx, uint32_t width, uint32_t height); /* also clears */
+crt_status crt_accum_clear(crt_context* ctx);
+/* Use a caller-owned DEVICE buffer of width*height float4 (e.g. a torch tensor that is then NCCL-reduced). NULL = internal. */
+crt_status crt_set_accum_device_buffer(crt_context* ctx, void* device_float4);
+void*      crt_accum_device_ptr(crt_context* ctx);
+
+/* ---- render (replaces LaunchKernel, Kernel.cu:102-158,178-191). Asynchronous on the context stream. ---- */
+crt_status crt_render(crt_context* ctx, const crt_render_params* params);
+/* mean -> 255*sqrt -> clamp -> pack A<<24|B<<16|G<<8|R (Kernel.cu:12-19,151-157). out is HOST memory. Synchronises. */
+crt_status crt_resolve(crt_context* ctx, uint32_t* out_rgba8);
+crt_status crt_resolve_device(crt_context* ctx, void* device_out_rgba8); /* async */
+crt_status crt_read_accum(crt_context* ctx, float* out_float4);          /* width*height*4 floats, synchronises */
+/* Closest-hit hittable index (index into the uploaded list, -1 = miss) of one primary ray per pixel.
+ * Always exact math; jitter = CRT_JITTER_*. out is HOST memory, width*height int32. */
+crt_status crt_primary_ids(crt_context* ctx, int32_t jitter, uint64_t seed, int32_t* out_ids);
+crt_status crt_get_counters(crt_context* ctx, crt_counters* out);   /* synchronises */
+crt_status crt_reset_counters(crt_context* ctx);
+/* GPU milliseconds between the CUDA events that bracketed the last crt_render call (synchronises). */
+crt_status crt_last_render_ms(crt_context* ctx, float* out_ms);
+
+/* ---- synthetic scenes of BASELINE.json, splitmix64-seeded; host-only, no GPU needed ---- */
+enum { CRT_SCENE_RTIOW = 1, CRT_SCENE_TEXTURED = 2, CRT_SCENE_GRID_1M = 3, CRT_SCENE_STRESS_10K = 4,
+       CRT_SCENE_REFERENCE_DEFAULT = 5 /* CudaLayer.cpp:103-256: XZRect checker ground + 16 spheres */ };
+typedef struct crt_scene_builder crt_scene_builder;
+crt_status crt_scene_generate(int32_t kind, uint64_t seed, uint64_t size_hint, crt_scene_builder** out);
+const crt_scene_desc* crt_scene_builder_desc(const crt_scene_builder* b);
+/* Default camera of the generated scene for an image of the given aspect. */
+crt_status crt_scene_builder_camera(const crt_scene_builder* b, uint32_t width, uint32_t height, crt_input_struct* out);
+void       crt_scene_builder_free(crt_scene_builder* b);
+/* Reference host-side camera mapping (CudaLayer.cpp:45-62): position/orientation/up/fov(deg) -> InputStruct. */
+crt_status crt_camera_look(const float position[3], const float orientation[3], const float world_up[3],
+                           float fov_degrees, float near_plane, float far_plane,
+                           const float background_start[3], const float background_end[3], crt_input_struct* out);
+
+/* ---- headless framebuffer writer (replaces the GL blit, CudaLayer.cpp:379-386) ---- */
+crt_status crt_write_ppm(const char* path, const uint32_t* rgba8, uint32_t width, uint32_t height, int flip_rows);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CRT_H */
