@@ -69,7 +69,8 @@ class Counters(C.Structure):
 
 class BvhStats(C.Structure):
     _fields_ = [("n_prims", C.c_uint64), ("n_nodes", C.c_uint64), ("max_depth", C.c_uint64), ("smem_nodes", C.c_uint64),
-                ("sah_cost", C.c_double), ("build_ms", C.c_double), ("node_bytes", C.c_uint64), ("prim_bytes", C.c_uint64)]
+                ("sah_cost", C.c_double), ("build_ms", C.c_double), ("node_bytes", C.c_uint64), ("prim_bytes", C.c_uint64),
+                ("h2d_bytes", C.c_uint64)]
 
 
 assert C.sizeof(Hittable) == 32 and C.sizeof(Material) == 16 and C.sizeof(Texture) == 48 and C.sizeof(InputStruct) == 72

@@ -240,6 +240,7 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
     S.n_nodes = (int)nn; S.n_prims = (int)np;
     S.smem_nodes = S.smem_prims = S.smem_mats = 0;
     ctx->stats = P.stats;
+    ctx->stats.h2d_bytes = h2d;
     ctx->scene_h2d_bytes = h2d;
     ctx->have_scene = true;
     return CRT_OK;

@@ -127,6 +127,7 @@ typedef struct crt_bvh_stats {
     double sah_cost;
     double build_ms;
     uint64_t node_bytes, prim_bytes;
+    uint64_t h2d_bytes; /* bytes copied host -> device by the last scene upload (nodes, primitives, materials, texels) */
 } crt_bvh_stats;
 
 typedef struct crt_context crt_context;

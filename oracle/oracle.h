@@ -28,6 +28,9 @@ int oracle_render(const crt_scene_desc* scene, const crt_input_struct* cam, uint
                   uint32_t max_depth, int jitter_center, int n_threads, int accel, uint32_t* out_rgba8, float* out_mean,
                   int32_t* out_ids, uint64_t* out_rays);
 
+/* Seed base of RenderInit (Kernel.cu:175 uses 1984). Only for noise-floor measurements between two oracle runs. */
+void oracle_set_seed_base(uint64_t seed);
+
 /* Kernel.cu:151-157 + 12-19 applied to an accumulation buffer (float4 per pixel: rgb sum, sample count). */
 void oracle_resolve(const float* accum_float4, uint32_t n_pixels, uint32_t* out_rgba8);
 

@@ -58,171 +58,9 @@ std::shared_ptr<spdlog::logger> Log::s_Logger;
 
 namespace {
 
-struct RefScene
-{
-    char* slab = nullptr;
-    Hittable** list = nullptr;
-    size_t n = 0;
-    char* world_mem = nullptr;
-    Hittable* world = nullptr;
-    std::unordered_map<const Material*, int> mat_to_index;
-    std::vector<unsigned char*> image_copies;
-    std::vector<Image*> images; // one Image object per (texture use); kept alive in slab
-};
-
-// Record = [Hittable][Hittable::ObjectUnion][largest prim][Material][Material::ObjectUnion][largest mat]
-//          [Texture][Texture::ObjectUnion][largest tex payload: Checker + 2 Constant, or Image]
-size_t RecordSize()
-{
-    size_t prim = std::max(std::max(sizeof(Sphere), sizeof(XYRect)), std::max(sizeof(XZRect), sizeof(YZRect)));
-    size_t mat = std::max(std::max(sizeof(Lambertian), sizeof(Metal)), std::max(sizeof(Dielectric), sizeof(DiffuseLight)));
-    size_t tex = std::max(sizeof(Checker) + 2 * sizeof(Constant), sizeof(Image));
-    size_t s = sizeof(Hittable) + sizeof(Hittable::ObjectUnion) + prim + sizeof(Material) + sizeof(Material::ObjectUnion) +
-               mat + sizeof(Texture) + sizeof(Texture::ObjectUnion) + tex;
-    return (s + 15) & ~size_t(15);
-}
-
-Vec3 V(const float* c)
-{
-    return Vec3(c[0], c[1], c[2]);
-}
-
-bool BuildScene(const crt_scene_desc* sd, RefScene& rs)
-{
-    rs.n = sd->n_hittables;
-    const size_t rec = RecordSize();
-    size_t prim_sz = std::max(std::max(sizeof(Sphere), sizeof(XYRect)), std::max(sizeof(XZRect), sizeof(YZRect)));
-    size_t mat_sz = std::max(std::max(sizeof(Lambertian), sizeof(Metal)), std::max(sizeof(Dielectric), sizeof(DiffuseLight)));
-    size_t list_bytes = (rs.n * sizeof(Hittable*) + 15) & ~size_t(15);
-    rs.slab = (char*)calloc(1, list_bytes + rs.n * rec);
-    if (!rs.slab)
-        return false;
-    rs.list = (Hittable**)rs.slab;
-
-    for (size_t i = 0; i < rs.n; i++) {
-        const crt_hittable& h = sd->hittables[i];
-        if (h.material < 0 || (uint64_t)h.material >= sd->n_materials)
-            return false;
-        const crt_material& m = sd->materials[h.material];
-        char* p = rs.slab + list_bytes + i * rec;
-        Hittable* hit = (Hittable*)p;
-        p += sizeof(Hittable);
-        hit->Object = (Hittable::ObjectUnion*)p;
-        p += sizeof(Hittable::ObjectUnion);
-        void* prim = p;
-        p += prim_sz;
-        Material* mat = (Material*)p;
-        p += sizeof(Material);
-        mat->Object = (Material::ObjectUnion*)p;
-        p += sizeof(Material::ObjectUnion);
-        void* matobj = p;
-        p += mat_sz;
-        Texture* tex = (Texture*)p;
-        p += sizeof(Texture);
-        tex->Object = (Texture::ObjectUnion*)p;
-        p += sizeof(Texture::ObjectUnion);
-        void* texobj = p;
-
-        // texture
-        if (m.type != CRT_DIELECTRIC) {
-            if (m.texture < 0 || (uint64_t)m.texture >= sd->n_textures)
-                return false;
-            const crt_texture& t = sd->textures[m.texture];
-            switch (t.type) {
-            case CRT_CONSTANT:
-                tex->Object->constant = new (texobj) Constant(V(t.color));
-                tex->type = TextureType::CONSTANT;
-                break;
-            case CRT_CHECKER: {
-                Checker* ck = (Checker*)texobj;
-                Constant* odd = new ((char*)texobj + sizeof(Checker)) Constant(V(t.odd));
-                Constant* even = new ((char*)texobj + sizeof(Checker) + sizeof(Constant)) Constant(V(t.even));
-                tex->Object->checker = new (ck) Checker(odd, even);
-                tex->type = TextureType::CHECKER;
-                break;
-            }
-            case CRT_IMAGE: {
-                unsigned char* data = nullptr;
-                int w = 0, hh = 0;
-                if (t.image >= 0 && (uint64_t)t.image < sd->n_images) {
-                    const crt_image& im = sd->images[t.image];
-                    data = const_cast<unsigned char*>(im.pixels); // read-only use (Texture.cuh:83-105)
-                    w = im.width;
-                    hh = im.height;
-                }
-                tex->Object->image = new (texobj) Image(data, "", w, hh);
-                tex->type = TextureType::IMAGE;
-                break;
-            }
-            default:
-                return false;
-            }
-        }
-        // material
-        switch (m.type) {
-        case CRT_LAMBERTIAN:
-            mat->Object->lambertian = new (matobj) Lambertian(tex);
-            mat->type = MaterialType::LAMBERTIAN;
-            break;
-        case CRT_METAL:
-            mat->Object->metal = new (matobj) Metal(tex, m.param);
-            mat->type = MaterialType::METAL;
-            break;
-        case CRT_DIELECTRIC:
-            mat->Object->dielectric = new (matobj) Dielectric(m.param);
-            mat->type = MaterialType::DIELECTRIC;
-            break;
-        case CRT_DIFFUSELIGHT:
-            mat->Object->diffuse_light = new (matobj) DiffuseLight(tex, m.light_intensity);
-            mat->type = MaterialType::DIFFUSELIGHT;
-            break;
-        default:
-            return false;
-        }
-        // primitive
-        Vec3 c(h.cx, h.cy, h.cz);
-        switch (h.type) {
-        case CRT_SPHERE:
-            hit->Object->sphere = new (prim) Sphere(c, h.a, mat);
-            hit->type = HittableType::SPHERE;
-            break;
-        case CRT_XYRECT:
-            hit->Object->xy_rect = new (prim) XYRect(c, h.a, h.b, mat);
-            hit->type = HittableType::XYRECT;
-            break;
-        case CRT_XZRECT:
-            hit->Object->xz_rect = new (prim) XZRect(c, h.a, h.b, mat);
-            hit->type = HittableType::XZRECT;
-            break;
-        case CRT_YZRECT:
-            hit->Object->yz_rect = new (prim) YZRect(c, h.a, h.b, mat);
-            hit->type = HittableType::YZRECT;
-            break;
-        default:
-            return false;
-        }
-        hit->isActive = h.active != 0;
-        rs.list[i] = hit;
-        rs.mat_to_index[mat] = (int)i;
-    }
-
-    // World root, as CudaLayer.cpp:247-256
-    rs.world_mem = (char*)calloc(1, sizeof(Hittable) + sizeof(Hittable::ObjectUnion) + sizeof(BVHNode));
-    rs.world = (Hittable*)rs.world_mem;
-    rs.world->Object = (Hittable::ObjectUnion*)(rs.world + 1);
-    rs.world->Object->bvh_node = (BVHNode*)(rs.world->Object + 1);
-    rs.world->type = HittableType::BVHNODE;
-    rs.world->Object->bvh_node = new (rs.world->Object->bvh_node) BVHNode(rs.list, 0, rs.n);
-    return true;
-}
-
-void FreeScene(RefScene& rs)
-{
-    if (rs.world)
-        rs.world->Object->bvh_node->Destroy();
-    free(rs.world_mem);
-    free(rs.slab);
-}
+#define REF_ALLOC(n) calloc(1, (n))
+#define REF_FREE(p) free(p)
+#include "ref_scene.inc"
 
 InputStruct ToInputs(const crt_input_struct* c)
 {
@@ -418,6 +256,33 @@ int refhost_render(const crt_scene_desc* scene, const crt_input_struct* cam, uin
         *out_rays = J.rays.load();
     FreeScene(rs);
     return 0;
+}
+
+// Reference scene graph in HOST memory for driving the drop-in LaunchKernel of libcrt.so from tests
+// (the graph is what CudaLayer hands over; cudaMallocManaged memory is host-readable in the same way).
+void* refhost_world_create(const crt_scene_desc* scene)
+{
+    RefScene* rs = new RefScene();
+    if (!BuildScene(scene, *rs)) {
+        FreeScene(*rs);
+        delete rs;
+        return nullptr;
+    }
+    return rs;
+}
+void* refhost_world_root(void* handle)
+{
+    return handle ? (void*)((RefScene*)handle)->world : nullptr;
+}
+void* refhost_world_list(void* handle)
+{
+    return handle ? (void*)((RefScene*)handle)->list : nullptr;
+}
+void refhost_world_destroy(void* handle)
+{
+    if (!handle) return;
+    FreeScene(*(RefScene*)handle);
+    delete (RefScene*)handle;
 }
 
 // XORWOW known-answer hook: n uniforms from curand_init(seed, 0, 0).

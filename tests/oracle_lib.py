@@ -94,3 +94,61 @@ def oracle_resolve(accum: np.ndarray) -> np.ndarray:
     out = np.empty(accum.shape[:-1], dtype=np.uint32)
     oracle().oracle_resolve(accum.ctypes.data_as(C.c_void_p), n, out.ctypes.data_as(C.c_void_p))
     return out
+
+
+# ---- the reference's own CUDA kernel (oracle/_ref/libcrt_refkernel.so; GPU box only) ----
+_refkernel = None
+
+
+def have_refkernel() -> bool:
+    return os.path.exists(REFKERNEL_SO)
+
+
+def refkernel():
+    global _refkernel
+    if _refkernel is None:
+        lib = C.CDLL(REFKERNEL_SO)
+        lib.refkernel_render.restype = C.c_int
+        lib.refkernel_render.argtypes = [C.POINTER(capi.SceneDesc), C.POINTER(capi.InputStruct), C.c_uint32, C.c_uint32, C.c_uint32,
+                                         C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
+        lib.refkernel_primary_ids.restype = C.c_int
+        lib.refkernel_primary_ids.argtypes = [C.POINTER(capi.SceneDesc), C.POINTER(capi.InputStruct), C.c_uint32, C.c_uint32, C.c_void_p]
+        _refkernel = lib
+    return _refkernel
+
+
+def refkernel_render(scene, cam, width, height, spp, max_depth, reps=1):
+    """Reference CUDA kernel, unmodified (Kernel.cu via LaunchKernel). Returns (rgba8 HxW uint32, [ms per rep])."""
+    rgba = np.zeros((height, width), dtype=np.uint32)
+    ms = np.zeros(max(reps, 1), dtype=np.float32)
+    rc = refkernel().refkernel_render(C.byref(scene.desc), C.byref(cam), width, height, spp, max_depth, reps,
+                                      rgba.ctypes.data_as(C.c_void_p), ms.ctypes.data_as(C.c_void_p))
+    if rc != 0:
+        raise RuntimeError(f"refkernel_render failed with {rc}")
+    return rgba, [float(x) for x in ms[:reps]]
+
+
+def refkernel_primary_ids(scene, cam, width, height):
+    ids = np.full((height, width), -9, dtype=np.int32)
+    rc = refkernel().refkernel_primary_ids(C.byref(scene.desc), C.byref(cam), width, height, ids.ctypes.data_as(C.c_void_p))
+    if rc != 0:
+        raise RuntimeError(f"refkernel_primary_ids failed with {rc}")
+    return ids
+
+
+def refhost_world(scene):
+    """Reference scene graph in host memory -> (handle, root Hittable*) for driving the drop-in LaunchKernel."""
+    lib = refhost()
+    lib.refhost_world_create.restype = C.c_void_p
+    lib.refhost_world_create.argtypes = [C.POINTER(capi.SceneDesc)]
+    lib.refhost_world_root.restype = C.c_void_p
+    lib.refhost_world_root.argtypes = [C.c_void_p]
+    lib.refhost_world_destroy.argtypes = [C.c_void_p]
+    h = lib.refhost_world_create(C.byref(scene.desc))
+    if not h:
+        raise RuntimeError("refhost_world_create failed")
+    return h, lib.refhost_world_root(h)
+
+
+def refhost_world_destroy(handle):
+    refhost().refhost_world_destroy(handle)

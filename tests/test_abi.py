@@ -1,0 +1,67 @@
+"""The C-ABI library loads without a GPU and exports every symbol include/*.h declares."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from cudaraytracer_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared(header):
+    src = open(os.path.join(ROOT, "include", header)).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    names = re.findall(r"^\s*(?:const\s+)?[A-Za-z_][A-Za-z0-9_]*\s*\*?\s+\*?\s*([A-Za-z_][A-Za-z0-9_]*)\s*\(", src, flags=re.M)
+    return sorted(set(n for n in names if n.startswith("crt_") or n.startswith("Launch")))
+
+
+def test_headers_declare_something():
+    assert len(_declared("crt.h")) >= 28
+    assert set(_declared("crt_legacy.h")) >= {"LaunchKernel", "LaunchRandInit", "LaunchRenderInit"}
+
+
+@pytest.mark.parametrize("header", ["crt.h", "crt_legacy.h"])
+def test_every_declared_symbol_is_exported(header):
+    lib = C.CDLL(capi.LIB_PATH)
+    missing = [n for n in _declared(header) if not hasattr(lib, n)]
+    assert not missing, missing
+
+
+def test_binding_table_covers_the_header():
+    declared = set(_declared("crt.h"))
+    assert declared <= set(capi.SIGNATURES), declared - set(capi.SIGNATURES)
+    lib = capi.load()
+    assert lib.crt_abi_version() == 1
+
+
+def test_struct_layouts():
+    assert C.sizeof(capi.Hittable) == 32 and C.sizeof(capi.Material) == 16 and C.sizeof(capi.Texture) == 48
+    assert C.sizeof(capi.InputStruct) == 72 and C.sizeof(capi.RenderParams) == 40 and C.sizeof(capi.Counters) == 40
+
+
+def test_scene_generators_run_on_host():
+    from cudaraytracer_b200 import Scene
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    assert 470 <= s.n_hittables <= 490
+    h = s.hittable_array()
+    assert h["type"].max() == capi.SPHERE and h["a"][0] == 1000.0
+    s2 = Scene.generate(capi.SCENE_RTIOW, 1984)
+    assert (s2.hittable_array() == h).all()  # deterministic
+    d = Scene.generate(capi.SCENE_REFERENCE_DEFAULT, 1984)
+    assert d.n_hittables == 17 and d.hittable_array()["type"][0] == capi.XZRECT
+    g = Scene.generate(capi.SCENE_GRID_1M, 1984, 30)
+    assert g.n_hittables == 901
+
+
+def test_no_gpu_fails_loudly():
+    """Without a CUDA device context creation must fail with an error, never fall back."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    lib = capi.load()
+    ctx = C.c_void_p()
+    st = lib.crt_context_create(0, C.byref(ctx))
+    assert st != capi.CRT_OK and not ctx.value
+    assert b"no CUDA device" in lib.crt_last_error_string(None)

@@ -1,0 +1,258 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star / SURVEY.md §8d):
+  * primary-hit hittable IDs with xi = 0.5 jitter: BIT-EXACT against the oracle;
+  * RGBA8 resolve of an identical FP32 buffer: BIT-EXACT (Kernel.cu:12-19,151-157);
+  * images at equal spp: statistical. The RNG streams differ by design (Philox vs XORWOW), so the test
+    measures the oracle-vs-oracle noise floor with two seed bases and requires
+    RMSE(new, oracle) <= 1.25 x RMSE(oracle, oracle'), plus an unbiasedness check on block means.
+"""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from cudaraytracer_b200 import Renderer, Scene, capi, look_camera
+
+pytestmark = pytest.mark.gpu
+
+SCENES = [("rtiow", capi.SCENE_RTIOW, 0, 400, 225),          # C1 of BASELINE.json
+          ("refdefault", capi.SCENE_REFERENCE_DEFAULT, 0, 200, 150),
+          ("textured", capi.SCENE_TEXTURED, 512, 240, 135),
+          ("stress", capi.SCENE_STRESS_10K, 40, 160, 90),
+          ("grid", capi.SCENE_GRID_1M, 60, 160, 90)]
+
+
+@pytest.fixture(scope="module")
+def renderer():
+    r = Renderer(0)
+    yield r
+    r.close()
+
+
+def _setup(r, scene, cam, W, H):
+    r.upload(scene)
+    r.set_camera(cam)
+    r.resize(W, H)
+
+
+@pytest.mark.parametrize("name,kind,hint,W,H", SCENES)
+def test_primary_ids_bit_exact(renderer, name, kind, hint, W, H):
+    s = Scene.generate(kind, 1984, hint)
+    cam = s.default_camera(W, H)
+    _setup(renderer, s, cam, W, H)
+    ids = renderer.primary_ids(capi.JITTER_CENTER)
+    accel = O.BVH_REFERENCE if s.n_hittables < 2000 else O.BRUTE_FORCE
+    ref = O.oracle_render(s, cam, W, H, 0, 50, want_ids=True, want_rgba=False, want_mean=False, accel=accel)["ids"]
+    assert ids.shape == ref.shape
+    assert np.array_equal(ids, ref), f"{(ids != ref).sum()} of {ids.size} primary-hit IDs differ"
+    assert (ids >= 0).any()
+
+
+def test_primary_ids_odd_sizes_and_cameras(renderer):
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    for (W, H, pos, fov) in [(37, 23, (13, 2, 3), 35.0), (130, 61, (0, 6, 14), 60.0), (64, 64, (-8, 1.0, -5), 20.0), (17, 90, (2, 0.5, 9), 90.0)]:
+        o = -np.array(pos, dtype=np.float64)
+        o /= np.linalg.norm(o)
+        cam = look_camera(pos, tuple(float(x) for x in o), fov_deg=fov)
+        _setup(renderer, s, cam, W, H)
+        ids = renderer.primary_ids(capi.JITTER_CENTER)
+        ref = O.oracle_render(s, cam, W, H, 0, 50, want_ids=True, want_rgba=False, want_mean=False)["ids"]
+        assert np.array_equal(ids, ref), (W, H, pos, (ids != ref).sum())
+
+
+def test_resolve_bit_exact(renderer):
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    W, H = 200, 113
+    cam = s.default_camera(W, H)
+    _setup(renderer, s, cam, W, H)
+    renderer.render(spp=7, max_depth=50)
+    acc = renderer.read_accum()
+    img = renderer.resolve()
+    assert np.array_equal(img, O.oracle_resolve(acc))
+    assert (acc[..., 3] == 7).all()
+    assert (img >> 24 == 255).all()
+
+
+def _rmse(a, b):
+    return float(np.sqrt(np.mean((a.astype(np.float64) - b.astype(np.float64)) ** 2)))
+
+
+def _block_mean(a, bs):
+    H, W = a.shape[:2]
+    Hc, Wc = H // bs * bs, W // bs * bs
+    return a[:Hc, :Wc].reshape(Hc // bs, bs, Wc // bs, bs, -1).mean(axis=(1, 3))
+
+
+@pytest.mark.parametrize("name,kind,hint,W,H", SCENES[:4])
+def test_image_matches_oracle_statistically(renderer, name, kind, hint, W, H):
+    W, H = W // 2, H // 2
+    spp, depth = 64, 50
+    s = Scene.generate(kind, 1984, hint)
+    cam = s.default_camera(W, H)
+    _setup(renderer, s, cam, W, H)
+    renderer.render(spp=spp, max_depth=depth)
+    acc = renderer.read_accum()
+    new = np.clip(acc[..., :3] / acc[..., 3:4], 0, 4)
+    O.oracle().oracle_set_seed_base(1984)
+    a = np.clip(O.oracle_render(s, cam, W, H, spp, depth)["mean"], 0, 4)
+    O.oracle().oracle_set_seed_base(777001)
+    b = np.clip(O.oracle_render(s, cam, W, H, spp, depth)["mean"], 0, 4)
+    O.oracle().oracle_set_seed_base(1984)
+    floor = _rmse(a, b)
+    got = max(_rmse(new, a), _rmse(new, b))
+    # tolerance stated by SURVEY.md §8d: RMSE(new, oracle) <= 1.25 x the oracle-vs-oracle noise floor at equal spp
+    assert got <= 1.25 * floor, f"RMSE new-vs-oracle {got:.5f} vs noise floor {floor:.5f}"
+    # unbiasedness: 8x8 block means (noise / 8) must agree within 5 sigma of the block-level noise floor + 0.5 %
+    bs = 8
+    nb, ab, bb = _block_mean(new, bs), _block_mean(a, bs), _block_mean(b, bs)
+    ref_b = 0.5 * (ab + bb)
+    sigma = max(_rmse(ab, bb), 1e-6)
+    bias = float(np.abs((nb - ref_b).mean(axis=(0, 1))).max())
+    assert bias <= 5 * sigma / np.sqrt(nb.shape[0] * nb.shape[1]) + 0.005 * float(ref_b.mean()), (bias, sigma)
+    # PSNR of the 8-bit output against the oracle's, reported via assertion message on failure
+    img = renderer.resolve()
+    ref8 = O.oracle_resolve(np.concatenate([a, np.ones_like(a[..., :1])], axis=-1))
+    from cudaraytracer_b200 import unpack_rgba8
+    mse = np.mean((unpack_rgba8(img).astype(np.float64) - unpack_rgba8(ref8).astype(np.float64)) ** 2)
+    mse_floor = np.mean((unpack_rgba8(O.oracle_resolve(np.concatenate([b, np.ones_like(b[..., :1])], axis=-1))).astype(np.float64) -
+                         unpack_rgba8(ref8).astype(np.float64)) ** 2)
+    psnr = 10 * np.log10(255.0 ** 2 / max(mse, 1e-12))
+    psnr_floor = 10 * np.log10(255.0 ** 2 / max(mse_floor, 1e-12))
+    assert psnr >= psnr_floor - 1.0, (psnr, psnr_floor)
+
+
+def test_exact_math_render_agrees_with_fast(renderer):
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    W, H = 96, 54
+    cam = s.default_camera(W, H)
+    _setup(renderer, s, cam, W, H)
+    renderer.render(spp=32, max_depth=50)
+    fast = renderer.read_accum()
+    renderer.clear()
+    renderer.render(spp=32, max_depth=50, flags=capi.FLAG_EXACT_MATH)
+    exact = renderer.read_accum()
+    # same Philox streams, different rounding: almost every pixel follows the same paths
+    close = np.isclose(fast[..., :3], exact[..., :3], rtol=1e-3, atol=1e-3).all(axis=-1).mean()
+    assert close > 0.9, close
+    assert abs(fast[..., :3].mean() - exact[..., :3].mean()) / exact[..., :3].mean() < 0.01
+
+
+def test_determinism_and_progressive_split(renderer):
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    W, H = 120, 67
+    cam = s.default_camera(W, H)
+    _setup(renderer, s, cam, W, H)
+    renderer.render(spp=12, max_depth=50)
+    one = renderer.read_accum()
+    renderer.clear()
+    renderer.render(spp=12, max_depth=50)
+    assert np.array_equal(one.view(np.uint32), renderer.read_accum().view(np.uint32))
+    # progressive: 5 + 7 samples added in order == 12 at once, bit for bit (sequential per-pixel accumulation)
+    renderer.clear()
+    renderer.render(spp=5, max_depth=50, spp_begin=0)
+    renderer.render(spp=7, max_depth=50, spp_begin=5)
+    assert np.array_equal(one.view(np.uint32), renderer.read_accum().view(np.uint32))
+    # another seed gives another image
+    renderer.clear()
+    renderer.render(spp=12, max_depth=50, seed=5)
+    assert not np.array_equal(one, renderer.read_accum())
+
+
+def test_spp_sharding_reproduces_the_same_samples(renderer):
+    """Rank g of G renders samples g, g+G, ...: the union over ranks is the single-GPU sample set."""
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    W, H = 96, 54
+    cam = s.default_camera(W, H)
+    _setup(renderer, s, cam, W, H)
+    renderer.render(spp=16, max_depth=50)
+    full = renderer.read_accum().astype(np.float64)
+    total = np.zeros_like(full)
+    G = 4
+    for g in range(G):
+        renderer.clear()
+        renderer.render(spp=16 // G, max_depth=50, spp_begin=g, spp_stride=G)
+        total += renderer.read_accum()
+    assert (total[..., 3] == 16).all()
+    assert np.allclose(total[..., :3], full[..., :3], rtol=1e-5, atol=1e-5)
+
+
+def test_counters(renderer):
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    W, H = 64, 36
+    cam = s.default_camera(W, H)
+    _setup(renderer, s, cam, W, H)
+    renderer.reset_counters()
+    renderer.render(spp=4, max_depth=50, flags=capi.FLAG_COUNT_TESTS)
+    c = renderer.counters()
+    assert c.paths == W * H * 4
+    assert c.paths <= c.rays <= c.paths * 50
+    assert c.box_tests > c.rays and c.prim_tests > 0
+    assert c.kernel_launches >= 1
+    # mean path length close to the oracle's on the same scene (same transport)
+    ref = O.oracle_render(s, cam, W, H, 4, 50)
+    assert abs(c.rays / c.paths - ref["rays"] / (W * H * 4)) < 0.25
+
+
+def test_max_depth_one_and_truncated_grid(renderer):
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    W, H = 50, 40
+    cam = s.default_camera(W, H)
+    _setup(renderer, s, cam, W, H)
+    renderer.reset_counters()
+    renderer.render(spp=2, max_depth=1)
+    c = renderer.counters()
+    assert c.rays == c.paths == W * H * 2
+    acc = renderer.read_accum()
+    ids = renderer.primary_ids()
+    # depth 1: a path that hits anything is black (Kernel.cu:79); interior hit pixels are black, missed ones carry the sky
+    pad = np.pad(ids, 1, mode="edge")
+    interior = np.ones_like(ids, dtype=bool)
+    for dy in (0, 1, 2):
+        for dx in (0, 1, 2):
+            interior &= (pad[dy:dy + H, dx:dx + W] >= 0)
+    assert interior.any() and (acc[..., :3][interior] == 0).all()
+    assert (acc[..., :3][ids < 0].sum(axis=-1) > 0).mean() > 0.9
+    renderer.clear()
+    renderer.render(spp=1, max_depth=5, flags=capi.FLAG_TRUNCATED_GRID)  # Kernel.cu:183-184: 48 x 32 covered
+    acc = renderer.read_accum()
+    assert (acc[:32, :48, 3] == 1).all() and (acc[32:, :, 3] == 0).all() and (acc[:, 48:, 3] == 0).all()
+
+
+def test_edge_case_scenes(renderer):
+    W, H = 40, 30
+    cam = look_camera((0, 0, 5), (0, 0, -1))
+    empty = Scene.from_arrays([], [], [])
+    _setup(renderer, empty, cam, W, H)
+    assert (renderer.primary_ids() == -1).all()
+    renderer.render(spp=2, max_depth=5)
+    acc = renderer.read_accum()
+    ref = O.oracle_render(empty, cam, W, H, 2, 5)
+    assert np.allclose(acc[..., :3] / 2, ref["mean"], atol=2e-3)  # only the sub-pixel jitter differs
+    tex = [dict(type=capi.CONSTANT, color=(0.5, 0.5, 0.5))]
+    mat = [dict(type=capi.LAMBERTIAN, texture=0), dict(type=capi.DIELECTRIC, param=1.5)]
+    hs = [dict(type=capi.SPHERE, cx=0, cy=0, cz=0, a=1.0, material=0, active=1),
+          dict(type=capi.SPHERE, cx=0.5, cy=0, cz=2, a=0.5, material=1, active=0),   # inactive: must be ignored
+          dict(type=capi.SPHERE, cx=-1.5, cy=0, cz=1, a=-0.4, material=1, active=1)]  # negative radius (hollow glass trick)
+    for n in (1, 2, 3):
+        sc = Scene.from_arrays(hs[:n], mat, tex)
+        _setup(renderer, sc, cam, W, H)
+        ids = renderer.primary_ids()
+        ref = O.oracle_render(sc, cam, W, H, 0, 5, want_ids=True, want_rgba=False, want_mean=False)["ids"]
+        assert np.array_equal(ids, ref), n
+        assert 1 not in ids
+
+
+def test_error_behaviour():
+    r = Renderer(0)
+    from cudaraytracer_b200 import CrtError
+    with pytest.raises(CrtError):
+        r.render(spp=1, max_depth=5)  # no scene
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    r.upload(s)
+    with pytest.raises(CrtError):
+        r.render(spp=1, max_depth=5)  # no camera / framebuffer
+    bad = Scene.from_arrays([dict(type=capi.SPHERE, cx=0, cy=0, cz=0, a=1.0, material=3)], [dict(type=capi.LAMBERTIAN, texture=0)],
+                            [dict(type=capi.CONSTANT, color=(1, 1, 1))])
+    with pytest.raises(CrtError):
+        r.upload(bad)
+    r.close()

@@ -1,0 +1,96 @@
+"""GPU tests against the reference's OWN CUDA kernel (Kernel.cu compiled unmodified for sm_100a with its release
+flags, oracle/_ref/libcrt_refkernel.so) and of the drop-in LaunchKernel symbol exported by libcrt.so."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from cudaraytracer_b200 import Renderer, Scene, capi, unpack_rgba8
+
+pytestmark = pytest.mark.gpu
+needs_refkernel = pytest.mark.skipif(not O.have_refkernel(), reason="oracle/_ref/libcrt_refkernel.so not built")
+needs_refhost = pytest.mark.skipif(not O.have_refhost(), reason="oracle/_ref/libcrt_refhost.so not built")
+
+SCENES = [("rtiow", capi.SCENE_RTIOW, 0, 400, 225), ("refdefault", capi.SCENE_REFERENCE_DEFAULT, 0, 208, 160),
+          ("textured", capi.SCENE_TEXTURED, 512, 240, 144), ("stress", capi.SCENE_STRESS_10K, 40, 160, 96)]
+
+
+@needs_refkernel
+@pytest.mark.parametrize("name,kind,hint,W,H", SCENES)
+def test_primary_ids_vs_reference_kernel(name, kind, hint, W, H):
+    """The reference GPU build is fast-math (CMakeLists.txt:36), our ID path is IEEE like the host oracle: IDs must be
+    identical except where fast-math rounding flips a silhouette tie; the oracle comparison (test_gpu_parity) is the
+    bit-exact bar. Here: >= 99.9 % identical and every difference sits on an ID edge of the oracle map."""
+    s = Scene.generate(kind, 1984, hint)
+    cam = s.default_camera(W, H)
+    r = Renderer(0)
+    r.upload(s); r.set_camera(cam); r.resize(W, H)
+    ours = r.primary_ids(capi.JITTER_CENTER)
+    r.close()
+    ref = O.refkernel_primary_ids(s, cam, W, H)
+    diff = ours != ref
+    assert diff.mean() <= 1e-3, f"{diff.sum()} of {diff.size} differ"
+    if diff.any():
+        pad = np.pad(ours, 1, mode="edge")
+        edge = np.zeros_like(diff)
+        for dy in (0, 1, 2):
+            for dx in (0, 1, 2):
+                edge |= pad[dy:dy + H, dx:dx + W] != ours
+        assert (edge | ~diff).all(), "an ID mismatch away from any silhouette"
+
+
+@needs_refkernel
+@pytest.mark.parametrize("name,kind,hint,W,H", SCENES[:3])
+def test_image_vs_reference_kernel(name, kind, hint, W, H):
+    """Converged 8-bit images at equal spp: PSNR(new, reference kernel) must be within 1 dB of PSNR(reference kernel run A,
+    reference kernel run B) (two frames of the reference differ by their RNG state), on the covered region."""
+    spp, depth = 64, 50
+    s = Scene.generate(kind, 1984, hint)
+    cam = s.default_camera(W, H)
+    r = Renderer(0)
+    r.upload(s); r.set_camera(cam); r.resize(W, H)
+    r.render(spp=spp, max_depth=depth)
+    ours = unpack_rgba8(r.resolve()).astype(np.float64)
+    r.close()
+    a, _ = O.refkernel_render(s, cam, W, H, spp, depth, reps=1)
+    b, _ = O.refkernel_render(s, cam, W, H, spp, depth, reps=2)  # second frame continues the RNG state: independent noise
+    Hc, Wc = H // 16 * 16, W // 16 * 16
+    assert (a[:Hc, :Wc] >> 24 == 255).all()
+    a = unpack_rgba8(a).astype(np.float64)[:Hc, :Wc]; b = unpack_rgba8(b).astype(np.float64)[:Hc, :Wc]; ours = ours[:Hc, :Wc]
+    psnr = lambda x, y: 10 * np.log10(255.0 ** 2 / max(np.mean((x - y) ** 2), 1e-12))
+    floor = psnr(a, b)
+    got = min(psnr(ours, a), psnr(ours, b))
+    assert got >= floor - 1.0, (got, floor)
+    assert abs(ours.mean() - a.mean()) < 0.01 * a.mean() + 0.5
+
+
+@needs_refhost
+def test_legacy_launchkernel_drop_in():
+    """LaunchKernel exported by libcrt.so, fed with the reference's own scene graph (host memory) and a device buffer."""
+    import torch
+    lib = capi.load()
+    W, H, spp, depth = 208, 160, 32, 12
+    s = Scene.generate(capi.SCENE_REFERENCE_DEFAULT, 1984)
+    cam = s.default_camera(W, H)
+    handle, world = O.refhost_world(s)
+    try:
+        pos = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+        lib.LaunchRandInit(None)
+        lib.LaunchKernel(C.c_void_p(pos.data_ptr()), W, H, spp, depth, C.c_void_p(world), None, cam)
+        img = pos.cpu().numpy().view(np.uint32).reshape(H, W)
+        assert (img >> 24 == 255).all()
+        ref = O.oracle_render(s, cam, W, H, spp, depth)["rgba"]
+        x, y = unpack_rgba8(img).astype(np.float64), unpack_rgba8(ref).astype(np.float64)
+        assert abs(x.mean() - y.mean()) < 0.02 * y.mean()
+        psnr = 10 * np.log10(255.0 ** 2 / np.mean((x - y) ** 2))
+        assert psnr > 20.0, psnr
+        # second frame: fresh noise (the reference's RNG state persists across frames), same scene -> no re-upload
+        lib.LaunchKernel(C.c_void_p(pos.data_ptr()), W, H, spp, depth, C.c_void_p(world), None, cam)
+        img2 = pos.cpu().numpy().view(np.uint32).reshape(H, W)
+        assert not np.array_equal(img, img2)
+        c = capi.Counters()
+        assert lib.crt_legacy_counters(C.byref(c)) == 0 and c.paths == 2 * W * H * spp
+    finally:
+        lib.crt_legacy_shutdown()
+        O.refhost_world_destroy(handle)
