@@ -170,7 +170,9 @@ def run_gpu_arm(args):
         spp = args.spp
     scene = Scene.generate(getattr(capi, kind_name), 1984, hint)
     cam = scene.default_camera(W, H)
-    stream = torch.cuda.current_stream(dev)
+    # a non-default torch stream: our kernels, torch's fills and NCCL all run on it, and torch events time it
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.set_stream(stream)
     r = Renderer(local)
     r.set_stream(stream.cuda_stream)
     r.upload(scene)
@@ -264,11 +266,10 @@ def run_gpu_arm(args):
         sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
         peak_tflops = FP32_LANES * 2 * sm_mhz * 1e6 / 1e12
         # kernel-only duration: the render launch of the last step, measured by the library's own events
+        r.reset_counters()
         accum.zero_()
         r.render(spp=spp, max_depth=depth, spp_begin=rank, spp_stride=world, variant=variant)
         k_ms = r.last_render_ms()
-        r.reset_counters()
-        accum.zero_(); r.render(spp=spp, max_depth=depth, spp_begin=rank, spp_stride=world, variant=variant); k_ms = r.last_render_ms()
         kc = r.counters()
         achieved = kc.rays * f_ray / (k_ms / 1e3) / 1e12
         b_ray = 32.0 / (kc.rays / kc.paths) / spp  # megakernel: one float4 read + write per PIXEL per launch

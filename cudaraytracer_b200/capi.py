@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcrt.so")
+LIB_PATH = os.environ.get("CRT_LIB_PATH") or os.path.join(_HERE, "libcrt.so")  # override: A/B experiments only
 
 # enums of include/crt.h
 CRT_OK = 0

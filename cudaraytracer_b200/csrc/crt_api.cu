@@ -388,7 +388,8 @@ static size_t plan_smem(const crt_context* ctx, int blocks_per_sm, DevScene& S, 
     budget = std::min<long>(budget, ctx->smem_optin);
     if (ctx->smem_budget_override >= 0) budget = std::min<long>(ctx->smem_budget_override, ctx->smem_optin);
     budget = std::max<long>(budget, 0);
-    const long full = (long)S.n_nodes * 64 + (long)S.n_prims * 48;
+    const long node_b = 64;
+    const long full = (long)S.n_nodes * node_b + (long)S.n_prims * 48;
     if (full <= budget) {
         S.smem_nodes = S.n_nodes; S.smem_prims = S.n_prims; S.smem_mats = S.n_prims;
         all = true;
@@ -396,7 +397,7 @@ static size_t plan_smem(const crt_context* ctx, int blocks_per_sm, DevScene& S, 
     }
     all = false;
     long rem = budget;
-    S.smem_nodes = (int)std::min<long>(S.n_nodes, rem / 64); rem -= (long)S.smem_nodes * 64;
+    S.smem_nodes = (int)std::min<long>(S.n_nodes, rem / node_b); rem -= (long)S.smem_nodes * node_b;
     S.smem_prims = (int)std::min<long>(S.n_prims, rem / 16); rem -= (long)S.smem_prims * 16;
     S.smem_mats = (int)std::min<long>(S.n_prims, rem / 32); rem -= (long)S.smem_mats * 32;
     return (size_t)(budget - rem);
@@ -411,6 +412,27 @@ static cudaError_t launch_mega(const RenderArgs& A, dim3 grid, size_t smem, cuda
     return cudaGetLastError();
 }
 
+template <bool EXACT, bool COUNT, bool ALL, int THRESH>
+static cudaError_t launch_mega2(const RenderArgs& A, dim3 grid, size_t smem, cudaStream_t st)
+{
+    cudaError_t e = cudaFuncSetAttribute(k_render_mega2<EXACT, COUNT, ALL, THRESH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_render_mega2<EXACT, COUNT, ALL, THRESH><<<grid, CRT_BLOCK_THREADS, smem, st>>>(A);
+    return cudaGetLastError();
+}
+
+// Experimental schedule selection for the fast (non-exact, non-counting) megakernel: CRT_MEGA_THRESH=0 keeps
+// k_render_mega; 1/8/16/24/32 pick k_render_mega2 with that refill threshold.
+static int mega_thresh_env()
+{
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("CRT_MEGA_THRESH");
+        v = e ? atoi(e) : 0;
+    }
+    return v;
+}
+
 static cudaError_t dispatch_mega(const RenderArgs& A, dim3 grid, size_t smem, cudaStream_t st, bool exact, bool count, bool all)
 {
     if (exact) {
@@ -418,6 +440,14 @@ static cudaError_t dispatch_mega(const RenderArgs& A, dim3 grid, size_t smem, cu
         return all ? launch_mega<true, false, true>(A, grid, smem, st) : launch_mega<true, false, false>(A, grid, smem, st);
     }
     if (count) return all ? launch_mega<false, true, true>(A, grid, smem, st) : launch_mega<false, true, false>(A, grid, smem, st);
+    switch (mega_thresh_env()) {
+    case 1: return all ? launch_mega2<false, false, true, 1>(A, grid, smem, st) : launch_mega2<false, false, false, 1>(A, grid, smem, st);
+    case 8: return all ? launch_mega2<false, false, true, 8>(A, grid, smem, st) : launch_mega2<false, false, false, 8>(A, grid, smem, st);
+    case 16: return all ? launch_mega2<false, false, true, 16>(A, grid, smem, st) : launch_mega2<false, false, false, 16>(A, grid, smem, st);
+    case 24: return all ? launch_mega2<false, false, true, 24>(A, grid, smem, st) : launch_mega2<false, false, false, 24>(A, grid, smem, st);
+    case 32: return all ? launch_mega2<false, false, true, 32>(A, grid, smem, st) : launch_mega2<false, false, false, 32>(A, grid, smem, st);
+    default: break;
+    }
     return all ? launch_mega<false, false, true>(A, grid, smem, st) : launch_mega<false, false, false>(A, grid, smem, st);
 }
 

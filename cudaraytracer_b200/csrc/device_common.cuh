@@ -7,6 +7,7 @@
 #define CRT_STACK_SIZE 64
 #define CRT_BLOCK_THREADS 256
 
+
 struct DevImage
 {
     const uchar4* texels; // RGB8 of the reference (Texture.cuh:76) padded to RGBA8 so one 32-bit load fetches a texel

@@ -301,18 +301,19 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
     else {
         B.nodes.emplace_back();
         B.nodes[0].box = all;
-        B.nodes[0].child[0] = n == 1 ? ~0 : 0;
-        B.nodes[0].child[1] = 0; // marked empty below
+        B.nodes[0].child[0] = ~0;
+        B.nodes[0].child[1] = ~0; // single object: left == right, like the reference (Hittable.cuh:326-328)
     }
 
     // 4. breadth-first emission; leaves get their final primitive slot in BFS discovery order so that
     //    primitives referenced by neighbouring nodes are neighbours in memory too.
     const uint32_t nn = (uint32_t)B.nodes.size();
     out->nodes.assign(nn, CrtPackedNode());
-    out->prims.assign(4 * (size_t)n, 0.f);
-    out->prim_k.assign(n, 0.f);
-    out->mats.assign(8 * (size_t)n, 0.f);
-    out->prim_id.assign(n, -1);
+    const size_t np_alloc = n ? n : 1;
+    out->prims.assign(4 * np_alloc, 0.f);
+    out->prim_k.assign(np_alloc, 0.f);
+    out->mats.assign(8 * np_alloc, 0.f);
+    out->prim_id.assign(np_alloc, -1);
     std::vector<int32_t> order;   // BFS order -> build node
     std::vector<int32_t> newidx(nn, -1);
     order.reserve(nn);
@@ -341,10 +342,19 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
         if (root_area > 0.f)
             sah += 1.0 * bn.box.half_area() / root_area;
         for (int c = 0; c < 2; c++) {
-            bool empty = (n < 2) && (c == 1 || n == 0);
-            if (empty) {
+            if (n == 0 && c == 0) {
+                // Empty scene: one dummy sphere with a NaN centre (its discriminant is NaN, so it can never be hit)
+                // behind an always-true box, so that the kernels need no special case.
                 store_box(pn.w, c, all, true, abs_pad);
-                pn.child[c] = ~0; // leaf 0 behind an empty box: never reached
+                pn.child[c] = ~(int32_t)(((uint32_t)CRT_SPHERE << CRT_LEAF_TYPE_SHIFT) | 0u);
+                out->prims[0] = out->prims[1] = out->prims[2] = std::numeric_limits<float>::quiet_NaN();
+                out->prims[3] = 0.f;
+                out->prim_id[0] = -1;
+                continue;
+            }
+            if (n < 2 && c == 1) { // second slot repeats the first (its test fails the strict t < t_max)
+                for (int i = 0; i < 6; i++) pn.w[6 + i] = pn.w[i];
+                pn.child[1] = pn.child[0];
                 continue;
             }
             int32_t ch = bn.child[c];

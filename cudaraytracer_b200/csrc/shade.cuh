@@ -79,7 +79,7 @@ __device__ __forceinline__ float3 ball_sample(float u0, float u1, float u2)
     float s = fast_sqrt(fmaxf(0.0f, 1.0f - z * z));
     float sn, cs;
     __sincosf(2.0f * CRT_PI * u1, &sn, &cs);
-    float r = cbrtf(u2);
+    float r = exp2f(__log2f(u2) * (1.0f / 3.0f)); // u2^(1/3): MUFU.LG2 + MUFU.EX2 (u2 in (0,1], so log2 is finite)
     return f3(r * s * cs, r * s * sn, r * z);
 }
 

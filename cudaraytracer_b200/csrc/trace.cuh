@@ -27,9 +27,12 @@ struct SceneView
 template <bool SMEM_ALL> __device__ __forceinline__ void load_node(const SceneView& S, int i, float4& w0, float4& w1, float4& w2, int2& ch)
 {
     if (SMEM_ALL || i < S.smem_nodes) {
-        const float4* p = S.s_nodes + 4 * i;
-        w0 = p[0]; w1 = p[1]; w2 = p[2];
-        float4 w3 = p[3];
+        // shared-memory copy is SoA by word: word k of node i sits at s_nodes[k * smem_nodes + i], so lanes at
+        // different nodes spread over all eight 16-byte bank groups (the AoS 64-byte stride used only two of them)
+        const float4* p = S.s_nodes + i;
+        const int n = S.smem_nodes;
+        w0 = p[0]; w1 = p[n]; w2 = p[2 * n];
+        float4 w3 = p[3 * n];
         ch = make_int2(__float_as_int(w3.x), __float_as_int(w3.y));
     }
     else {
@@ -69,12 +72,17 @@ __device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem
     float4* sp = sn + 4 * (size_t)D.smem_nodes;
     float4* sm = sp + D.smem_prims;
     const int tid = threadIdx.x, nt = blockDim.x;
-    for (int i = tid; i < 4 * D.smem_nodes; i += nt) sn[i] = __ldg(D.nodes + i);
+    for (int i = tid; i < 4 * D.smem_nodes; i += nt) sn[(i & 3) * D.smem_nodes + (i >> 2)] = __ldg(D.nodes + i);
     for (int i = tid; i < D.smem_prims; i += nt) sp[i] = __ldg(D.prims + i);
     for (int i = tid; i < 2 * D.smem_mats; i += nt) sm[i] = __ldg(D.mats + i);
     S.s_nodes = sn; S.s_prims = sp; S.s_mats = sm;
     return S;
 }
+
+#define CRT_TRAV_DONE ((int)0x80000000)
+#ifndef CRT_TRAV_STYLE
+#define CRT_TRAV_STYLE 0
+#endif
 
 struct Hit
 {
@@ -187,63 +195,64 @@ __device__ __forceinline__ Hit closest_hit(const SceneView& S, float3 o, float3 
 
     int stack[CRT_STACK_SIZE];
     int sp = 0;
-    int node = 0;
+    int cur = 0; // >= 0: inner node, < 0: leaf (~code), CRT_TRAV_DONE: finished
 
+#if CRT_TRAV_STYLE == 1
+    // while-while (Aila & Laine 2009): every lane stays in the node loop until it holds a leaf (or is done), then the
+    // warp tests leaves together; ncu r1 showed the interleaved form running its leaf tests with 6 of 32 lanes.
+    while (cur != CRT_TRAV_DONE) {
+        while (cur >= 0) {
+#else
     while (true) {
-        float4 w0, w1, w2;
-        int2 ch;
-        load_node<SMEM_ALL>(S, node, w0, w1, w2, ch);
-        if (COUNT) n_box += 2;
+        {
+#endif
+            float4 w0, w1, w2;
+            int2 ch;
+            load_node<SMEM_ALL>(S, cur, w0, w1, w2, ch);
+            if (COUNT) n_box += 2;
 
-        float lx0, ly0, lz0, hx0, hy0, hz0, lx1, ly1, lz1, hx1, hy1, hz1;
-        if (EXACT) {
-            lx0 = (w0.x - o.x) * id.x; ly0 = (w0.y - o.y) * id.y; lz0 = (w0.z - o.z) * id.z;
-            hx0 = (w0.w - o.x) * id.x; hy0 = (w1.x - o.y) * id.y; hz0 = (w1.y - o.z) * id.z;
-            lx1 = (w1.z - o.x) * id.x; ly1 = (w1.w - o.y) * id.y; lz1 = (w2.x - o.z) * id.z;
-            hx1 = (w2.y - o.x) * id.x; hy1 = (w2.z - o.y) * id.y; hz1 = (w2.w - o.z) * id.z;
+            float lx0, ly0, lz0, hx0, hy0, hz0, lx1, ly1, lz1, hx1, hy1, hz1;
+            if (EXACT) {
+                lx0 = (w0.x - o.x) * id.x; ly0 = (w0.y - o.y) * id.y; lz0 = (w0.z - o.z) * id.z;
+                hx0 = (w0.w - o.x) * id.x; hy0 = (w1.x - o.y) * id.y; hz0 = (w1.y - o.z) * id.z;
+                lx1 = (w1.z - o.x) * id.x; ly1 = (w1.w - o.y) * id.y; lz1 = (w2.x - o.z) * id.z;
+                hx1 = (w2.y - o.x) * id.x; hy1 = (w2.z - o.y) * id.y; hz1 = (w2.w - o.z) * id.z;
+            }
+            else {
+                lx0 = fmaf(w0.x, id.x, -ood.x); ly0 = fmaf(w0.y, id.y, -ood.y); lz0 = fmaf(w0.z, id.z, -ood.z);
+                hx0 = fmaf(w0.w, id.x, -ood.x); hy0 = fmaf(w1.x, id.y, -ood.y); hz0 = fmaf(w1.y, id.z, -ood.z);
+                lx1 = fmaf(w1.z, id.x, -ood.x); ly1 = fmaf(w1.w, id.y, -ood.y); lz1 = fmaf(w2.x, id.z, -ood.z);
+                hx1 = fmaf(w2.y, id.x, -ood.x); hy1 = fmaf(w2.z, id.y, -ood.y); hz1 = fmaf(w2.w, id.z, -ood.z);
+            }
+            const float tn0 = fmaxf(fmaxf(fminf(lx0, hx0), fminf(ly0, hy0)), fmaxf(fminf(lz0, hz0), t_min));
+            const float tf0 = fminf(fminf(fmaxf(lx0, hx0), fmaxf(ly0, hy0)), fminf(fmaxf(lz0, hz0), h.t));
+            const float tn1 = fmaxf(fmaxf(fminf(lx1, hx1), fminf(ly1, hy1)), fmaxf(fminf(lz1, hz1), t_min));
+            const float tf1 = fminf(fminf(fmaxf(lx1, hx1), fmaxf(ly1, hy1)), fminf(fmaxf(lz1, hz1), h.t));
+            // The boxes are padded on the host (scene_pack.cpp); <= keeps degenerate (flat) boxes alive.
+            const bool h0 = tn0 <= tf0;
+            const bool h1 = tn1 <= tf1;
+            if (h0 && h1) {
+                const bool swap = tn1 < tn0;
+                cur = swap ? ch.y : ch.x;
+                stack[sp++] = swap ? ch.x : ch.y;
+            }
+            else if (h0) cur = ch.x;
+            else if (h1) cur = ch.y;
+            else cur = sp ? stack[--sp] : CRT_TRAV_DONE;
         }
-        else {
-            lx0 = fmaf(w0.x, id.x, -ood.x); ly0 = fmaf(w0.y, id.y, -ood.y); lz0 = fmaf(w0.z, id.z, -ood.z);
-            hx0 = fmaf(w0.w, id.x, -ood.x); hy0 = fmaf(w1.x, id.y, -ood.y); hz0 = fmaf(w1.y, id.z, -ood.z);
-            lx1 = fmaf(w1.z, id.x, -ood.x); ly1 = fmaf(w1.w, id.y, -ood.y); lz1 = fmaf(w2.x, id.z, -ood.z);
-            hx1 = fmaf(w2.y, id.x, -ood.x); hy1 = fmaf(w2.z, id.y, -ood.y); hz1 = fmaf(w2.w, id.z, -ood.z);
-        }
-        float tn0 = fmaxf(fmaxf(fminf(lx0, hx0), fminf(ly0, hy0)), fmaxf(fminf(lz0, hz0), t_min));
-        float tf0 = fminf(fminf(fmaxf(lx0, hx0), fmaxf(ly0, hy0)), fminf(fmaxf(lz0, hz0), h.t));
-        float tn1 = fmaxf(fmaxf(fminf(lx1, hx1), fminf(ly1, hy1)), fmaxf(fminf(lz1, hz1), t_min));
-        float tf1 = fminf(fminf(fmaxf(lx1, hx1), fmaxf(ly1, hy1)), fminf(fmaxf(lz1, hz1), h.t));
-        // Slightly widened acceptance: the boxes are padded on the host, and <= keeps degenerate (flat) boxes alive.
-        const bool h0 = tn0 <= tf0 * 1.0000004f;
-        const bool h1 = tn1 <= tf1 * 1.0000004f;
-
-        int next;
-        if (h0 && h1) {
-            int c0 = ch.x, c1 = ch.y;
-            if (tn1 < tn0) { int t = c0; c0 = c1; c1 = t; }
-            next = c0;
-            stack[sp++] = c1;
-        }
-        else if (h0) next = ch.x;
-        else if (h1) next = ch.y;
-        else {
-            if (sp == 0) break;
-            next = stack[--sp];
-        }
-
-        bool done = false;
-        while (next < 0) {
-            const int code = ~next;
+        while (cur < 0 && cur != CRT_TRAV_DONE) {
+            const int code = ~cur;
             if (COUNT) n_prim++;
             float t;
             if (leaf_test<EXACT, SMEM_ALL>(S, code, o, d, a, inv_a, t_min, h.t, t)) {
                 h.t = t;
                 h.leaf = code;
             }
-            if (sp == 0) { done = true; break; }
-            next = stack[--sp];
+            cur = sp ? stack[--sp] : CRT_TRAV_DONE;
         }
-        if (done) break;
-        node = next;
+#if CRT_TRAV_STYLE != 1
+        if (cur == CRT_TRAV_DONE) break;
+#endif
     }
     return h;
 }

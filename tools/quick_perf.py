@@ -35,3 +35,7 @@ for i in range(reps):
     extra = f" box/ray {c.box_tests / c.rays:.1f} prim/ray {c.prim_tests / c.rays:.2f}" if flags & 2 else ""
     print(f"{W}x{H} spp {spp} depth {depth} variant {variant}: {ms:.2f} ms  {c.rays / ms / 1e3:.1f} Mrays/s  "
           f"{spp / ms * 1e3 * (W * H) / (1920 * 1080):.1f} 1080p-spp/s  L {c.rays / c.paths:.2f}{extra}")
+
+import hashlib
+acc = r.read_accum()
+print("accum sha1", hashlib.sha1(acc.tobytes()).hexdigest()[:16], "mean", float(acc[..., :3].mean() / spp))
