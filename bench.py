@@ -178,7 +178,8 @@ def run_gpu_arm(args):
     r.upload(scene)
     r.set_camera(cam)
     r.resize(W, H)
-    accum = torch.zeros((H, W, 4), dtype=torch.float32, device=dev)  # the progressive accumulation buffer (NCCL-reducible)
+    # the progressive accumulation buffer: int64 x {R, G, B, samples}, Q31.32 sums (order-free, so the NCCL sum is exact)
+    accum = torch.zeros((H, W, 4), dtype=torch.int64, device=dev)
     r.set_accum_device_buffer(accum.data_ptr())
     rgba = torch.zeros((H, W), dtype=torch.int32, device=dev)
     host_rgba = torch.zeros((H, W), dtype=torch.int32).pin_memory()

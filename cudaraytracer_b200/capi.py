@@ -17,7 +17,7 @@ CRT_OK = 0
 SPHERE, XYRECT, XZRECT, YZRECT = 0, 1, 2, 3
 LAMBERTIAN, METAL, DIELECTRIC, DIFFUSELIGHT = 0, 1, 2, 3
 CONSTANT, CHECKER, IMAGE = 0, 1, 2
-VARIANT_AUTO, VARIANT_MEGAKERNEL, VARIANT_WAVEFRONT = 0, 1, 2
+VARIANT_AUTO, VARIANT_MEGAKERNEL, VARIANT_WAVEFRONT, VARIANT_PIPELINE = 0, 1, 2, 3
 JITTER_RANDOM, JITTER_CENTER = 0, 1
 FLAG_EXACT_MATH, FLAG_COUNT_TESTS, FLAG_TRUNCATED_GRID = 1, 2, 4
 SCENE_RTIOW, SCENE_TEXTURED, SCENE_GRID_1M, SCENE_STRESS_10K, SCENE_REFERENCE_DEFAULT = 1, 2, 3, 4, 5

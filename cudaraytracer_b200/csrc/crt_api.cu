@@ -5,7 +5,7 @@
 #include "crt_internal.h"
 
 #include "kernels.cuh"
-#include "wavefront.cuh"
+#include "pipeline.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -47,15 +47,21 @@ struct crt_context
 
     // framebuffer
     uint32_t width = 0, height = 0;
-    float4* d_accum_own = nullptr;
-    float4* d_accum = nullptr;
+    long long* d_accum_own = nullptr; // 4 x int64 per pixel {R, G, B, samples}, Q31.32 (device_common.cuh)
+    long long* d_accum = nullptr;
+    float4* d_accum_f = nullptr;      // staging for crt_read_accum
     uint32_t* d_rgba = nullptr;
     int* d_ids = nullptr;
 
-    DevCounters* d_counters = nullptr;
+    DevCounters* d_counters = nullptr; // CRT_COUNTER_SHARDS entries
+    WfShard* d_shards = nullptr;       // work counters of the pipelined megakernel
+    int pipe_thresh = 20, pipe_rounds = 16, pipe_slots = 0, pipe_check = 4; // CRT_PIPE_THRESH / _ROUNDS / _SLOTS / _CHECK
     uint64_t launches = 0;
 
     WavefrontState wf;
+    size_t wf_slots = 1u << 20; // path slots of the wavefront pool (CRT_WF_SLOTS)
+    int wf_thresh = 24;         // extend refills a warp when fewer lanes than this are traversing (CRT_WF_THRESH)
+    int wf_batch_iters = 32;    // extend+shade iterations enqueued between two reads of the active count
 
     std::string err;
 };
@@ -139,10 +145,18 @@ crt_status crt_context_create(int device, crt_context** out)
     ctx->smem_per_sm = (int)prop.sharedMemPerMultiprocessor;
     const char* env = getenv("CRT_SMEM_KB");
     if (env) ctx->smem_budget_override = atoi(env) * 1024;
+    if ((env = getenv("CRT_WF_SLOTS")) && atol(env) > 0) ctx->wf_slots = (size_t)atol(env);
+    if ((env = getenv("CRT_WF_THRESH")) && atoi(env) > 0) ctx->wf_thresh = atoi(env);
+    if ((env = getenv("CRT_WF_BATCH_ITERS")) && atoi(env) > 0) ctx->wf_batch_iters = atoi(env);
+    if ((env = getenv("CRT_PIPE_THRESH")) && atoi(env) > 0) ctx->pipe_thresh = atoi(env);
+    if ((env = getenv("CRT_PIPE_ROUNDS")) && atoi(env) > 0) ctx->pipe_rounds = atoi(env);
+    if ((env = getenv("CRT_PIPE_SLOTS")) && atoi(env) > 0) ctx->pipe_slots = atoi(env);
+    if ((env = getenv("CRT_PIPE_CHECK")) && atoi(env) > 0) ctx->pipe_check = atoi(env);
     if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
-        (e = cudaMalloc(&ctx->d_counters, sizeof(DevCounters))) != cudaSuccess ||
-        (e = cudaMemset(ctx->d_counters, 0, sizeof(DevCounters))) != cudaSuccess) {
+        (e = cudaMalloc(&ctx->d_counters, CRT_COUNTER_SHARDS * sizeof(DevCounters))) != cudaSuccess ||
+        (e = cudaMemset(ctx->d_counters, 0, CRT_COUNTER_SHARDS * sizeof(DevCounters))) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->d_shards, WF_SHARDS * sizeof(WfShard))) != cudaSuccess) {
         crt_status s = cuda_fail(nullptr, e, "crt_context_create");
         crt_context_destroy(ctx);
         return s;
@@ -160,9 +174,11 @@ void crt_context_destroy(crt_context* ctx)
     free_scene(ctx);
     wavefront_free(ctx->wf);
     cudaFree(ctx->d_accum_own);
+    cudaFree(ctx->d_accum_f);
     cudaFree(ctx->d_rgba);
     cudaFree(ctx->d_ids);
     cudaFree(ctx->d_counters);
+    cudaFree(ctx->d_shards);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -334,10 +350,12 @@ crt_status crt_framebuffer_resize(crt_context* ctx, uint32_t width, uint32_t hei
     const bool external = ctx->d_accum && ctx->d_accum != ctx->d_accum_own;
     if (width != ctx->width || height != ctx->height || !ctx->d_rgba) {
         cudaFree(ctx->d_accum_own); ctx->d_accum_own = nullptr;
+        cudaFree(ctx->d_accum_f); ctx->d_accum_f = nullptr;
         cudaFree(ctx->d_rgba); ctx->d_rgba = nullptr;
         cudaFree(ctx->d_ids); ctx->d_ids = nullptr;
         size_t n = (size_t)width * height;
-        CU(cudaMalloc(&ctx->d_accum_own, n * sizeof(float4)));
+        CU(cudaMalloc(&ctx->d_accum_own, n * 4 * sizeof(long long)));
+        CU(cudaMalloc(&ctx->d_accum_f, n * sizeof(float4)));
         CU(cudaMalloc(&ctx->d_rgba, n * 4));
         CU(cudaMalloc(&ctx->d_ids, n * 4));
         ctx->width = width;
@@ -353,20 +371,22 @@ crt_status crt_accum_clear(crt_context* ctx)
     if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_accum_clear: ctx is NULL");
     if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_accum_clear: no framebuffer");
     CU(cudaSetDevice(ctx->device));
-    uint32_t n = ctx->width * ctx->height;
-    k_clear<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_accum, n);
+    uint32_t n = ctx->width * ctx->height * 2u; // two 16-byte halves per pixel
+    k_clear<<<(n + 255) / 256, 256, 0, ctx->stream>>>(reinterpret_cast<longlong2*>(ctx->d_accum), n);
     ctx->launches++;
     CU(cudaGetLastError());
     return CRT_OK;
 }
 
-crt_status crt_set_accum_device_buffer(crt_context* ctx, void* device_float4)
+crt_status crt_set_accum_device_buffer(crt_context* ctx, void* device_int64x4)
 {
     if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_set_accum_device_buffer: ctx is NULL");
     if (!ctx->d_accum_own) return crt_set_error(ctx, CRT_ERR_STATE, "crt_set_accum_device_buffer: call crt_framebuffer_resize first");
     CU(cudaSetDevice(ctx->device));
     CU(cudaStreamSynchronize(ctx->stream));
-    ctx->d_accum = device_float4 ? (float4*)device_float4 : ctx->d_accum_own;
+    if (((uintptr_t)device_int64x4 & 31u) != 0)
+        return crt_set_error(ctx, CRT_ERR_INVALID, "crt_set_accum_device_buffer: the buffer must be 32-byte aligned");
+    ctx->d_accum = device_int64x4 ? (long long*)device_int64x4 : ctx->d_accum_own;
     return CRT_OK;
 }
 
@@ -412,27 +432,6 @@ static cudaError_t launch_mega(const RenderArgs& A, dim3 grid, size_t smem, cuda
     return cudaGetLastError();
 }
 
-template <bool EXACT, bool COUNT, bool ALL, int THRESH>
-static cudaError_t launch_mega2(const RenderArgs& A, dim3 grid, size_t smem, cudaStream_t st)
-{
-    cudaError_t e = cudaFuncSetAttribute(k_render_mega2<EXACT, COUNT, ALL, THRESH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    k_render_mega2<EXACT, COUNT, ALL, THRESH><<<grid, CRT_BLOCK_THREADS, smem, st>>>(A);
-    return cudaGetLastError();
-}
-
-// Experimental schedule selection for the fast (non-exact, non-counting) megakernel: CRT_MEGA_THRESH=0 keeps
-// k_render_mega; 1/8/16/24/32 pick k_render_mega2 with that refill threshold.
-static int mega_thresh_env()
-{
-    static int v = -1;
-    if (v < 0) {
-        const char* e = getenv("CRT_MEGA_THRESH");
-        v = e ? atoi(e) : 0;
-    }
-    return v;
-}
-
 static cudaError_t dispatch_mega(const RenderArgs& A, dim3 grid, size_t smem, cudaStream_t st, bool exact, bool count, bool all)
 {
     if (exact) {
@@ -440,14 +439,6 @@ static cudaError_t dispatch_mega(const RenderArgs& A, dim3 grid, size_t smem, cu
         return all ? launch_mega<true, false, true>(A, grid, smem, st) : launch_mega<true, false, false>(A, grid, smem, st);
     }
     if (count) return all ? launch_mega<false, true, true>(A, grid, smem, st) : launch_mega<false, true, false>(A, grid, smem, st);
-    switch (mega_thresh_env()) {
-    case 1: return all ? launch_mega2<false, false, true, 1>(A, grid, smem, st) : launch_mega2<false, false, false, 1>(A, grid, smem, st);
-    case 8: return all ? launch_mega2<false, false, true, 8>(A, grid, smem, st) : launch_mega2<false, false, false, 8>(A, grid, smem, st);
-    case 16: return all ? launch_mega2<false, false, true, 16>(A, grid, smem, st) : launch_mega2<false, false, false, 16>(A, grid, smem, st);
-    case 24: return all ? launch_mega2<false, false, true, 24>(A, grid, smem, st) : launch_mega2<false, false, false, 24>(A, grid, smem, st);
-    case 32: return all ? launch_mega2<false, false, true, 32>(A, grid, smem, st) : launch_mega2<false, false, false, 32>(A, grid, smem, st);
-    default: break;
-    }
     return all ? launch_mega<false, false, true>(A, grid, smem, st) : launch_mega<false, false, false>(A, grid, smem, st);
 }
 
@@ -464,6 +455,214 @@ static int mega_blocks_per_sm(bool exact, bool count)
     return n;
 }
 
+// ------------------------------------------------------------------------------------------
+// wavefront driver
+// ------------------------------------------------------------------------------------------
+template <int THRESH, bool ALL> static cudaError_t launch_extend(const WfArgs& W, int grid, size_t smem, cudaStream_t st)
+{
+    static bool configured = false; // per instantiation; the attribute is sticky for the process
+    static size_t configured_smem = 0;
+    if (!configured || smem > configured_smem) {
+        cudaError_t e = cudaFuncSetAttribute(k_wf_extend<THRESH, ALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+        configured_smem = smem;
+    }
+    k_wf_extend<THRESH, ALL><<<grid, WF_EXT_THREADS, smem, st>>>(W);
+    return cudaGetLastError();
+}
+
+static cudaError_t dispatch_extend(const WfArgs& W, int grid, size_t smem, cudaStream_t st, int thresh, bool all)
+{
+#define CRT_EXT_CASE(T) case T: return all ? launch_extend<T, true>(W, grid, smem, st) : launch_extend<T, false>(W, grid, smem, st)
+    switch (thresh) {
+        CRT_EXT_CASE(8);
+        CRT_EXT_CASE(16);
+        CRT_EXT_CASE(20);
+        CRT_EXT_CASE(28);
+        CRT_EXT_CASE(32);
+    default:
+        CRT_EXT_CASE(24);
+    }
+#undef CRT_EXT_CASE
+}
+
+// Renders A.spp_count samples per covered pixel with the wavefront pipeline. Synchronises the stream once per
+// `wf_batch_iters` iterations to read the active count (8 bytes, pinned).
+static crt_status render_wavefront(crt_context* ctx, RenderArgs A)
+{
+    const uint64_t P = (uint64_t)A.cover_w * A.cover_h;
+    if (P == 0 || A.spp_count == 0) return CRT_OK;
+    const size_t capacity = (size_t)std::min<uint64_t>(ctx->wf_slots, P * A.spp_count);
+    CU(wavefront_reserve(ctx->wf, std::max<size_t>(capacity, 1024)));
+    WavefrontState& w = ctx->wf;
+
+    WfArgs W;
+    memset(&W, 0, sizeof(W));
+    W.r0 = w.r0; W.r1 = w.r1; W.thr = w.thr; W.px = w.px;
+    W.c = w.c;
+    W.n_pixels_cover = (uint32_t)P;
+    W.capacity = (int)capacity;
+
+    bool all = false;
+    DevScene ext_scene = A.scene;
+    // one CTA of 1024 threads per SM: the whole opt-in shared memory is available to the one scene copy
+    long budget = ctx->smem_optin - 1024; // static shared memory of the kernel + allocation granularity
+    if (ctx->smem_budget_override >= 0) budget = std::min<long>(budget, ctx->smem_budget_override);
+    size_t smem;
+    {
+        const long full = (long)ext_scene.n_nodes * 64 + (long)ext_scene.n_prims * 16;
+        if (full <= budget) {
+            ext_scene.smem_nodes = ext_scene.n_nodes; ext_scene.smem_prims = ext_scene.n_prims; ext_scene.smem_mats = 0;
+            all = true;
+            smem = (size_t)full;
+        }
+        else {
+            long rem = budget;
+            ext_scene.smem_nodes = (int)std::min<long>(ext_scene.n_nodes, rem / 64); rem -= (long)ext_scene.smem_nodes * 64;
+            ext_scene.smem_prims = (int)std::min<long>(ext_scene.n_prims, rem / 16); rem -= (long)ext_scene.smem_prims * 16;
+            ext_scene.smem_mats = 0;
+            smem = (size_t)(budget - rem);
+        }
+    }
+    const int ext_grid = ctx->sm_count;
+    const int shade_grid = (int)std::min<size_t>((size_t)ctx->sm_count * 8, (capacity + WF_SHADE_THREADS - 1) / WF_SHADE_THREADS);
+
+    // passes: the work counter is 32 bits
+    const uint32_t stride = A.spp_stride ? A.spp_stride : 1u;
+    const uint32_t spp_per_pass = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(A.spp_count, 0xF0000000ull / P));
+    for (uint32_t done = 0; done < A.spp_count; done += spp_per_pass) {
+        const uint32_t spp = std::min(spp_per_pass, A.spp_count - done);
+        W.R = A;
+        W.R.spp_begin = A.spp_begin + done * stride;
+        W.R.spp_count = spp;
+        W.R.spp_stride = stride;
+        const uint32_t work_total = (uint32_t)(P * spp);
+        const uint32_t first = (uint32_t)std::min<uint64_t>(capacity, work_total);
+        k_wf_generate<<<((uint32_t)capacity + WF_SHADE_THREADS - 1) / WF_SHADE_THREADS, WF_SHADE_THREADS, 0, ctx->stream>>>(W, work_total);
+        ctx->launches++;
+        CU(cudaGetLastError());
+        int iter = 0;
+        unsigned long long first_paths = first;
+        while (true) {
+            for (int it = 0; it < ctx->wf_batch_iters; it++, iter++) {
+                W.iter = iter;
+                W.R.scene = ext_scene;
+                CU(dispatch_extend(W, ext_grid, smem, ctx->stream, ctx->wf_thresh, all));
+                W.R.scene = A.scene; // shade reads the tables from global memory
+                W.R.scene.smem_nodes = W.R.scene.smem_prims = W.R.scene.smem_mats = 0;
+                k_wf_shade<<<shade_grid, WF_SHADE_THREADS, 0, ctx->stream>>>(W);
+                CU(cudaGetLastError());
+                ctx->launches += 2;
+            }
+            k_wf_fold_counters<<<1, 1, 0, ctx->stream>>>(w.c, A.counters, first_paths, (iter - 1) & 1, w.d_alive);
+            ctx->launches++;
+            first_paths = 0;
+            CU(cudaMemcpyAsync(w.h_alive, w.d_alive, 2 * sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+            if (w.h_alive[0] == 0u && w.h_alive[1] == 0u) break; // no live path and no unclaimed (pixel, sample) item
+        }
+        const uint32_t npx = A.cover_w * A.cover_h;
+        k_wf_add_count<<<(npx + 255) / 256, 256, 0, ctx->stream>>>(A.accum, A.width, A.cover_w, A.cover_h, (long long)spp);
+        ctx->launches++;
+        CU(cudaGetLastError());
+    }
+    return CRT_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// pipelined persistent megakernel driver
+// ------------------------------------------------------------------------------------------
+__global__ void k_pipe_init(WfShard* shards, uint32_t work_total)
+{
+    const uint32_t i = threadIdx.x;
+    if (i >= WF_SHARDS) return;
+    const uint32_t per = work_total / WF_SHARDS, extra = work_total % WF_SHARDS;
+    const uint32_t b = i * per + min(i, extra);
+    shards[i].head = b;
+    shards[i].end = b + per + (i < extra ? 1u : 0u);
+}
+
+template <int THRESH, bool ALL> static cudaError_t launch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st)
+{
+    static size_t configured_smem = 0;
+    if (smem > configured_smem) {
+        cudaError_t e = cudaFuncSetAttribute(k_render_pipe<THRESH, ALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured_smem = smem;
+    }
+    k_render_pipe<THRESH, ALL><<<grid, PIPE_THREADS, smem, st>>>(W);
+    return cudaGetLastError();
+}
+
+static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st, int thresh, bool all)
+{
+#define CRT_PIPE_CASE(T) case T: return all ? launch_pipe<T, true>(W, grid, smem, st) : launch_pipe<T, false>(W, grid, smem, st)
+    switch (thresh) {
+        CRT_PIPE_CASE(12);
+        CRT_PIPE_CASE(16);
+        CRT_PIPE_CASE(24);
+        CRT_PIPE_CASE(28);
+        CRT_PIPE_CASE(32);
+    default:
+        CRT_PIPE_CASE(20);
+    }
+#undef CRT_PIPE_CASE
+}
+
+static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
+{
+    const uint64_t P = (uint64_t)A.cover_w * A.cover_h;
+    if (P == 0 || A.spp_count == 0) return CRT_OK;
+    // shared memory: [scene prefix][pool of N slots: 56 B of path state + 7 ring entries]
+    const long per_slot = 3 * 16 + 8 + 4 * PQ_COUNT;
+    const long budget = (ctx->smem_budget_override >= 0 ? std::min<long>(ctx->smem_budget_override, ctx->smem_optin) : (long)ctx->smem_optin) - 1024;
+    const long full = (long)A.scene.n_nodes * 64 + (long)A.scene.n_prims * 48;
+    int n_slots = ctx->pipe_slots > 0 ? ctx->pipe_slots : (full + 2048 * per_slot <= budget ? 2048 : 1024);
+    while (n_slots & (n_slots - 1)) n_slots &= n_slots - 1; // power of two
+    n_slots = std::max(n_slots, 64);
+    if ((long)n_slots * per_slot > budget) return crt_set_error(ctx, CRT_ERR_INVALID, "render_pipeline: CRT_PIPE_SLOTS does not fit in shared memory");
+    bool all = false;
+    long rem = budget - (long)n_slots * per_slot;
+    if (full <= rem) {
+        A.scene.smem_nodes = A.scene.n_nodes; A.scene.smem_prims = A.scene.n_prims; A.scene.smem_mats = A.scene.n_prims;
+        all = true;
+        rem -= full;
+    }
+    else {
+        A.scene.smem_nodes = (int)std::min<long>(A.scene.n_nodes, rem / 64); rem -= (long)A.scene.smem_nodes * 64;
+        A.scene.smem_prims = (int)std::min<long>(A.scene.n_prims, rem / 16); rem -= (long)A.scene.smem_prims * 16;
+        A.scene.smem_mats = (int)std::min<long>(A.scene.n_prims, rem / 32); rem -= (long)A.scene.smem_mats * 32;
+    }
+    const size_t smem = (size_t)(budget - rem);
+
+    PipeArgs W;
+    memset(&W, 0, sizeof(W));
+    W.shards = ctx->d_shards;
+    W.stat = ctx->d_counters;
+    W.n_pixels_cover = (uint32_t)P;
+    W.n_slots = n_slots;
+    W.max_rounds = ctx->pipe_rounds;
+    W.check_every = ctx->pipe_check;
+    const uint32_t stride = A.spp_stride ? A.spp_stride : 1u;
+    const uint32_t spp_per_pass = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(A.spp_count, 0xF0000000ull / P));
+    for (uint32_t done = 0; done < A.spp_count; done += spp_per_pass) {
+        const uint32_t spp = std::min(spp_per_pass, A.spp_count - done);
+        W.R = A;
+        W.R.spp_begin = A.spp_begin + done * stride;
+        W.R.spp_count = spp;
+        W.R.spp_stride = stride;
+        k_pipe_init<<<1, WF_SHARDS, 0, ctx->stream>>>(ctx->d_shards, (uint32_t)(P * spp));
+        CU(cudaGetLastError());
+        CU(dispatch_pipe(W, ctx->sm_count, smem, ctx->stream, ctx->pipe_thresh, all));
+        const uint32_t npx = A.cover_w * A.cover_h;
+        k_wf_add_count<<<(npx + 255) / 256, 256, 0, ctx->stream>>>(A.accum, A.width, A.cover_w, A.cover_h, (long long)spp);
+        CU(cudaGetLastError());
+        ctx->launches += 3;
+    }
+    return CRT_OK;
+}
+
 extern "C" {
 
 crt_status crt_render(crt_context* ctx, const crt_render_params* p)
@@ -472,7 +671,7 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
     if (!ctx->have_scene) return crt_set_error(ctx, CRT_ERR_STATE, "crt_render: no scene uploaded");
     if (!ctx->have_cam) return crt_set_error(ctx, CRT_ERR_STATE, "crt_render: no camera set");
     if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_render: no framebuffer (crt_framebuffer_resize)");
-    if (p->variant < CRT_VARIANT_AUTO || p->variant > CRT_VARIANT_WAVEFRONT) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_render: bad variant");
+    if (p->variant < CRT_VARIANT_AUTO || p->variant > CRT_VARIANT_PIPELINE) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_render: bad variant");
     if (p->jitter != CRT_JITTER_RANDOM && p->jitter != CRT_JITTER_CENTER) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_render: bad jitter mode");
     CU(cudaSetDevice(ctx->device));
 
@@ -494,8 +693,13 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
     if (p->spp_count > 0 && A.cover_w > 0 && A.cover_h > 0) {
         int variant = p->variant == CRT_VARIANT_AUTO ? CRT_VARIANT_MEGAKERNEL : p->variant;
-        if (variant == CRT_VARIANT_WAVEFRONT) {
-            return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, "crt_render: wavefront variant not built yet");
+        if (variant == CRT_VARIANT_WAVEFRONT || variant == CRT_VARIANT_PIPELINE) {
+            if (exact || count) return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, "crt_render: EXACT_MATH / COUNT_TESTS are megakernel-only");
+            crt_status ws = variant == CRT_VARIANT_WAVEFRONT ? render_wavefront(ctx, A) : render_pipeline(ctx, A);
+            if (ws != CRT_OK) return ws;
+            CU(cudaEventRecord(ctx->ev1, ctx->stream));
+            ctx->timed = true;
+            return CRT_OK;
         }
         bool all = false;
         size_t smem = plan_smem(ctx, mega_blocks_per_sm(exact, count), A.scene, all);
@@ -545,7 +749,11 @@ crt_status crt_read_accum(crt_context* ctx, float* out_float4)
     if (!ctx || !out_float4) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_read_accum: NULL argument");
     if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_read_accum: no framebuffer");
     CU(cudaSetDevice(ctx->device));
-    CU(cudaMemcpyAsync(out_float4, ctx->d_accum, (size_t)ctx->width * ctx->height * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    const uint32_t n = ctx->width * ctx->height;
+    k_accum_to_float<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_accum, ctx->d_accum_f, n);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(out_float4, ctx->d_accum_f, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     return CRT_OK;
 }
@@ -588,10 +796,12 @@ crt_status crt_get_counters(crt_context* ctx, crt_counters* out)
 {
     if (!ctx || !out) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_get_counters: NULL argument");
     CU(cudaSetDevice(ctx->device));
-    DevCounters h;
-    CU(cudaMemcpyAsync(&h, ctx->d_counters, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    static_assert(sizeof(DevCounters) == 128, "one counter shard per 128 bytes");
+    std::vector<DevCounters> h(CRT_COUNTER_SHARDS);
+    CU(cudaMemcpyAsync(h.data(), ctx->d_counters, h.size() * sizeof(DevCounters), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
-    out->paths = h.paths; out->rays = h.rays; out->box_tests = h.box_tests; out->prim_tests = h.prim_tests;
+    out->paths = out->rays = out->box_tests = out->prim_tests = 0;
+    for (const DevCounters& c : h) { out->paths += c.paths; out->rays += c.rays; out->box_tests += c.box_tests; out->prim_tests += c.prim_tests; }
     out->kernel_launches = ctx->launches;
     return CRT_OK;
 }
@@ -600,7 +810,7 @@ crt_status crt_reset_counters(crt_context* ctx)
 {
     if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_reset_counters: ctx is NULL");
     CU(cudaSetDevice(ctx->device));
-    CU(cudaMemsetAsync(ctx->d_counters, 0, sizeof(DevCounters), ctx->stream));
+    CU(cudaMemsetAsync(ctx->d_counters, 0, CRT_COUNTER_SHARDS * sizeof(DevCounters), ctx->stream));
     ctx->launches = 0;
     return CRT_OK;
 }

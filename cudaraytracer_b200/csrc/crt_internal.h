@@ -18,7 +18,7 @@ crt_status crt_set_error(crt_context* ctx, crt_status st, const char* msg);
 //   w1 = {c0.hi.y, c0.hi.z, c1.lo.x, c1.lo.y}
 //   w2 = {c1.lo.z, c1.hi.x, c1.hi.y, c1.hi.z}
 //   w3 = {child0, child1, 0, 0} (int bits)
-// child >= 0: index of an inner node. child < 0: leaf, ~child = (type << 28) | prim index.
+// child >= 0: index of an inner node. child < 0: leaf, ~child = (type << 28) | (material type << 26) | prim index.
 // Nodes are stored breadth-first so the first K nodes are the hottest (they are staged in shared memory).
 //
 // Primitive i (leaf order): prim[i] = sphere {cx, cy, cz, r}
@@ -37,7 +37,8 @@ struct CrtPackedNode
 static_assert(sizeof(CrtPackedNode) == 64, "node is 64 bytes");
 
 #define CRT_LEAF_TYPE_SHIFT 28
-#define CRT_LEAF_INDEX_MASK 0x0FFFFFFF
+#define CRT_LEAF_MAT_SHIFT 26 /* 2 bits: the material type of the primitive, so that a hit can be binned without a load */
+#define CRT_LEAF_INDEX_MASK 0x03FFFFFF
 
 struct CrtPackedScene
 {

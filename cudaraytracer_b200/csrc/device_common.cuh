@@ -38,16 +38,38 @@ struct DevCamera
     float lens_radius, focus_dist; // thin-lens extension; lens_radius == 0 is the reference camera
 };
 
-struct DevCounters
+// Counters are SHARDED over CRT_COUNTER_SHARDS addresses 128 bytes apart (same-address atomics serialise in the L2, ~8 ns
+// each on B200); crt_get_counters sums the shards.
+#define CRT_COUNTER_SHARDS 64
+struct alignas(128) DevCounters
 {
     unsigned long long paths, rays, box_tests, prim_tests;
 };
+
+// Progressive accumulation buffer: four signed 64-bit integers per pixel {R, G, B, samples}. R/G/B hold the radiance SUM in
+// Q31.32 fixed point (value * 2^32). Integer addition is associative, so the buffer is bit-identical for any schedule of the
+// same sample set: any kernel variant, any order of atomic adds, any number of GPUs summed with NCCL (SURVEY.md §7 hard parts).
+// Every binary32 sample >= 2^-32 in magnitude is represented exactly, i.e. the sum is the exact sum of the FP32 samples.
+#define CRT_FIXED_ONE 4294967296.0f
+#define CRT_FIXED_INV 2.3283064365386963e-10f
+#define CRT_FIXED_MAX 1073741824.0f /* per-sample clamp (2^30): 2^33 samples of that size before overflow */
+
+__device__ __forceinline__ long long crt_to_fixed(float x)
+{
+    if (!(x == x)) x = 0.0f; // a NaN sample (degenerate direction) contributes nothing
+    x = fminf(fmaxf(x, -CRT_FIXED_MAX), CRT_FIXED_MAX);
+    return __float2ll_rn(x * CRT_FIXED_ONE); // exact: power-of-two scaling, then an exact integer conversion
+}
+__host__ __device__ __forceinline__ float crt_from_fixed(long long v)
+{
+    return (float)v * CRT_FIXED_INV; // one rounding (int64 -> binary32), the scaling is exact
+}
 
 struct RenderArgs
 {
     DevScene scene;
     DevCamera cam;
-    float4* accum;       // width*height: xyz = radiance sum, w = samples accumulated
+    long long* accum;    // width*height x {R, G, B, samples}, see above
     DevCounters* counters;
     uint32_t width, height;       // image size
     uint32_t cover_w, cover_h;    // pixels actually rendered (== width/height unless CRT_FLAG_TRUNCATED_GRID)
@@ -100,7 +122,9 @@ __host__ __device__ __forceinline__ float crt_uniform(uint32_t x)
 }
 
 // ------------------------------------------------------------------------------------------
-// float3 helpers (operators kept minimal; contraction is left to the compiler in the fast path)
+// float3 helpers. Device code is compiled with -fmad=false: the compiler never contracts a*b+c on its own, every fused
+// multiply-add of the fast path is an explicit fmaf(). That makes the arithmetic of a function independent of the kernel it is
+// inlined into, which is what lets the three render variants produce bit-identical samples.
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
 __device__ __forceinline__ float3 operator+(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
@@ -108,7 +132,9 @@ __device__ __forceinline__ float3 operator-(float3 a, float3 b) { return f3(a.x 
 __device__ __forceinline__ float3 operator*(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
 __device__ __forceinline__ float3 operator*(float s, float3 a) { return f3(s * a.x, s * a.y, s * a.z); }
 __device__ __forceinline__ float3 operator-(float3 a) { return f3(-a.x, -a.y, -a.z); }
-__device__ __forceinline__ float dot3(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float dot3(float3 a, float3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+// a + s * b
+__device__ __forceinline__ float3 madd3(float s, float3 b, float3 a) { return f3(fmaf(s, b.x, a.x), fmaf(s, b.y, a.y), fmaf(s, b.z, a.z)); }
 
 // Approximate single-instruction forms for the throughput path (MUFU.RCP / MUFU.SQRT; ~1-2 ulp).
 __device__ __forceinline__ float fast_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }

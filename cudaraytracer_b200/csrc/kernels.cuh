@@ -4,8 +4,10 @@
 //                   waiting for the longest path of the warp, which is what Kernel.cu:137-148 + color() do).
 //   k_primary_ids   exact-arithmetic primary-ray closest hit -> hittable index (parity hook).
 //   k_resolve       accumulation buffer -> packed RGBA8, bit-compatible with Kernel.cu:12-19,151-157.
-//   k_clear         zero the accumulation buffer.
-// Wavefront kernels live in wavefront.cuh.
+//   k_clear         zero the accumulation buffer.      k_accum_to_float  fixed-point buffer -> float4 {sum rgb, samples}.
+// Wavefront kernels live in wavefront.cuh. Both variants share gen_primary() / scatter_step() below, so that every
+// (pixel, sample) yields the same FP32 radiance whichever kernel computes it, and the integer accumulation makes the
+// buffers bit-identical.
 #pragma once
 
 #include "shade.cuh"
@@ -22,7 +24,7 @@ __device__ __forceinline__ void tile_pixel(uint32_t tiles_x, int& x, int& y)
 
 __device__ __forceinline__ void flush_counters(DevCounters* c, unsigned paths, unsigned rays, unsigned nbox, unsigned nprim, bool count)
 {
-    // warp-aggregated: one atomic per warp per counter
+    // warp-aggregated: one atomic per warp per counter, spread over the counter shards
     for (int off = 16; off > 0; off >>= 1) {
         paths += __shfl_xor_sync(0xffffffffu, paths, off);
         rays += __shfl_xor_sync(0xffffffffu, rays, off);
@@ -32,6 +34,7 @@ __device__ __forceinline__ void flush_counters(DevCounters* c, unsigned paths, u
         }
     }
     if ((threadIdx.x & 31) == 0) {
+        c += (blockIdx.x + (threadIdx.x >> 5)) & (CRT_COUNTER_SHARDS - 1);
         atomicAdd(&c->paths, (unsigned long long)paths);
         atomicAdd(&c->rays, (unsigned long long)rays);
         if (count) {
@@ -39,6 +42,38 @@ __device__ __forceinline__ void flush_counters(DevCounters* c, unsigned paths, u
             atomicAdd(&c->prim_tests, (unsigned long long)nprim);
         }
     }
+}
+
+// Camera path start for (pixel, sample): Philox block (pixel, sample, 0, CAMERA) -> jitter + lens (Kernel.cu:139-146).
+template <bool EXACT>
+__device__ __forceinline__ void gen_primary(const RenderArgs& A, int x, int y, uint32_t pixel, uint32_t sample, float3& o, float3& d)
+{
+    uint4 r = crt_philox4x32_10(make_uint4(pixel, sample, 0u, CRT_STREAM_CAMERA), A.seed_lo, A.seed_hi);
+    float j1 = 0.5f, j2 = 0.5f;
+    if (A.jitter == CRT_JITTER_RANDOM) { j1 = crt_uniform(r.x); j2 = crt_uniform(r.y); }
+    camera_ray<EXACT>(A.cam, A.width, A.height, x, y, j1, j2, o, d);
+    if (A.cam.lens_radius > 0.f) apply_lens(A.cam, crt_uniform(r.z), crt_uniform(r.w), o, d);
+}
+
+// What happens to a path after its closest-hit query (Kernel.cu:40-77). Returns true if the path continues with the
+// scattered ray (o, d, thr updated, bounce incremented); false if it ended, with its radiance in `add`.
+template <bool SMEM_ALL>
+__device__ __forceinline__ bool scatter_step(const RenderArgs& A, const SceneView& S, Hit h, uint32_t pixel, uint32_t sample,
+                                             uint32_t& bounce, float3& o, float3& d, float3& thr, float3& add)
+{
+    if (h.leaf < 0) { // miss: background (Kernel.cu:41-44)
+        add = thr * background(A.cam, d);
+        return false;
+    }
+    uint4 r = crt_philox4x32_10(make_uint4(pixel, sample, bounce, CRT_STREAM_SCATTER), A.seed_lo, A.seed_hi);
+    float4 xi = make_float4(crt_uniform(r.x), crt_uniform(r.y), crt_uniform(r.z), crt_uniform(r.w));
+    bool alive = shade_hit<SMEM_ALL>(S, h, o, d, thr, add, xi);
+    bounce++;
+    if (alive && bounce >= A.max_depth) { // exceeded recursion: black (Kernel.cu:79)
+        alive = false;
+        add = f3(0.f, 0.f, 0.f);
+    }
+    return alive;
 }
 
 template <bool EXACT, bool COUNT, bool SMEM_ALL>
@@ -53,8 +88,7 @@ __global__ void __launch_bounds__(CRT_BLOCK_THREADS) k_render_mega(const __grid_
     const bool inside = (uint32_t)x < A.cover_w && (uint32_t)y < A.cover_h;
     const uint32_t pixel = (uint32_t)y * A.width + (uint32_t)x;
 
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (inside) acc = A.accum[pixel];
+    long long acc_r = 0, acc_g = 0, acc_b = 0; // this launch's samples; added to the buffer once at the end
 
     unsigned n_paths = 0, n_rays = 0, n_box = 0, n_prim = 0;
     uint32_t s = 0;
@@ -68,11 +102,7 @@ __global__ void __launch_bounds__(CRT_BLOCK_THREADS) k_render_mega(const __grid_
         if (need_gen) {
             if (s >= A.spp_count) break;
             sample = A.spp_begin + s * stride;
-            uint4 r = crt_philox4x32_10(make_uint4(pixel, sample, 0u, CRT_STREAM_CAMERA), A.seed_lo, A.seed_hi);
-            float j1 = 0.5f, j2 = 0.5f;
-            if (A.jitter == CRT_JITTER_RANDOM) { j1 = crt_uniform(r.x); j2 = crt_uniform(r.y); }
-            camera_ray<EXACT>(A.cam, A.width, A.height, x, y, j1, j2, o, d);
-            if (A.cam.lens_radius > 0.f) apply_lens(A.cam, crt_uniform(r.z), crt_uniform(r.w), o, d);
+            gen_primary<EXACT>(A, x, y, pixel, sample, o, d);
             thr = f3(1.f, 1.f, 1.f);
             bounce = 0;
             need_gen = false;
@@ -80,30 +110,19 @@ __global__ void __launch_bounds__(CRT_BLOCK_THREADS) k_render_mega(const __grid_
         }
         n_rays++;
         Hit h = closest_hit<EXACT, COUNT, SMEM_ALL>(S, o, d, 0.001f, 3.402823466e+38f, n_box, n_prim);
-        bool finished;
         float3 add;
-        if (h.leaf < 0) {
-            add = thr * background(A.cam, d);
-            finished = true;
-        }
-        else {
-            uint4 r = crt_philox4x32_10(make_uint4(pixel, sample, bounce, CRT_STREAM_SCATTER), A.seed_lo, A.seed_hi);
-            float4 xi = make_float4(crt_uniform(r.x), crt_uniform(r.y), crt_uniform(r.z), crt_uniform(r.w));
-            bool alive = shade_hit<SMEM_ALL>(S, h, o, d, thr, add, xi);
-            bounce++;
-            finished = !alive;
-            if (alive && bounce >= A.max_depth) { // exceeded recursion: black (Kernel.cu:79)
-                finished = true;
-                add = f3(0.f, 0.f, 0.f);
-            }
-        }
-        if (finished) {
-            acc.x += add.x; acc.y += add.y; acc.z += add.z; acc.w += 1.0f;
+        if (!scatter_step<SMEM_ALL>(A, S, h, pixel, sample, bounce, o, d, thr, add)) {
+            acc_r += crt_to_fixed(add.x); acc_g += crt_to_fixed(add.y); acc_b += crt_to_fixed(add.z);
             s++;
             need_gen = true;
         }
     }
-    if (inside) A.accum[pixel] = acc;
+    if (inside) { // the pixel is owned by this thread for the whole launch: plain read-modify-write
+        longlong2* px = reinterpret_cast<longlong2*>(A.accum + 4 * (size_t)pixel);
+        longlong2 rg = px[0], bn = px[1];
+        rg.x += acc_r; rg.y += acc_g; bn.x += acc_b; bn.y += (long long)A.spp_count;
+        px[0] = rg; px[1] = bn;
+    }
     flush_counters(A.counters, n_paths, n_rays, n_box, n_prim, COUNT);
 }
 
@@ -139,14 +158,17 @@ template <bool SMEM_ALL> __global__ void __launch_bounds__(CRT_BLOCK_THREADS) k_
 }
 
 // Kernel.cu:151-157 + RgbToInt :12-19: col / spp -> 255 * sqrtf -> clamp [0,255] -> truncate -> A<<24|B<<16|G<<8|R.
-// IEEE division and square root so the result is bit-identical to the host oracle for the same buffer.
-__global__ void k_resolve(const float4* __restrict__ accum, uint32_t* __restrict__ out, uint32_t width, uint32_t cover_w, uint32_t cover_h)
+// The FP32 sum is the one crt_read_accum reports (fixed point -> binary32, one rounding); IEEE division and square root
+// so the result is bit-identical to the host oracle for the same buffer.
+__global__ void k_resolve(const long long* __restrict__ accum, uint32_t* __restrict__ out, uint32_t width, uint32_t cover_w, uint32_t cover_h)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= cover_w * cover_h) return;
     uint32_t x = i % cover_w, y = i / cover_w;
     uint32_t pixel = y * width + x;
-    float4 a = accum[pixel];
+    const longlong2* px = reinterpret_cast<const longlong2*>(accum + 4 * (size_t)pixel);
+    longlong2 rg = px[0], bn = px[1];
+    float4 a = make_float4(crt_from_fixed(rg.x), crt_from_fixed(rg.y), crt_from_fixed(bn.x), (float)bn.y);
     uint32_t packed = 0xFF000000u;
     if (a.w > 0.f) {
         float r = mul_rn(255.0f, sqrt_rn(div_rn(a.x, a.w)));
@@ -160,170 +182,17 @@ __global__ void k_resolve(const float4* __restrict__ accum, uint32_t* __restrict
     out[pixel] = packed;
 }
 
-__global__ void k_clear(float4* __restrict__ accum, uint32_t n)
+__global__ void k_accum_to_float(const long long* __restrict__ accum, float4* __restrict__ out, uint32_t n)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) accum[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i >= n) return;
+    const longlong2* px = reinterpret_cast<const longlong2*>(accum + 4 * (size_t)i);
+    longlong2 rg = px[0], bn = px[1];
+    out[i] = make_float4(crt_from_fixed(rg.x), crt_from_fixed(rg.y), crt_from_fixed(bn.x), (float)bn.y);
 }
 
-// ------------------------------------------------------------------------------------------
-// k_render_mega2 — megakernel with a FLAT per-lane state machine and thresholded lane refill.
-//
-// ncu of k_render_mega (profiles/r1) shows the traversal loop running with 17 of 32 lanes on average: every lane
-// of a warp waits for the warp's longest traversal before any lane may shade. Here a lane is in one of three
-// states — at a node (cur >= 0), at a leaf (cur < 0), or waiting to shade/regenerate (cur == IDLE) — and the warp
-// runs shade/regenerate for the waiting lanes as soon as fewer than THRESH lanes are still traversing, instead of
-// when none is. THRESH = 1 reproduces the old schedule; 32 refills as soon as any lane waits.
-// Arithmetic, Philox keys and accumulation order are identical to k_render_mega, so the two are bit-identical.
-// ------------------------------------------------------------------------------------------
-#define CRT_IDLE ((int)0x80000000)
-
-template <bool EXACT, bool COUNT, bool SMEM_ALL, int THRESH>
-__global__ void __launch_bounds__(CRT_BLOCK_THREADS, 4) k_render_mega2(const __grid_constant__ RenderArgs A)
+__global__ void k_clear(longlong2* __restrict__ accum, uint32_t n2)
 {
-    extern __shared__ float4 smem[];
-    const SceneView S = stage_scene(A.scene, smem);
-    __syncthreads();
-
-    int x, y;
-    tile_pixel((A.cover_w + 15) / 16, x, y);
-    const bool inside = (uint32_t)x < A.cover_w && (uint32_t)y < A.cover_h;
-    const uint32_t pixel = (uint32_t)y * A.width + (uint32_t)x;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (inside) acc = A.accum[pixel];
-
-    unsigned n_paths = 0, n_rays = 0, n_box = 0, n_prim = 0;
-    uint32_t s = 0, bounce = 0, sample = 0;
-    const uint32_t stride = A.spp_stride ? A.spp_stride : 1u;
-    bool alive = inside && A.spp_count > 0;
-    bool need_gen = true;
-    float3 o = f3(0.f, 0.f, 0.f), d = f3(0.f, 0.f, 1.f), thr = f3(1.f, 1.f, 1.f);
-    float3 id = f3(0.f, 0.f, 0.f), ood = f3(0.f, 0.f, 0.f);
-    float a = 1.f, inv_a = 1.f;
-    Hit h;
-    h.t = 3.402823466e+38f;
-    h.leaf = -1;
-    int cur = CRT_IDLE, sp = 0;
-    int stack[CRT_STACK_SIZE];
-    const float t_min = 0.001f;
-
-    while (true) {
-        const bool trav = cur != CRT_IDLE;
-        const bool want_s = alive && !trav;
-        const unsigned mt = __ballot_sync(0xffffffffu, trav);
-        const unsigned ms = __ballot_sync(0xffffffffu, want_s);
-        if ((mt | ms) == 0u) break;
-        if (ms != 0u && (mt == 0u || __popc(mt) < THRESH)) {
-            if (want_s) {
-                if (!need_gen && h.leaf < 0) { // the ray escaped: background (Kernel.cu:41-44)
-                    float3 add = thr * background(A.cam, d);
-                    acc.x += add.x; acc.y += add.y; acc.z += add.z; acc.w += 1.0f;
-                    s++;
-                    need_gen = true;
-                }
-                if (need_gen && s >= A.spp_count) {
-                    alive = false;
-                }
-                else {
-                    const bool gen = need_gen;
-                    if (gen) sample = A.spp_begin + s * stride;
-                    // one Philox block per lane, whichever state it is in
-                    const uint4 r = crt_philox4x32_10(make_uint4(pixel, sample, gen ? 0u : bounce, gen ? CRT_STREAM_CAMERA : CRT_STREAM_SCATTER),
-                                                      A.seed_lo, A.seed_hi);
-                    const float4 xi = make_float4(crt_uniform(r.x), crt_uniform(r.y), crt_uniform(r.z), crt_uniform(r.w));
-                    if (gen) {
-                        float j1 = 0.5f, j2 = 0.5f;
-                        if (A.jitter == CRT_JITTER_RANDOM) { j1 = xi.x; j2 = xi.y; }
-                        camera_ray<EXACT>(A.cam, A.width, A.height, x, y, j1, j2, o, d);
-                        if (A.cam.lens_radius > 0.f) apply_lens(A.cam, xi.z, xi.w, o, d);
-                        thr = f3(1.f, 1.f, 1.f);
-                        bounce = 0;
-                        need_gen = false;
-                        n_paths++;
-                    }
-                    else {
-                        float3 add;
-                        bool cont = shade_hit<SMEM_ALL>(S, h, o, d, thr, add, xi);
-                        bounce++;
-                        if (cont && bounce >= A.max_depth) { // exceeded recursion: black (Kernel.cu:79)
-                            cont = false;
-                            add = f3(0.f, 0.f, 0.f);
-                        }
-                        if (!cont) {
-                            acc.x += add.x; acc.y += add.y; acc.z += add.z; acc.w += 1.0f;
-                            s++;
-                            need_gen = true; // regenerates at the next refill
-                        }
-                    }
-                    if (!need_gen) { // start the closest-hit query of the new ray
-                        n_rays++;
-                        const float tiny = 1e-18f;
-                        float3 dc = f3(fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x, fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y,
-                                       fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
-                        if (EXACT) {
-                            a = dot3_rn(d, d); inv_a = 0.f;
-                            id = f3(div_rn(1.0f, dc.x), div_rn(1.0f, dc.y), div_rn(1.0f, dc.z));
-                            ood = f3(0.f, 0.f, 0.f);
-                        }
-                        else {
-                            a = dot3(d, d); inv_a = fast_rcp(a);
-                            id = f3(fast_rcp(dc.x), fast_rcp(dc.y), fast_rcp(dc.z));
-                            ood = f3(o.x * id.x, o.y * id.y, o.z * id.z);
-                        }
-                        h.t = 3.402823466e+38f;
-                        h.leaf = -1;
-                        cur = 0;
-                        sp = 0;
-                    }
-                }
-            }
-            continue;
-        }
-
-        if (cur >= 0) { // ---- node step: both child boxes, near child first ----
-            float4 w0, w1, w2;
-            int2 ch;
-            load_node<SMEM_ALL>(S, cur, w0, w1, w2, ch);
-            if (COUNT) n_box += 2;
-            float lx0, ly0, lz0, hx0, hy0, hz0, lx1, ly1, lz1, hx1, hy1, hz1;
-            if (EXACT) {
-                lx0 = (w0.x - o.x) * id.x; ly0 = (w0.y - o.y) * id.y; lz0 = (w0.z - o.z) * id.z;
-                hx0 = (w0.w - o.x) * id.x; hy0 = (w1.x - o.y) * id.y; hz0 = (w1.y - o.z) * id.z;
-                lx1 = (w1.z - o.x) * id.x; ly1 = (w1.w - o.y) * id.y; lz1 = (w2.x - o.z) * id.z;
-                hx1 = (w2.y - o.x) * id.x; hy1 = (w2.z - o.y) * id.y; hz1 = (w2.w - o.z) * id.z;
-            }
-            else {
-                lx0 = fmaf(w0.x, id.x, -ood.x); ly0 = fmaf(w0.y, id.y, -ood.y); lz0 = fmaf(w0.z, id.z, -ood.z);
-                hx0 = fmaf(w0.w, id.x, -ood.x); hy0 = fmaf(w1.x, id.y, -ood.y); hz0 = fmaf(w1.y, id.z, -ood.z);
-                lx1 = fmaf(w1.z, id.x, -ood.x); ly1 = fmaf(w1.w, id.y, -ood.y); lz1 = fmaf(w2.x, id.z, -ood.z);
-                hx1 = fmaf(w2.y, id.x, -ood.x); hy1 = fmaf(w2.z, id.y, -ood.y); hz1 = fmaf(w2.w, id.z, -ood.z);
-            }
-            const float tn0 = fmaxf(fmaxf(fminf(lx0, hx0), fminf(ly0, hy0)), fmaxf(fminf(lz0, hz0), t_min));
-            const float tf0 = fminf(fminf(fmaxf(lx0, hx0), fmaxf(ly0, hy0)), fminf(fmaxf(lz0, hz0), h.t));
-            const float tn1 = fmaxf(fmaxf(fminf(lx1, hx1), fminf(ly1, hy1)), fmaxf(fminf(lz1, hz1), t_min));
-            const float tf1 = fminf(fminf(fmaxf(lx1, hx1), fmaxf(ly1, hy1)), fminf(fmaxf(lz1, hz1), h.t));
-            const bool h0 = tn0 <= tf0;
-            const bool h1 = tn1 <= tf1;
-            if (h0 && h1) {
-                const bool swap = tn1 < tn0;
-                cur = swap ? ch.y : ch.x;
-                stack[sp++] = swap ? ch.x : ch.y;
-            }
-            else if (h0) cur = ch.x;
-            else if (h1) cur = ch.y;
-            else cur = sp ? stack[--sp] : CRT_IDLE;
-        }
-        if (cur < 0 && cur != CRT_IDLE) { // ---- leaf step ----
-            const int code = ~cur;
-            if (COUNT) n_prim++;
-            float t;
-            if (leaf_test<EXACT, SMEM_ALL>(S, code, o, d, a, inv_a, t_min, h.t, t)) {
-                h.t = t;
-                h.leaf = code;
-            }
-            cur = sp ? stack[--sp] : CRT_IDLE;
-        }
-    }
-    if (inside) A.accum[pixel] = acc;
-    flush_counters(A.counters, n_paths, n_rays, n_box, n_prim, COUNT);
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n2) accum[i] = make_longlong2(0, 0);
 }

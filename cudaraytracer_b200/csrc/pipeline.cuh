@@ -1,0 +1,338 @@
+// pipeline.cuh — k_render_pipe: persistent-CTA megakernel with a shared-memory path pool and material-binned queues.
+//
+// Replaces Kernel.cu:102-158 + color() :30-80 like the other two variants, with the schedule that the ncu evidence asks for:
+//   * k_render_mega (one thread = one pixel) runs its node loop with ~12-17 of 32 lanes: a warp waits for its longest
+//     traversal and for its longest path (profiles/r01_a);
+//   * the HBM wavefront (wavefront.cuh) fixes that with per-lane refill, but pays a kernel ramp/drain per bounce, L2 latency
+//     on every refill and ~160 B of queue traffic per ray (profiles/r01_b).
+// Here ONE CTA of 1024 threads per SM keeps N path slots in SHARED memory (SoA float4) together with the scene, and seven
+// ring queues of slot ids: EXT (rays waiting for a closest-hit query), one queue per shading class (miss, Lambertian, metal,
+// dielectric, light) and GEN (finished slots waiting for a new (pixel, sample) work item). Every warp alternates between
+//   - extend: lanes pop rays from EXT individually as they go idle (ballot/popc + one CAS per warp), traverse, and push the
+//     finished ray into the queue of the material it hit — rays are BINNED BY MATERIAL on the way out;
+//   - shade: when a class queue holds a full warp of rays, the warp pops 32 of them and shades them with uniform control
+//     flow, accumulates finished paths (order-free integer atomics), and pushes survivors back to EXT / finished slots to GEN;
+//   - generate: pops 32 free slots, claims 32 work items with one atomic on a sharded global counter, starts camera paths.
+// Nothing leaves the SM except the accumulation atomics and one work-counter atomic per 32 paths.
+// The per-sample arithmetic is gen_primary()/scatter_step() of kernels.cuh, so the buffer is bit-identical to the other variants.
+#pragma once
+
+#include "wavefront.cuh"
+
+#define PIPE_THREADS 1024
+#define PIPE_WARPS (PIPE_THREADS / 32)
+#define PIPE_EMPTY (-1)
+
+enum { PQ_EXT = 0, PQ_MISS = 1, PQ_LAMBERTIAN = 2, PQ_METAL = 3, PQ_DIELECTRIC = 4, PQ_LIGHT = 5, PQ_GEN = 6, PQ_COUNT = 7 };
+
+struct PipeArgs
+{
+    RenderArgs R;
+    WfShard* shards;         // WF_SHARDS global work counters over the (pixel, sample) items of this launch
+    DevCounters* stat;       // CRT_COUNTER_SHARDS ray/path counters
+    uint32_t n_pixels_cover; // work item w -> sample w / n_pixels_cover, pixel w % n_pixels_cover
+    int n_slots;             // N, a power of two
+    int max_rounds;          // traversal rounds between two refills at most
+    int check_every;         // a warp looks for shade/generate work every check_every-th iteration
+};
+
+// Control words of the queues (static shared memory). head/tail count reservations and never wrap in practice
+// (32-bit, one increment per queue operation of one CTA).
+struct PipeCtl
+{
+    unsigned int head[PQ_COUNT + 1];
+    unsigned int tail[PQ_COUNT + 1];
+    int live; // slots not yet retired; the CTA exits at 0
+};
+
+struct PipePool
+{
+    float4* a; // {o.x, o.y, o.z, d.x}
+    float4* b; // {d.y, d.z, t_hit, leaf code (int bits)}
+    float4* c; // {throughput rgb, bounce (uint bits)}
+    uint2* px; // {pixel, sample}
+    int* ring; // PQ_COUNT rings of n_slots entries
+    unsigned int mask;
+    int n;
+};
+
+__device__ __forceinline__ volatile int* pipe_entry(const PipePool& P, int q, unsigned int pos)
+{
+    return (volatile int*)(P.ring + q * P.n + (int)(pos & P.mask));
+}
+
+// Warp-aggregated push of `slot` (where pred) into queue q. The pool writes of the pushing lanes must be complete.
+__device__ __forceinline__ void pipe_push(const PipePool& P, PipeCtl* ctl, int q, bool pred, int slot, unsigned lane_lt)
+{
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0u) return;
+    unsigned int base = 0;
+    const int leader = __ffs(m) - 1;
+    if ((int)(threadIdx.x & 31u) == leader) base = atomicAdd(&ctl->tail[q], (unsigned int)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (pred) *pipe_entry(P, q, base + __popc(m & lane_lt)) = slot;
+}
+
+// Push where every pushing lane names its own queue: lanes are grouped with match.any, one atomic per distinct queue.
+__device__ __forceinline__ void pipe_push_binned(const PipePool& P, PipeCtl* ctl, int q, bool pred, int slot, unsigned lane_lt)
+{
+    const unsigned grp = __match_any_sync(0xffffffffu, pred ? q : -1); // lanes with the same destination
+    if (!__any_sync(0xffffffffu, pred)) return;
+    const int leader = __ffs(grp) - 1;
+    unsigned int base = 0;
+    if (pred && (int)(threadIdx.x & 31u) == leader) base = atomicAdd(&ctl->tail[q], (unsigned int)__popc(grp));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (pred) *pipe_entry(P, q, base + __popc(grp & lane_lt)) = slot;
+}
+
+// Orders this thread's shared-memory pool writes before its queue write. Shared-memory accesses of one thread are performed
+// in program order by the SM, so only the compiler has to be kept from reordering them.
+__device__ __forceinline__ void pipe_release() { asm volatile("" ::: "memory"); }
+
+// Warp-level pop of up to `want` entries of queue q (never more than are reserved by producers). Returns the count n and
+// gives lanes with rank < n their slot id. One CAS per call; a lost race returns 0 and the caller simply tries again later.
+__device__ __forceinline__ int pipe_pop(const PipePool& P, PipeCtl* ctl, int q, int want, int rank, bool take, int& slot)
+{
+    unsigned int h = 0;
+    int n = 0;
+    if ((threadIdx.x & 31u) == 0u) {
+        h = *(volatile unsigned int*)&ctl->head[q];
+        const unsigned int t = *(volatile unsigned int*)&ctl->tail[q];
+        n = min(want, (int)(t - h));
+        if (n > 0 && atomicCAS(&ctl->head[q], h, h + (unsigned int)n) != h) n = 0;
+    }
+    h = __shfl_sync(0xffffffffu, h, 0);
+    n = __shfl_sync(0xffffffffu, n, 0);
+    if (take && rank < n) {
+        volatile int* e = pipe_entry(P, q, h + (unsigned int)rank);
+        int v;
+        while ((v = *e) == PIPE_EMPTY) { } // the producer reserved this entry before us; its store is in flight
+        *e = PIPE_EMPTY;
+        slot = v;
+    }
+    return n;
+}
+
+__device__ __forceinline__ void pipe_item(const PipeArgs& A, uint32_t w, int& x, int& y, uint32_t& pixel, uint32_t& sample)
+{
+    const uint32_t s = w / A.n_pixels_cover, q = w - s * A.n_pixels_cover;
+    y = (int)(q / A.R.cover_w);
+    x = (int)(q - (uint32_t)y * A.R.cover_w);
+    pixel = (uint32_t)y * A.R.width + (uint32_t)x;
+    sample = A.R.spp_begin + s * A.R.spp_stride;
+}
+
+// Claims up to `need` consecutive work items from the sharded global counters (one atomic). Warp-uniform result.
+// `exhausted` becomes true (and stays true) once a scan over every shard found nothing.
+__device__ __forceinline__ int pipe_claim(const PipeArgs& A, int need, unsigned int& shard_cursor, bool& exhausted, uint32_t& base)
+{
+    int g = 0;
+    uint32_t wb = 0;
+    unsigned int sc = shard_cursor;
+    if ((threadIdx.x & 31u) == 0u && !exhausted) {
+        for (int k = 0; k < WF_SHARDS; k++) {
+            WfShard* sh = &A.shards[(sc + (unsigned)k) & (WF_SHARDS - 1)];
+            const unsigned int end = sh->end;
+            if (*(volatile unsigned int*)&sh->head < end) {
+                const unsigned int b = atomicAdd(&sh->head, (unsigned int)need);
+                if (b < end) {
+                    g = (int)min((unsigned int)need, end - b);
+                    wb = b;
+                    sc = (sc + (unsigned)k) & (WF_SHARDS - 1);
+                    break;
+                }
+            }
+        }
+    }
+    g = __shfl_sync(0xffffffffu, g, 0);
+    base = __shfl_sync(0xffffffffu, wb, 0);
+    shard_cursor = __shfl_sync(0xffffffffu, sc, 0);
+    if (g == 0) exhausted = true;
+    return g;
+}
+
+template <bool SMEM_ALL> __device__ __forceinline__ uint32_t pipe_mat_bits(const SceneView& S, int i)
+{
+    if (SMEM_ALL || i < S.smem_mats) return __float_as_uint(S.s_mats[2 * i + 1].w);
+    return __float_as_uint(__ldg(S.g_mats + 2 * (size_t)i + 1).w);
+}
+
+// One batch of queue q (n <= 32 slots, lane < n holds `slot`): generate, or shade one bounce.
+template <bool SMEM_ALL>
+__device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S, const PipePool& P, PipeCtl* ctl, int q, int n, int slot,
+                                           unsigned lane, unsigned lt, unsigned int& shard_cursor, bool& exhausted, unsigned& n_rays,
+                                           unsigned& n_paths)
+{
+    const bool mine = (int)lane < n;
+    if (q == PQ_GEN) {
+        int done = 0;
+        bool started = false;
+        while (done < n) {
+            uint32_t base;
+            const int g = pipe_claim(A, n - done, shard_cursor, exhausted, base);
+            if (g == 0) break;
+            if (mine && (int)lane >= done && (int)lane < done + g) {
+                int x, y;
+                uint32_t pixel, sample;
+                pipe_item(A, base + (uint32_t)((int)lane - done), x, y, pixel, sample);
+                float3 o, d;
+                gen_primary<false>(A.R, x, y, pixel, sample, o, d);
+                P.a[slot] = make_float4(o.x, o.y, o.z, d.x);
+                P.b[slot] = make_float4(d.y, d.z, 0.f, 0.f);
+                P.c[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(0u));
+                P.px[slot] = make_uint2(pixel, sample);
+                n_paths++;
+                started = true;
+            }
+            done += g;
+        }
+        if (lane == 0 && done < n) atomicSub(&ctl->live, n - done); // no work left: these slots retire
+        pipe_release();
+        pipe_push(P, ctl, PQ_EXT, started, slot, lt);
+        return;
+    }
+    bool alive = false, ended = false;
+    if (mine) {
+        const float4 a0 = P.a[slot], b0 = P.b[slot], c0 = P.c[slot];
+        const uint2 ps = P.px[slot];
+        float3 o = f3(a0.x, a0.y, a0.z), d = f3(a0.w, b0.x, b0.y), thr = f3(c0.x, c0.y, c0.z), add;
+        uint32_t bounce = __float_as_uint(c0.w);
+        Hit h;
+        h.t = b0.z;
+        h.leaf = __float_as_int(b0.w);
+        n_rays++;
+        alive = scatter_step<SMEM_ALL>(A.R, S, h, ps.x, ps.y, bounce, o, d, thr, add);
+        if (alive) {
+            P.a[slot] = make_float4(o.x, o.y, o.z, d.x);
+            P.b[slot] = make_float4(d.y, d.z, 0.f, 0.f);
+            P.c[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(bounce));
+        }
+        else { // accumulate: order-free integer atomics, fire-and-forget
+            unsigned long long* px = reinterpret_cast<unsigned long long*>(A.R.accum + 4 * (size_t)ps.x);
+            atomicAdd(px + 0, (unsigned long long)crt_to_fixed(add.x));
+            atomicAdd(px + 1, (unsigned long long)crt_to_fixed(add.y));
+            atomicAdd(px + 2, (unsigned long long)crt_to_fixed(add.z));
+            ended = true;
+        }
+    }
+    pipe_release();
+    pipe_push(P, ctl, PQ_EXT, alive, slot, lt);
+    pipe_push(P, ctl, PQ_GEN, ended, slot, lt);
+}
+
+template <int THRESH, bool SMEM_ALL>
+__global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_constant__ PipeArgs A)
+{
+    extern __shared__ float4 smem[];
+    __shared__ PipeCtl ctl;
+    const SceneView S = stage_scene(A.R.scene, smem);
+    PipePool P;
+    {
+        float4* p = smem + 4 * (size_t)A.R.scene.smem_nodes + A.R.scene.smem_prims + 2 * (size_t)A.R.scene.smem_mats;
+        P.n = A.n_slots;
+        P.mask = (unsigned int)A.n_slots - 1u;
+        P.a = p; p += P.n;
+        P.b = p; p += P.n;
+        P.c = p; p += P.n;
+        P.px = reinterpret_cast<uint2*>(p); p += P.n / 2;
+        P.ring = reinterpret_cast<int*>(p);
+    }
+    for (int i = threadIdx.x; i < PQ_COUNT * P.n; i += PIPE_THREADS) P.ring[i] = i >= PQ_GEN * P.n ? i - PQ_GEN * P.n : PIPE_EMPTY;
+    if (threadIdx.x <= PQ_COUNT) { ctl.head[threadIdx.x] = 0u; ctl.tail[threadIdx.x] = threadIdx.x == PQ_GEN ? (unsigned int)P.n : 0u; }
+    if (threadIdx.x == 0) ctl.live = P.n; // every slot starts in the GEN queue
+    __syncthreads();
+
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, lt = (1u << lane) - 1u;
+    const float t_min = 0.001f;
+    int slot = -1, cur = CRT_TRAV_DONE, sp = 0;
+    TravRay r = trav_setup<false>(f3(0.f, 0.f, 0.f), f3(0.f, 0.f, 1.f));
+    Hit h;
+    h.t = 0.f;
+    h.leaf = -1;
+    int stack[CRT_STACK_SIZE];
+    unsigned n_rays = 0, n_paths = 0;
+    unsigned int shard_cursor = (blockIdx.x * PIPE_WARPS + warp) & (WF_SHARDS - 1);
+    bool exhausted = false;
+
+    bool refill_short = true;
+    for (unsigned it = 0; *(volatile int*)&ctl.live > 0; it++) {
+        const unsigned act0 = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
+        bool worked = false;
+        // ---- shade / generate duty: lanes 1..6 each look at one queue. With 32 warps looking, every A.check_every-th
+        //      iteration of a warp is enough to keep the class queues short; a warp that could not refill looks at once ----
+        if (refill_short || (it % (unsigned)A.check_every) == 0u) {
+            int sz = 0;
+            if (lane < PQ_COUNT) sz = (int)(*(volatile unsigned int*)&ctl.tail[lane] - *(volatile unsigned int*)&ctl.head[lane]);
+            const unsigned full_q = __ballot_sync(0xffffffffu, lane >= 1u && sz >= 32);
+            const unsigned some_q = __ballot_sync(0xffffffffu, lane >= 1u && sz > 0);
+            const int ext_sz = __shfl_sync(0xffffffffu, sz, 0);
+            int q = -1;
+            if (full_q) {
+                // rotate the starting queue with the warp id so that the warps do not all go for the same one
+                const unsigned rot = 1u + (warp % (PQ_COUNT - 1));
+                const unsigned hi = full_q >> rot << rot;
+                q = __ffs(hi ? hi : full_q) - 1;
+            }
+            else if (some_q && act0 == 0u && ext_sz <= 0) {
+                q = __ffs(some_q) - 1; // starving: nothing to traverse, so a partial batch is better than waiting
+            }
+            if (q >= 0) {
+                int s2 = -1;
+                const int n = pipe_pop(P, &ctl, q, 32, (int)lane, true, s2);
+                if (n > 0) {
+                    pipe_batch<SMEM_ALL>(A, S, P, &ctl, q, n, s2, lane, lt, shard_cursor, exhausted, n_rays, n_paths);
+                    worked = true;
+                    // Lanes in mid-traversal kept only {slot, cur, sp, t, leaf} across the batch: rebuild the per-ray constants.
+                    const int si = max(slot, 0);
+                    const float4 a0 = P.a[si], b0 = P.b[si];
+                    r = trav_setup<false>(f3(a0.x, a0.y, a0.z), f3(a0.w, b0.x, b0.y));
+                }
+            }
+        }
+        // ---- extend: refill idle lanes from EXT ----
+        bool idle = cur == CRT_TRAV_DONE;
+        unsigned m = __ballot_sync(0xffffffffu, idle);
+        refill_short = false;
+        if (m != 0u) {
+            int s2 = -1;
+            const int rank = __popc(m & lt);
+            const int n = pipe_pop(P, &ctl, PQ_EXT, __popc(m), rank, idle, s2);
+            if (idle && rank < n) {
+                slot = s2;
+                const float4 a0 = P.a[slot], b0 = P.b[slot];
+                r = trav_setup<false>(f3(a0.x, a0.y, a0.z), f3(a0.w, b0.x, b0.y));
+                h.t = 3.402823466e+38f;
+                h.leaf = -1;
+                cur = 0;
+                sp = 0;
+            }
+            refill_short = n < __popc(m);
+        }
+        unsigned act = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
+        if (act == 0u) {
+            if (!worked) __nanosleep(100);
+            continue;
+        }
+        // ---- traverse: until fewer than THRESH lanes are busy (a refill is due) or it is time to look at the queues ----
+        const int leave_below = refill_short ? 1 : THRESH; // EXT ran dry: leaving early would only spin
+        int rounds = 0;
+        do {
+            if (cur >= 0) node_step<false, SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
+            if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
+            act = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
+            rounds++;
+        } while (__popc(act) >= leave_below && rounds < A.max_rounds);
+            // ---- finished lanes: store the hit, push the slot into the queue of what it hit ----
+        const bool fin = cur == CRT_TRAV_DONE && slot >= 0;
+        {
+            // the leaf code carries the material type of what was hit (crt_internal.h): no load needed to bin the ray
+            const int cls = h.leaf < 0 ? PQ_MISS : PQ_LAMBERTIAN + ((h.leaf >> CRT_LEAF_MAT_SHIFT) & 3);
+            if (fin) reinterpret_cast<float2*>(P.b + slot)[1] = make_float2(h.t, __int_as_float(h.leaf));
+            pipe_release();
+            pipe_push_binned(P, &ctl, cls, fin, slot, lt);
+            if (fin) slot = -1;
+        }
+    }
+    // ray / path counters: block-aggregated into one of the counter shards
+    flush_counters(A.stat, n_paths, n_rays, 0u, 0u, false);
+}

@@ -213,7 +213,7 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
         return false;
     }
     if (sd->n_hittables > (uint64_t)CRT_LEAF_INDEX_MASK) {
-        *err = "scene: too many hittables (limit 2^28 - 1)";
+        *err = "scene: too many hittables (limit 2^26 - 1)";
         return false;
     }
     // 1. active filter + validation
@@ -369,7 +369,8 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
                 store_box(pn.w, c, B.pbox[k], false, abs_pad);
                 if (root_area > 0.f)
                     sah += 1.0 * B.pbox[k].half_area() / root_area;
-                pn.child[c] = ~(int32_t)(((uint32_t)h.type << CRT_LEAF_TYPE_SHIFT) | slot);
+                pn.child[c] = ~(int32_t)(((uint32_t)h.type << CRT_LEAF_TYPE_SHIFT) |
+                                         ((uint32_t)sd->materials[h.material].type << CRT_LEAF_MAT_SHIFT) | slot);
                 float* pr = &out->prims[4 * (size_t)slot];
                 float hw = h.a / 2, hh = h.b / 2;
                 switch (h.type) {

@@ -42,11 +42,11 @@ __device__ __forceinline__ void camera_ray(const DevCamera& C, uint32_t width, u
         float inv_w = fast_rcp(fw);
         float u = (((float)x - cx) + j1) * inv_w;
         float v = ((cy - (float)y) + j2) * inv_w;
-        float3 dist = f3(u * C.rx + v * C.ux, u * C.ry + v * C.uy, u * C.rz + v * C.uz);
-        float3 start = f3(C.near_plane * dist.x + C.ox + C.fov * C.fx, C.near_plane * dist.y + C.oy + C.fov * C.fy,
-                          C.near_plane * dist.z + C.oz + C.fov * C.fz);
-        float3 second = f3(C.far_plane * dist.x + C.far_k * C.fx + C.ox, C.far_plane * dist.y + C.far_k * C.fy + C.oy,
-                           C.far_plane * dist.z + C.far_k * C.fz + C.oz);
+        float3 dist = f3(fmaf(u, C.rx, v * C.ux), fmaf(u, C.ry, v * C.uy), fmaf(u, C.rz, v * C.uz));
+        float3 start = f3(fmaf(C.fov, C.fx, fmaf(C.near_plane, dist.x, C.ox)), fmaf(C.fov, C.fy, fmaf(C.near_plane, dist.y, C.oy)),
+                          fmaf(C.fov, C.fz, fmaf(C.near_plane, dist.z, C.oz)));
+        float3 second = f3(fmaf(C.far_plane, dist.x, fmaf(C.far_k, C.fx, C.ox)), fmaf(C.far_plane, dist.y, fmaf(C.far_k, C.fy, C.oy)),
+                           fmaf(C.far_plane, dist.z, fmaf(C.far_k, C.fz, C.oz)));
         float3 dv = second - start;
         float inv = rsqrtf(dot3(dv, dv));
         origin = start;
@@ -63,9 +63,9 @@ __device__ __forceinline__ void apply_lens(const DevCamera& C, float l1, float l
     float s, c;
     __sincosf(2.0f * CRT_PI * l2, &s, &c);
     float3 right = f3(C.rx, C.ry, C.rz), up = f3(C.ux, C.uy, C.uz), fwd = f3(C.fx, C.fy, C.fz);
-    float3 off = (r * c) * right + (r * s) * up;
+    float3 off = madd3(r * c, right, (r * s) * up);
     float tf = fast_div(C.focus_dist, dot3(dir, fwd));
-    float3 focus = origin + tf * dir;
+    float3 focus = madd3(tf, dir, origin);
     origin = origin + off;
     float3 dv = focus - origin;
     dir = rsqrtf(dot3(dv, dv)) * dv;
@@ -75,8 +75,8 @@ __device__ __forceinline__ void apply_lens(const DevCamera& C, float l1, float l
 // loop (Math.cuh:252-260), fixed cost, no divergence.
 __device__ __forceinline__ float3 ball_sample(float u0, float u1, float u2)
 {
-    float z = 1.0f - 2.0f * u0;
-    float s = fast_sqrt(fmaxf(0.0f, 1.0f - z * z));
+    float z = fmaf(-2.0f, u0, 1.0f);
+    float s = fast_sqrt(fmaxf(0.0f, fmaf(-z, z, 1.0f)));
     float sn, cs;
     __sincosf(2.0f * CRT_PI * u1, &sn, &cs);
     float r = exp2f(__log2f(u2) * (1.0f / 3.0f)); // u2^(1/3): MUFU.LG2 + MUFU.EX2 (u2 in (0,1], so log2 is finite)
@@ -106,7 +106,7 @@ __device__ __forceinline__ float3 background(const DevCamera& C, float3 d)
     float uy = d.y * rsqrtf(dot3(d, d));
     float t = 0.5f * (uy + 1.0f);
     float s = 1.0f - t;
-    return f3(s * C.bg0[0] + t * C.bg1[0], s * C.bg0[1] + t * C.bg1[1], s * C.bg0[2] + t * C.bg1[2]);
+    return f3(fmaf(s, C.bg0[0], t * C.bg1[0]), fmaf(s, C.bg0[1], t * C.bg1[1]), fmaf(s, C.bg0[2], t * C.bg1[2]));
 }
 
 // One surface interaction. In: ray (o, d), hit (t, leaf code), four uniforms. Out: scattered ray in (o, d),
@@ -116,13 +116,13 @@ template <bool SMEM_ALL>
 __device__ __forceinline__ bool shade_hit(const SceneView& S, Hit h, float3& o, float3& d, float3& thr, float3& emitted, float4 xi)
 {
     const int slot = h.leaf & CRT_LEAF_INDEX_MASK;
-    const int type = h.leaf >> CRT_LEAF_TYPE_SHIFT;
+    const int type = (h.leaf >> CRT_LEAF_TYPE_SHIFT) & 3;
     float4 m0, m1;
     load_mat<SMEM_ALL>(S, slot, m0, m1);
     const uint32_t bits = __float_as_uint(m1.w);
     const int mat_type = bits & 15, tex_type = (bits >> 4) & 15, image_plus1 = bits >> 8;
 
-    float3 p = o + h.t * d; // Ray::PointAtParameter
+    float3 p = madd3(h.t, d, o); // Ray::PointAtParameter
     float3 n;
     float tu = 0.f, tv = 0.f;
     float4 pr = load_prim<SMEM_ALL>(S, slot);
@@ -166,10 +166,10 @@ __device__ __forceinline__ bool shade_hit(const SceneView& S, Hit h, float3& o, 
     }
     if (mat_type == CRT_METAL) {
         float3 ud = rsqrtf(dot3(d, d)) * d;
-        float3 refl = ud - (2.0f * dot3(ud, n)) * n;
+        float3 refl = madd3(-2.0f * dot3(ud, n), n, ud);
         float fuzz = m0.w;
         float3 nd = refl;
-        if (fuzz > 0.f) nd = refl + fuzz * ball_sample(xi.x, xi.y, xi.z);
+        if (fuzz > 0.f) nd = madd3(fuzz, ball_sample(xi.x, xi.y, xi.z), refl);
         o = p;
         d = nd;
         thr = albedo * thr;
@@ -179,14 +179,14 @@ __device__ __forceinline__ bool shade_hit(const SceneView& S, Hit h, float3& o, 
         const float ir = m0.w;
         float dn = dot3(d, n);
         float inv_len = rsqrtf(dot3(d, d));
-        float3 refl = d - (2.0f * dn) * n; // Reflect of the UN-normalised direction
+        float3 refl = madd3(-2.0f * dn, n, d); // Reflect of the UN-normalised direction
         float3 outn;
         float ratio, cosine;
         if (dn > 0.f) {
             outn = -n;
             ratio = ir;
             cosine = dn * inv_len;
-            cosine = fast_sqrt(1.0f - ir * ir * (1.0f - cosine * cosine)); // NaN when negative: only used if Refract succeeds
+            cosine = fast_sqrt(fmaf(-(ir * ir), fmaf(-cosine, cosine, 1.0f), 1.0f)); // NaN when negative: only used if Refract succeeds
         }
         else {
             outn = n;
@@ -196,16 +196,16 @@ __device__ __forceinline__ bool shade_hit(const SceneView& S, Hit h, float3& o, 
         // Refract, Math.cuh:292-304
         float3 uv = inv_len * d;
         float dt = dot3(uv, outn);
-        float disc = 1.0f - ratio * ratio * (1.0f - dt * dt);
+        float disc = fmaf(-(ratio * ratio), fmaf(-dt, dt, 1.0f), 1.0f);
         float prob = 1.0f;
         float3 refr = refl;
         if (disc > 0.f) {
-            refr = ratio * (uv - dt * outn) - fast_sqrt(disc) * outn;
+            refr = madd3(-fast_sqrt(disc), outn, ratio * madd3(-dt, outn, uv));
             float r0 = fast_div(1.0f - ir, 1.0f + ir);
             r0 = r0 * r0;
             float c1 = 1.0f - cosine;
             float c2 = c1 * c1;
-            prob = r0 + (1.0f - r0) * (c2 * c2 * c1); // pow(1 - cosine, 5)
+            prob = fmaf(1.0f - r0, c2 * c2 * c1, r0); // pow(1 - cosine, 5)
         }
         o = p;
         d = (xi.w < prob) ? refl : refr;

@@ -80,9 +80,6 @@ __device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem
 }
 
 #define CRT_TRAV_DONE ((int)0x80000000)
-#ifndef CRT_TRAV_STYLE
-#define CRT_TRAV_STYLE 0
-#endif
 
 struct Hit
 {
@@ -111,8 +108,8 @@ __device__ __forceinline__ bool sphere_test(float4 sph, float3 o, float3 d, floa
     else {
         float3 oc = o - f3(sph.x, sph.y, sph.z);
         float b = dot3(oc, d);
-        float c = dot3(oc, oc) - sph.w * sph.w;
-        float disc = b * b - a * c;
+        float c = fmaf(-sph.w, sph.w, dot3(oc, oc));
+        float disc = fmaf(-a, c, b * b);
         if (disc > 0.f) {
             float sq = fast_sqrt(disc);
             float t = (-b - sq) * inv_a;
@@ -142,8 +139,8 @@ __device__ __forceinline__ bool rect_test(float4 r, float k, float oa, float ob,
         float inv = fast_rcp(dk);
         t = (k - ok) * inv;
         if (t < t_min || t > t_max) return false;
-        pa = oa + t * da;
-        pb = ob + t * db;
+        pa = fmaf(t, da, oa);
+        pb = fmaf(t, db, ob);
     }
     if (pa < r.x || pa > r.y || pb < r.z || pb > r.w) return false;
     t_out = t;
@@ -155,7 +152,7 @@ __device__ __forceinline__ bool leaf_test(const SceneView& S, int code, float3 o
                                           float t_max, float& t_out)
 {
     const int slot = code & CRT_LEAF_INDEX_MASK;
-    const int type = code >> CRT_LEAF_TYPE_SHIFT;
+    const int type = (code >> CRT_LEAF_TYPE_SHIFT) & 3;
     float4 p = load_prim<SMEM_ALL>(S, slot);
     if (type == CRT_SPHERE)
         return sphere_test<EXACT>(p, o, d, a, inv_a, t_min, t_max, t_out);
@@ -163,6 +160,91 @@ __device__ __forceinline__ bool leaf_test(const SceneView& S, int code, float3 o
     if (type == CRT_XYRECT) return rect_test<EXACT>(p, k, o.x, o.y, o.z, d.x, d.y, d.z, t_min, t_max, t_out);
     if (type == CRT_XZRECT) return rect_test<EXACT>(p, k, o.x, o.z, o.y, d.x, d.z, d.y, t_min, t_max, t_out);
     return rect_test<EXACT>(p, k, o.y, o.z, o.x, d.y, d.z, d.x, t_min, t_max, t_out);
+}
+
+// Per-ray constants of a closest-hit query.
+struct TravRay
+{
+    float3 o, d;
+    float3 id;   // reciprocal direction (components clamped away from zero so that 0 * inf never appears)
+    float3 ood;  // o * id, fast path only: the slab test becomes one FFMA per plane
+    float a;     // Dot(dir, dir), Hittable.cuh:83
+    float inv_a; // fast path only
+};
+
+template <bool EXACT> __device__ __forceinline__ TravRay trav_setup(float3 o, float3 d)
+{
+    TravRay r;
+    r.o = o;
+    r.d = d;
+    const float tiny = 1e-18f;
+    float3 dc = f3(fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x, fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y,
+                   fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
+    if (!EXACT) dc = f3(fabsf(d.x) < tiny ? tiny : d.x, fabsf(d.y) < tiny ? tiny : d.y, fabsf(d.z) < tiny ? tiny : d.z);
+    if (EXACT) {
+        r.a = dot3_rn(d, d);
+        r.inv_a = 0.f;
+        r.id = f3(div_rn(1.0f, dc.x), div_rn(1.0f, dc.y), div_rn(1.0f, dc.z));
+        r.ood = f3(0.f, 0.f, 0.f);
+    }
+    else {
+        r.a = dot3(d, d);
+        r.inv_a = fast_rcp(r.a);
+        r.id = f3(fast_rcp(dc.x), fast_rcp(dc.y), fast_rcp(dc.z));
+        r.ood = f3(o.x * r.id.x, o.y * r.id.y, o.z * r.id.z);
+    }
+    return r;
+}
+
+// One inner-node visit: slab-test both child boxes against (t_min, t_hit), descend into the nearer hit child and push the
+// other. `cur` >= 0 on entry; on exit it is the next node (>= 0), a leaf (~code, < 0) or CRT_TRAV_DONE.
+template <bool EXACT, bool SMEM_ALL>
+__device__ __forceinline__ void node_step(const SceneView& S, const TravRay& r, float t_min, float t_hit, int& cur, int& sp, int* stack)
+{
+    float4 w0, w1, w2;
+    int2 ch;
+    load_node<SMEM_ALL>(S, cur, w0, w1, w2, ch);
+    float lx0, ly0, lz0, hx0, hy0, hz0, lx1, ly1, lz1, hx1, hy1, hz1;
+    if (EXACT) {
+        lx0 = (w0.x - r.o.x) * r.id.x; ly0 = (w0.y - r.o.y) * r.id.y; lz0 = (w0.z - r.o.z) * r.id.z;
+        hx0 = (w0.w - r.o.x) * r.id.x; hy0 = (w1.x - r.o.y) * r.id.y; hz0 = (w1.y - r.o.z) * r.id.z;
+        lx1 = (w1.z - r.o.x) * r.id.x; ly1 = (w1.w - r.o.y) * r.id.y; lz1 = (w2.x - r.o.z) * r.id.z;
+        hx1 = (w2.y - r.o.x) * r.id.x; hy1 = (w2.z - r.o.y) * r.id.y; hz1 = (w2.w - r.o.z) * r.id.z;
+    }
+    else {
+        lx0 = fmaf(w0.x, r.id.x, -r.ood.x); ly0 = fmaf(w0.y, r.id.y, -r.ood.y); lz0 = fmaf(w0.z, r.id.z, -r.ood.z);
+        hx0 = fmaf(w0.w, r.id.x, -r.ood.x); hy0 = fmaf(w1.x, r.id.y, -r.ood.y); hz0 = fmaf(w1.y, r.id.z, -r.ood.z);
+        lx1 = fmaf(w1.z, r.id.x, -r.ood.x); ly1 = fmaf(w1.w, r.id.y, -r.ood.y); lz1 = fmaf(w2.x, r.id.z, -r.ood.z);
+        hx1 = fmaf(w2.y, r.id.x, -r.ood.x); hy1 = fmaf(w2.z, r.id.y, -r.ood.y); hz1 = fmaf(w2.w, r.id.z, -r.ood.z);
+    }
+    const float tn0 = fmaxf(fmaxf(fminf(lx0, hx0), fminf(ly0, hy0)), fmaxf(fminf(lz0, hz0), t_min));
+    const float tf0 = fminf(fminf(fmaxf(lx0, hx0), fmaxf(ly0, hy0)), fminf(fmaxf(lz0, hz0), t_hit));
+    const float tn1 = fmaxf(fmaxf(fminf(lx1, hx1), fminf(ly1, hy1)), fmaxf(fminf(lz1, hz1), t_min));
+    const float tf1 = fminf(fminf(fmaxf(lx1, hx1), fmaxf(ly1, hy1)), fminf(fmaxf(lz1, hz1), t_hit));
+    // The boxes are padded on the host (scene_pack.cpp); <= keeps degenerate (flat) boxes alive.
+    const bool h0 = tn0 <= tf0;
+    const bool h1 = tn1 <= tf1;
+    if (h0 && h1) {
+        const bool swap = tn1 < tn0;
+        cur = swap ? ch.y : ch.x;
+        stack[sp++] = swap ? ch.x : ch.y;
+    }
+    else if (h0) cur = ch.x;
+    else if (h1) cur = ch.y;
+    else cur = sp ? stack[--sp] : CRT_TRAV_DONE;
+}
+
+// One leaf visit: test the primitive, shrink the hit distance, pop. `cur` < 0 and != CRT_TRAV_DONE on entry.
+template <bool EXACT, bool SMEM_ALL>
+__device__ __forceinline__ void leaf_step(const SceneView& S, const TravRay& r, float t_min, Hit& h, int& cur, int& sp, const int* stack)
+{
+    const int code = ~cur;
+    float t;
+    if (leaf_test<EXACT, SMEM_ALL>(S, code, r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) {
+        h.t = t;
+        h.leaf = code;
+    }
+    cur = sp ? stack[--sp] : CRT_TRAV_DONE;
 }
 
 // Closest hit in (t_min, t_max). Near-first ordered descent with a per-thread stack.
@@ -173,86 +255,18 @@ __device__ __forceinline__ Hit closest_hit(const SceneView& S, float3 o, float3 
     Hit h;
     h.t = t_max;
     h.leaf = -1;
-
-    // a = Dot(dir, dir), Hittable.cuh:83
-    float a, inv_a;
-    if (EXACT) { a = dot3_rn(d, d); inv_a = 0.f; }
-    else { a = dot3(d, d); inv_a = fast_rcp(a); }
-
-    // Reciprocal direction for the slab test. |d| is clamped away from zero so that 0 * inf never appears.
-    const float tiny = 1e-18f;
-    float3 dc = f3(fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x, fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y,
-                   fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
-    float3 id, ood;
-    if (EXACT) {
-        id = f3(div_rn(1.0f, dc.x), div_rn(1.0f, dc.y), div_rn(1.0f, dc.z));
-        ood = f3(0.f, 0.f, 0.f);
-    }
-    else {
-        id = f3(fast_rcp(dc.x), fast_rcp(dc.y), fast_rcp(dc.z));
-        ood = f3(o.x * id.x, o.y * id.y, o.z * id.z);
-    }
-
+    const TravRay r = trav_setup<EXACT>(o, d);
     int stack[CRT_STACK_SIZE];
     int sp = 0;
     int cur = 0; // >= 0: inner node, < 0: leaf (~code), CRT_TRAV_DONE: finished
-
-#if CRT_TRAV_STYLE == 1
-    // while-while (Aila & Laine 2009): every lane stays in the node loop until it holds a leaf (or is done), then the
-    // warp tests leaves together; ncu r1 showed the interleaved form running its leaf tests with 6 of 32 lanes.
-    while (cur != CRT_TRAV_DONE) {
-        while (cur >= 0) {
-#else
     while (true) {
-        {
-#endif
-            float4 w0, w1, w2;
-            int2 ch;
-            load_node<SMEM_ALL>(S, cur, w0, w1, w2, ch);
-            if (COUNT) n_box += 2;
-
-            float lx0, ly0, lz0, hx0, hy0, hz0, lx1, ly1, lz1, hx1, hy1, hz1;
-            if (EXACT) {
-                lx0 = (w0.x - o.x) * id.x; ly0 = (w0.y - o.y) * id.y; lz0 = (w0.z - o.z) * id.z;
-                hx0 = (w0.w - o.x) * id.x; hy0 = (w1.x - o.y) * id.y; hz0 = (w1.y - o.z) * id.z;
-                lx1 = (w1.z - o.x) * id.x; ly1 = (w1.w - o.y) * id.y; lz1 = (w2.x - o.z) * id.z;
-                hx1 = (w2.y - o.x) * id.x; hy1 = (w2.z - o.y) * id.y; hz1 = (w2.w - o.z) * id.z;
-            }
-            else {
-                lx0 = fmaf(w0.x, id.x, -ood.x); ly0 = fmaf(w0.y, id.y, -ood.y); lz0 = fmaf(w0.z, id.z, -ood.z);
-                hx0 = fmaf(w0.w, id.x, -ood.x); hy0 = fmaf(w1.x, id.y, -ood.y); hz0 = fmaf(w1.y, id.z, -ood.z);
-                lx1 = fmaf(w1.z, id.x, -ood.x); ly1 = fmaf(w1.w, id.y, -ood.y); lz1 = fmaf(w2.x, id.z, -ood.z);
-                hx1 = fmaf(w2.y, id.x, -ood.x); hy1 = fmaf(w2.z, id.y, -ood.y); hz1 = fmaf(w2.w, id.z, -ood.z);
-            }
-            const float tn0 = fmaxf(fmaxf(fminf(lx0, hx0), fminf(ly0, hy0)), fmaxf(fminf(lz0, hz0), t_min));
-            const float tf0 = fminf(fminf(fmaxf(lx0, hx0), fmaxf(ly0, hy0)), fminf(fmaxf(lz0, hz0), h.t));
-            const float tn1 = fmaxf(fmaxf(fminf(lx1, hx1), fminf(ly1, hy1)), fmaxf(fminf(lz1, hz1), t_min));
-            const float tf1 = fminf(fminf(fmaxf(lx1, hx1), fmaxf(ly1, hy1)), fminf(fmaxf(lz1, hz1), h.t));
-            // The boxes are padded on the host (scene_pack.cpp); <= keeps degenerate (flat) boxes alive.
-            const bool h0 = tn0 <= tf0;
-            const bool h1 = tn1 <= tf1;
-            if (h0 && h1) {
-                const bool swap = tn1 < tn0;
-                cur = swap ? ch.y : ch.x;
-                stack[sp++] = swap ? ch.x : ch.y;
-            }
-            else if (h0) cur = ch.x;
-            else if (h1) cur = ch.y;
-            else cur = sp ? stack[--sp] : CRT_TRAV_DONE;
-        }
+        node_step<EXACT, SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
+        if (COUNT) n_box += 2;
         while (cur < 0 && cur != CRT_TRAV_DONE) {
-            const int code = ~cur;
             if (COUNT) n_prim++;
-            float t;
-            if (leaf_test<EXACT, SMEM_ALL>(S, code, o, d, a, inv_a, t_min, h.t, t)) {
-                h.t = t;
-                h.leaf = code;
-            }
-            cur = sp ? stack[--sp] : CRT_TRAV_DONE;
+            leaf_step<EXACT, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
         }
-#if CRT_TRAV_STYLE != 1
         if (cur == CRT_TRAV_DONE) break;
-#endif
     }
     return h;
 }

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CRT_ABI_VERSION 1
+#define CRT_ABI_VERSION 2
 
 typedef enum crt_status {
     CRT_OK = 0,
@@ -95,7 +95,10 @@ typedef struct crt_input_struct {
     float background_end[3];
 } crt_input_struct;
 
-enum { CRT_VARIANT_AUTO = 0, CRT_VARIANT_MEGAKERNEL = 1, CRT_VARIANT_WAVEFRONT = 2 };
+enum { CRT_VARIANT_AUTO = 0,
+       CRT_VARIANT_MEGAKERNEL = 1, /* one thread = one pixel, all samples (the reference's schedule, Kernel.cu:137-148) */
+       CRT_VARIANT_WAVEFRONT = 2,  /* generate -> extend -> shade kernels over an HBM pool of path slots */
+       CRT_VARIANT_PIPELINE = 3 }; /* persistent CTAs: shared-memory path pool, material-binned queues */
 enum { CRT_JITTER_RANDOM = 0,   /* Philox jitter in (0,1], like curand_uniform (Kernel.cu:139-140) */
        CRT_JITTER_CENTER = 1 }; /* xi1 = xi2 = 0.5: RNG-free ray generation for ID parity */
 enum { CRT_FLAG_EXACT_MATH = 1u,      /* IEEE, unfused arithmetic in ray generation + primitive tests */
@@ -154,14 +157,21 @@ crt_status crt_set_camera(crt_context* ctx, const crt_input_struct* inputs);
  * aperture 0 restores the reference camera bit for bit. */
 crt_status crt_set_lens(crt_context* ctx, float aperture, float focus_dist);
 
-/* ---- framebuffer: progressive FP32 accumulation (sum of radiance, RGBA float4 per pixel, .w = sample count) ---- */
+/* ---- framebuffer: progressive accumulation buffer ----
+ * Device layout: four int64 per pixel {R, G, B, samples}; R/G/B are the radiance SUM in Q31.32 fixed point (value * 2^32).
+ * Every FP32 sample is added exactly, and integer addition is associative, so the buffer is bit-identical for any
+ * schedule of the same (pixel, sample) set: megakernel or wavefront, any atomic order, any number of GPUs whose buffers
+ * are summed (NCCL sum over int64). crt_read_accum converts to float4 {sum r, g, b, samples} (one rounding per value). */
 crt_status crt_framebuffer_resize(crt_context* ctx, uint32_t width, uint32_t height); /* also clears */
 crt_status crt_accum_clear(crt_context* ctx);
-/* Use a caller-owned DEVICE buffer of width*height float4 (e.g. a torch tensor that is then NCCL-reduced). NULL = internal. */
-crt_status crt_set_accum_device_buffer(crt_context* ctx, void* device_float4);
+/* Use a caller-owned, 32-byte-aligned DEVICE buffer of width*height*4 int64 (e.g. a torch tensor that is then
+ * NCCL-reduced). NULL = back to the internal buffer. */
+crt_status crt_set_accum_device_buffer(crt_context* ctx, void* device_int64x4);
 void*      crt_accum_device_ptr(crt_context* ctx);
 
-/* ---- render (replaces LaunchKernel, Kernel.cu:102-158,178-191). Asynchronous on the context stream. ---- */
+/* ---- render (replaces LaunchKernel, Kernel.cu:102-158,178-191). The megakernel is asynchronous on the context stream;
+ * the wavefront variant synchronises the stream internally (it reads its active-path count back between batches of
+ * extend/shade iterations). Both variants add the SAME samples: Philox is keyed by (seed; pixel, sample, bounce). ---- */
 crt_status crt_render(crt_context* ctx, const crt_render_params* params);
 /* mean -> 255*sqrt -> clamp -> pack A<<24|B<<16|G<<8|R (Kernel.cu:12-19,151-157). out is HOST memory. Synchronises. */
 crt_status crt_resolve(crt_context* ctx, uint32_t* out_rgba8);

@@ -174,6 +174,11 @@ def test_spp_sharding_reproduces_the_same_samples(renderer):
         total += renderer.read_accum()
     assert (total[..., 3] == 16).all()
     assert np.allclose(total[..., :3], full[..., :3], rtol=1e-5, atol=1e-5)
+    # and adding the shards into ONE buffer (what the NCCL integer sum does) is bit-identical to the single render
+    renderer.clear()
+    for g in range(G):
+        renderer.render(spp=16 // G, max_depth=50, spp_begin=g, spp_stride=G)
+    assert np.array_equal(renderer.read_accum().view(np.uint32), full.astype(np.float32).view(np.uint32))
 
 
 def test_counters(renderer):
@@ -256,3 +261,63 @@ def test_error_behaviour():
     with pytest.raises(CrtError):
         r.upload(bad)
     r.close()
+
+
+# ---- wavefront pipeline: same samples as the megakernel, order-free integer accumulation -> bit-identical buffers ----
+@pytest.mark.parametrize("variant", [capi.VARIANT_WAVEFRONT, capi.VARIANT_PIPELINE], ids=["wavefront", "pipeline"])
+@pytest.mark.parametrize("name,kind,hint,W,H", SCENES)
+def test_variants_bit_identical_to_megakernel(renderer, name, kind, hint, W, H, variant):
+    W, H = W // 2 + 1, H // 2 + 1  # odd sizes
+    s = Scene.generate(kind, 1984, hint)
+    cam = s.default_camera(W, H)
+    _setup(renderer, s, cam, W, H)
+    renderer.reset_counters()
+    renderer.render(spp=6, max_depth=50, variant=capi.VARIANT_MEGAKERNEL)
+    mega = renderer.read_accum()
+    cm = renderer.counters()
+    renderer.clear()
+    renderer.reset_counters()
+    renderer.render(spp=6, max_depth=50, variant=variant)
+    wave = renderer.read_accum()
+    cw = renderer.counters()
+    assert (wave[..., 3] == 6).all()
+    assert cw.paths == cm.paths == W * H * 6 and cw.rays == cm.rays
+    assert np.array_equal(mega.view(np.uint32), wave.view(np.uint32)), \
+        f"{(mega != wave).any(axis=-1).sum()} of {W * H} pixels differ between the variants"
+
+
+@pytest.mark.parametrize("variant", [capi.VARIANT_WAVEFRONT, capi.VARIANT_PIPELINE], ids=["wavefront", "pipeline"])
+def test_small_pool_progressive_and_sharded(monkeypatch, variant):
+    """A pool much smaller than the work (regeneration + drain), progressive calls, and spp sharding: all bit-identical."""
+    monkeypatch.setenv("CRT_WF_SLOTS", "3000")
+    monkeypatch.setenv("CRT_WF_BATCH_ITERS", "4")
+    monkeypatch.setenv("CRT_PIPE_SLOTS", "256")
+    r = Renderer(0)
+    try:
+        s = Scene.generate(capi.SCENE_RTIOW, 1984)
+        W, H = 97, 55
+        cam = s.default_camera(W, H)
+        _setup(r, s, cam, W, H)
+        r.render(spp=8, max_depth=50, variant=capi.VARIANT_MEGAKERNEL)
+        ref = r.read_accum()
+        r.clear()
+        r.render(spp=8, max_depth=50, variant=variant)
+        assert np.array_equal(ref.view(np.uint32), r.read_accum().view(np.uint32))
+        r.clear()
+        r.render(spp=3, max_depth=50, spp_begin=0, variant=variant)
+        r.render(spp=5, max_depth=50, spp_begin=3, variant=capi.VARIANT_MEGAKERNEL)
+        assert np.array_equal(ref.view(np.uint32), r.read_accum().view(np.uint32))
+        r.clear()
+        for g in range(4):  # four "ranks" adding into one buffer == the NCCL integer sum
+            r.render(spp=2, max_depth=50, spp_begin=g, spp_stride=4, variant=variant if g % 2 else capi.VARIANT_MEGAKERNEL)
+        assert np.array_equal(ref.view(np.uint32), r.read_accum().view(np.uint32))
+        # truncated grid + depth 1
+        r.clear()
+        r.render(spp=2, max_depth=1, flags=capi.FLAG_TRUNCATED_GRID, variant=variant)
+        a = r.read_accum()
+        r.clear()
+        r.render(spp=2, max_depth=1, flags=capi.FLAG_TRUNCATED_GRID, variant=capi.VARIANT_MEGAKERNEL)
+        assert np.array_equal(a.view(np.uint32), r.read_accum().view(np.uint32))
+        assert (a[:48, :96, 3] == 2).all() and (a[48:, :, 3] == 0).all() and (a[:, 96:, 3] == 0).all()
+    finally:
+        r.close()
