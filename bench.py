@@ -7,7 +7,8 @@ One "step" = one full render of the workload's frame (all samples per pixel) int
 the RGBA8 resolve. N = 1: workload C2 of BASELINE.json (RTIOW final scene, 1920x1080, 1024 spp, depth 50).
 N > 1 (launched by torchrun, one rank per GPU): samples are sharded over ranks (rank g renders sample indices
 g, g+N, ...; every rank renders `spp` samples, so the frame carries N x spp samples: weak scaling), the per-rank
-FP32 accumulation buffers are summed with ONE NCCL reduce to rank 0 inside the timed region, rank 0 resolves.
+fixed-point (int64) accumulation buffers are summed with ONE NCCL reduce to rank 0 inside the timed region (integer
+addition is order-free, so the N-GPU image is bit-identical to the 1-GPU image of the same samples), rank 0 resolves.
 
 Prints ONE JSON line (rank 0). `value` is device-timed (CUDA events on the stream the kernels run on) with the
 scene resident in HBM; `e2e` goes through the C ABI with HOST buffers (scene upload + BVH build + render + resolve
@@ -185,7 +186,11 @@ def run_gpu_arm(args):
     host_rgba = torch.zeros((H, W), dtype=torch.int32).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2: written between timed steps
     stats = r.bvh_stats()
-    variant = {"auto": capi.VARIANT_AUTO, "mega": capi.VARIANT_MEGAKERNEL, "wavefront": capi.VARIANT_WAVEFRONT}[args.variant]
+    variant = {"auto": capi.VARIANT_AUTO, "mega": capi.VARIANT_MEGAKERNEL, "wavefront": capi.VARIANT_WAVEFRONT,
+               "pipeline": capi.VARIANT_PIPELINE}[args.variant]
+    # what AUTO resolves to (crt_api.cu: pipelined persistent kernel from 256 primitives up, megakernel below)
+    resolved = args.variant if args.variant != "auto" else ("pipeline" if scene.n_hittables >= 256 else "mega")
+    kernel_name = {"mega": "k_render_mega", "wavefront": "k_wf_extend + k_wf_shade", "pipeline": "k_render_pipe"}[resolved]
 
     def device_step():
         """Scene resident in HBM: clear + render this rank's samples (+ reduce) + resolve on rank 0."""
@@ -273,10 +278,21 @@ def run_gpu_arm(args):
         k_ms = r.last_render_ms()
         kc = r.counters()
         achieved = kc.rays * f_ray / (k_ms / 1e3) / 1e12
-        b_ray = 32.0 / (kc.rays / kc.paths) / spp  # megakernel: one float4 read + write per PIXEL per launch
+        # algorithmic DRAM bytes per ray: mega = one 32-byte pixel read + write per launch; pipeline/wavefront = three 8-byte
+        # reductions per finished path into the accumulation buffer (+ wavefront: ~160 B of path state per ray)
+        rpp = kc.rays / kc.paths
+        b_ray = {"mega": 64.0 / rpp / spp, "pipeline": 24.0 / rpp, "wavefront": 24.0 / rpp + 160.0}[resolved]
         hbm_gbs = kc.rays * b_ray / (k_ms / 1e3) / 1e9
+        traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at this config, from the committed ncu capture
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                traffic = json.load(f).get(f"{args.workload}:{resolved}")
+        except Exception:
+            pass
         roofline = {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
-                    "traffic": None, "kernel": "k_render_mega", "kernel_ms": k_ms, "kernel_share_of_step": k_ms / ms_per_step,
+                    "traffic": traffic, "kernel": kernel_name, "kernel_ms": k_ms, "kernel_share_of_step": k_ms / ms_per_step,
+                    "bound_note": "no dense contraction and ~0.1 B/ray of DRAM traffic: neither tensor nor HBM bound; the kernel is "
+                                  "FP32/ALU issue bound (SURVEY.md 8d), the HBM fraction is given beside it",
                     "flop_per_ray": f_ray, "box_tests_per_ray": n_box, "prim_tests_per_ray": n_sph,
                     "peak_source": f"148 SMs x 128 lanes x 2 x {sm_mhz:.0f} MHz (SM clock sampled during the timed region)",
                     "hbm": {"achieved": hbm_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s", "frac": hbm_gbs / peaks.get("hbm_gbs", 6650.0),
@@ -307,8 +323,8 @@ def run_gpu_arm(args):
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
                 "config": {"workload": f"{args.workload}: {desc}", "scene_hittables": scene.n_hittables, "bvh_nodes": int(stats.n_nodes),
-                           "variant": args.variant, "spp_per_rank": spp, "spp_total": spp * world,
-                           "parallelism": f"spp-sharded x{world}" + (", one NCCL reduce of the FP32 accumulation buffer" if world > 1 else ""),
+                           "variant": args.variant, "variant_resolved": resolved, "spp_per_rank": spp, "spp_total": spp * world,
+                           "parallelism": f"spp-sharded x{world}" + (", one NCCL reduce (int64 sum) of the fixed-point accumulation buffer" if world > 1 else ""),
                            "l2": "256 MB buffer written between timed steps (L2 flush)", "rays_per_path": L},
                 "spp_per_s_1080p": (spp * world) / (ms_per_step / 1e3) * (W * H) / (1920 * 1080),
                 "roofline": roofline, "cpu_baseline": cpu,
@@ -331,10 +347,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
-    ap.add_argument("--variant", default="auto", choices=["auto", "mega", "wavefront"])
+    ap.add_argument("--variant", default="auto", choices=["auto", "mega", "wavefront", "pipeline"])
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (debug only)")
     ap.add_argument("--cpu-spp", type=int, default=8, help="spp of the bounded CPU-baseline sample")
-    ap.add_argument("--refkernel-spp", type=int, default=16, help="spp of the bounded reference-CUDA-kernel sample")
+    ap.add_argument("--refkernel-spp", type=int, default=64, help="spp of the bounded reference-CUDA-kernel sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-refkernel", action="store_true")
     args = ap.parse_args()

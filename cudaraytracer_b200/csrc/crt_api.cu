@@ -55,7 +55,7 @@ struct crt_context
 
     DevCounters* d_counters = nullptr; // CRT_COUNTER_SHARDS entries
     WfShard* d_shards = nullptr;       // work counters of the pipelined megakernel
-    int pipe_thresh = 20, pipe_rounds = 16, pipe_slots = 0, pipe_check = 4; // CRT_PIPE_THRESH / _ROUNDS / _SLOTS / _CHECK
+    int pipe_thresh = 20, pipe_rounds = 16, pipe_slots = 0, pipe_check = 1; // CRT_PIPE_THRESH / _ROUNDS / _SLOTS / _CHECK
     uint64_t launches = 0;
 
     WavefrontState wf;
@@ -692,7 +692,12 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
 
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
     if (p->spp_count > 0 && A.cover_w > 0 && A.cover_h > 0) {
-        int variant = p->variant == CRT_VARIANT_AUTO ? CRT_VARIANT_MEGAKERNEL : p->variant;
+        // AUTO, chosen by measurement (DESIGN.md "variant choice"): the pipelined persistent kernel wins as soon as traversal
+        // dominates (RTIOW 486 prims: 13.0 vs 11.5 Grays/s; 10k prims: 7.5 vs 5.4); below a few hundred primitives its
+        // queue handling costs more than the divergence it removes (67 prims: 16.4 vs 21.1) and the megakernel is used.
+        int variant = p->variant;
+        if (variant == CRT_VARIANT_AUTO)
+            variant = (exact || count || ctx->scene.n_prims < 256) ? CRT_VARIANT_MEGAKERNEL : CRT_VARIANT_PIPELINE;
         if (variant == CRT_VARIANT_WAVEFRONT || variant == CRT_VARIANT_PIPELINE) {
             if (exact || count) return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, "crt_render: EXACT_MATH / COUNT_TESTS are megakernel-only");
             crt_status ws = variant == CRT_VARIANT_WAVEFRONT ? render_wavefront(ctx, A) : render_pipeline(ctx, A);

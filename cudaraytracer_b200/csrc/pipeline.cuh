@@ -315,13 +315,15 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         }
         // ---- traverse: until fewer than THRESH lanes are busy (a refill is due) or it is time to look at the queues ----
         const int leave_below = refill_short ? 1 : THRESH; // EXT ran dry: leaving early would only spin
-        int rounds = 0;
-        do {
-            if (cur >= 0) node_step<false, SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
+        int rounds_left = A.max_rounds;
+        while (true) { // two node visits per vote
+            node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
+            if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
+            node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
             if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
             act = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
-            rounds++;
-        } while (__popc(act) >= leave_below && rounds < A.max_rounds);
+            if (__popc(act) < leave_below || --rounds_left <= 0) break;
+        }
             // ---- finished lanes: store the hit, push the slot into the queue of what it hit ----
         const bool fin = cur == CRT_TRAV_DONE && slot >= 0;
         {

@@ -234,6 +234,35 @@ __device__ __forceinline__ void node_step(const SceneView& S, const TravRay& r, 
     else cur = sp ? stack[--sp] : CRT_TRAV_DONE;
 }
 
+// The same visit executed by EVERY lane of the warp (fast path): lanes that are not at an inner node run it on node 0 and
+// discard the result. Inactive lanes cost a SIMT machine the same issue slots either way, and without the branch around the
+// body the loop loses its convergence-barrier bookkeeping (profiles/r01_c: 20 uniform instructions per round before this).
+template <bool SMEM_ALL>
+__device__ __forceinline__ void node_step_all(const SceneView& S, const TravRay& r, float t_min, float t_hit, int& cur, int& sp, int* stack)
+{
+    const bool at = cur >= 0;
+    float4 w0, w1, w2;
+    int2 ch;
+    load_node<SMEM_ALL>(S, at ? cur : 0, w0, w1, w2, ch);
+    const float lx0 = fmaf(w0.x, r.id.x, -r.ood.x), ly0 = fmaf(w0.y, r.id.y, -r.ood.y), lz0 = fmaf(w0.z, r.id.z, -r.ood.z);
+    const float hx0 = fmaf(w0.w, r.id.x, -r.ood.x), hy0 = fmaf(w1.x, r.id.y, -r.ood.y), hz0 = fmaf(w1.y, r.id.z, -r.ood.z);
+    const float lx1 = fmaf(w1.z, r.id.x, -r.ood.x), ly1 = fmaf(w1.w, r.id.y, -r.ood.y), lz1 = fmaf(w2.x, r.id.z, -r.ood.z);
+    const float hx1 = fmaf(w2.y, r.id.x, -r.ood.x), hy1 = fmaf(w2.z, r.id.y, -r.ood.y), hz1 = fmaf(w2.w, r.id.z, -r.ood.z);
+    const float tn0 = fmaxf(fmaxf(fminf(lx0, hx0), fminf(ly0, hy0)), fmaxf(fminf(lz0, hz0), t_min));
+    const float tf0 = fminf(fminf(fmaxf(lx0, hx0), fmaxf(ly0, hy0)), fminf(fmaxf(lz0, hz0), t_hit));
+    const float tn1 = fmaxf(fmaxf(fminf(lx1, hx1), fminf(ly1, hy1)), fmaxf(fminf(lz1, hz1), t_min));
+    const float tf1 = fminf(fminf(fmaxf(lx1, hx1), fmaxf(ly1, hy1)), fminf(fmaxf(lz1, hz1), t_hit));
+    const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+    const bool swap = tn1 < tn0;
+    const int first = (h0 && !(h1 && swap)) ? ch.x : ch.y; // the nearer hit child (or the only one)
+    const int second = swap ? ch.x : ch.y;
+    if (at) {
+        if (h0 && h1) stack[sp++] = second;
+        if (h0 || h1) cur = first;
+        else cur = sp ? stack[--sp] : CRT_TRAV_DONE;
+    }
+}
+
 // One leaf visit: test the primitive, shrink the hit distance, pop. `cur` < 0 and != CRT_TRAV_DONE on entry.
 template <bool EXACT, bool SMEM_ALL>
 __device__ __forceinline__ void leaf_step(const SceneView& S, const TravRay& r, float t_min, Hit& h, int& cur, int& sp, const int* stack)
