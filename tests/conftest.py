@@ -19,7 +19,8 @@ def _built():
     from cudaraytracer_b200 import capi
     import oracle_lib
 
-    if not (os.path.exists(capi.LIB_PATH) and os.path.exists(oracle_lib.ORACLE_SO)):
+    if not (os.path.exists(capi.LIB_PATH) and os.path.exists(oracle_lib.ORACLE_SO) and
+            os.path.exists(os.path.join(ROOT, "examples", "headless_render"))):
         import __graft_entry__
 
         __graft_entry__.build()

@@ -65,3 +65,19 @@ def test_no_gpu_fails_loudly():
     st = lib.crt_context_create(0, C.byref(ctx))
     assert st != capi.CRT_OK and not ctx.value
     assert b"no CUDA device" in lib.crt_last_error_string(None)
+
+
+def test_c_host_example_builds_and_fails_loudly_without_a_gpu(tmp_path):
+    """examples/headless_render.c: a plain-C host over include/crt.h (the reference's host is C++; the boundary is C)."""
+    import subprocess
+    import torch
+    exe = os.path.join(ROOT, "examples", "headless_render")
+    assert os.path.exists(exe), "built by make -C cudaraytracer_b200/csrc (target examples)"
+    out = str(tmp_path / "f.ppm")
+    r = subprocess.run([exe, "1", "64", "36", "2", "8", "2", out], capture_output=True, text=True)
+    if torch.cuda.is_available():
+        assert r.returncode == 0, r.stderr
+        data = open(out, "rb").read()
+        assert data.startswith(b"P6\n64 36\n255\n") and len(data) == len(b"P6\n64 36\n255\n") + 64 * 36 * 3
+    else:
+        assert r.returncode != 0 and "no CUDA device" in r.stderr

@@ -37,3 +37,18 @@ def test_sharded_sum_is_bit_identical(world):
     assert torch.equal(total, ref)
     assert int(ref[..., 3].min()) == spp == int(ref[..., 3].max())
     ref_r.close()
+
+
+def test_c_host_example_renders_a_ppm(tmp_path):
+    """examples/headless_render.c (plain C over the C ABI): progressive passes, resolve, PPM on disk."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = str(tmp_path / "f.ppm")
+    r = subprocess.run([os.path.join(root, "examples", "headless_render"), "1", "96", "54", "4", "50", "3", out], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    data = open(out, "rb").read()
+    head = b"P6\n96 54\n255\n"
+    assert data.startswith(head) and len(data) == len(head) + 96 * 54 * 3
+    img = np.frombuffer(data[len(head):], dtype=np.uint8).reshape(54, 96, 3)
+    assert img[0].mean() > img[-1].mean() * 0.5 and img.std() > 10  # an actual picture: sky on top (rows flipped on write)
