@@ -87,6 +87,7 @@ SIGNATURES = {
     "crt_scene_upload": (C.c_int, [_P, C.POINTER(SceneDesc)]),
     "crt_scene_from_reference": (C.c_int, [_P, _P]),
     "crt_bvh_get_stats": (C.c_int, [_P, C.POINTER(BvhStats)]),
+    "crt_bvh_build_check": (C.c_int, [C.POINTER(SceneDesc), C.POINTER(BvhStats)]),
     "crt_set_camera": (C.c_int, [_P, C.POINTER(InputStruct)]),
     "crt_set_lens": (C.c_int, [_P, C.c_float, C.c_float]),
     "crt_framebuffer_resize": (C.c_int, [_P, C.c_uint32, C.c_uint32]),

@@ -285,6 +285,58 @@ crt_status crt_scene_from_reference(crt_context* ctx, const void* world)
     return crt_scene_upload(ctx, &d);
 }
 
+crt_status crt_bvh_build_check(const crt_scene_desc* scene, crt_bvh_stats* out)
+{
+    if (!scene || !out) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_bvh_build_check: NULL argument");
+    CrtPackedScene P;
+    std::string err;
+    if (!crt_pack_scene(scene, &P, &err)) return crt_set_error(nullptr, CRT_ERR_INVALID, err.c_str());
+    *out = P.stats;
+    const size_t nn = P.nodes.size(), np = P.stats.n_prims;
+    std::vector<int> seen(np ? np : 1, 0);
+    struct Item { int node; float lo[3], hi[3]; };
+    std::vector<Item> st;
+    Item root;
+    root.node = 0;
+    for (int i = 0; i < 3; i++) { root.lo[i] = -INFINITY; root.hi[i] = INFINITY; }
+    st.push_back(root);
+    size_t visited = 0;
+    while (!st.empty()) {
+        Item it = st.back();
+        st.pop_back();
+        if (it.node < 0 || (size_t)it.node >= nn) return crt_set_error(nullptr, CRT_ERR_INVALID, "bvh check: child index out of range");
+        if (++visited > nn) return crt_set_error(nullptr, CRT_ERR_INVALID, "bvh check: cycle or shared node");
+        const CrtPackedNode& n = P.nodes[it.node];
+        for (int c = 0; c < 2; c++) {
+            const float* b = n.w + 6 * c;
+            if (np >= 2)
+                for (int i = 0; i < 3; i++)
+                    if (b[i] < it.lo[i] || b[3 + i] > it.hi[i]) return crt_set_error(nullptr, CRT_ERR_INVALID, "bvh check: child box outside its parent's box");
+            if (n.child[c] >= 0) {
+                Item ch;
+                ch.node = n.child[c];
+                for (int i = 0; i < 3; i++) { ch.lo[i] = b[i]; ch.hi[i] = b[3 + i]; }
+                st.push_back(ch);
+            }
+            else if (np > 0) {
+                const uint32_t code = (uint32_t)~n.child[c];
+                const uint32_t slot = code & CRT_LEAF_INDEX_MASK;
+                if (slot >= np) return crt_set_error(nullptr, CRT_ERR_INVALID, "bvh check: leaf slot out of range");
+                if (np >= 2 || c == 0) seen[slot]++;
+                const float* pr = &P.prims[4 * (size_t)slot];
+                if ((code >> CRT_LEAF_TYPE_SHIFT) == CRT_SPHERE) {
+                    const float r = fabsf(pr[3]);
+                    for (int i = 0; i < 3; i++)
+                        if (pr[i] - r < b[i] || pr[i] + r > b[3 + i]) return crt_set_error(nullptr, CRT_ERR_INVALID, "bvh check: sphere outside its leaf box");
+                }
+            }
+        }
+    }
+    for (size_t i = 0; i < np; i++)
+        if (seen[i] != 1) return crt_set_error(nullptr, CRT_ERR_INVALID, "bvh check: a primitive is referenced by no leaf or by several");
+    return CRT_OK;
+}
+
 crt_status crt_bvh_get_stats(const crt_context* ctx, crt_bvh_stats* out)
 {
     if (!ctx || !out) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_bvh_get_stats: NULL argument");

@@ -9,8 +9,11 @@
 #include "crt_internal.h"
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <thread>
@@ -62,7 +65,8 @@ struct Builder
     std::vector<float> cent; // 3 per prim
     std::vector<uint32_t> idx;
     std::vector<BuildNode> nodes;
-    int max_depth = 0;
+    std::atomic<int> max_depth{0};
+    int par_depth = 10; // levels whose left subtree gets its own thread (CRT_BVH_PAR_DEPTH; 0 = single-threaded build)
 
     static constexpr int kBins = 16;
 
@@ -75,10 +79,12 @@ struct Builder
         return r;
     }
 
-    // Returns the child reference for the range [b, e).
-    int32_t build(uint32_t b, uint32_t e, const Box& bounds, int depth)
+    // Returns the child reference for the range [b, e). A subtree over k primitives has exactly k - 1 inner nodes, so node
+    // indices are assigned by range (root of [b, e) at `base`, left subtree from base + 1, right subtree from base + (mid - b)):
+    // no shared counter, and big subtrees are built by their own threads.
+    int32_t build(uint32_t b, uint32_t e, const Box& bounds, int depth, uint32_t base)
     {
-        max_depth = std::max(max_depth, depth);
+        for (int cur = max_depth.load(std::memory_order_relaxed); depth > cur && !max_depth.compare_exchange_weak(cur, depth);) { }
         if (e - b == 1)
             return ~(int32_t)idx[b];
 
@@ -90,41 +96,51 @@ struct Builder
         int best_axis = -1, best_split = -1;
         float best_cost = std::numeric_limits<float>::infinity();
         const uint32_t n = e - b;
+        Box lb, rb; // child boxes; for a SAH split they fall out of the bins, no extra pass over the range
+        lb.reset();
+        rb.reset();
         if (n > 2) {
+            // one pass over the range bins all three axes
+            Box bins[3][kBins];
+            uint32_t cnt[3][kBins];
+            float scale[3];
             for (int ax = 0; ax < 3; ax++) {
                 float ext = cb.hi[ax] - cb.lo[ax];
-                if (!(ext > 0.f))
-                    continue;
-                Box bins[kBins];
-                uint32_t cnt[kBins];
+                scale[ax] = ext > 0.f ? (float)kBins / ext : 0.f;
                 for (int k = 0; k < kBins; k++) {
-                    bins[k].reset();
-                    cnt[k] = 0;
+                    bins[ax][k].reset();
+                    cnt[ax][k] = 0;
                 }
-                float scale = (float)kBins / ext;
-                for (uint32_t i = b; i < e; i++) {
-                    uint32_t p = idx[i];
-                    int k = (int)((cent[3 * (size_t)p + ax] - cb.lo[ax]) * scale);
+            }
+            for (uint32_t i = b; i < e; i++) {
+                const uint32_t p = idx[i];
+                const Box& pb = pbox[p];
+                for (int ax = 0; ax < 3; ax++) {
+                    int k = (int)((cent[3 * (size_t)p + ax] - cb.lo[ax]) * scale[ax]);
                     k = std::min(std::max(k, 0), kBins - 1);
-                    bins[k].grow(pbox[p]);
-                    cnt[k]++;
+                    bins[ax][k].grow(pb);
+                    cnt[ax][k]++;
                 }
+            }
+            for (int ax = 0; ax < 3; ax++) {
+                if (!(scale[ax] > 0.f))
+                    continue;
                 float right_area[kBins];
                 uint32_t right_cnt[kBins];
                 Box acc;
                 acc.reset();
                 uint32_t c = 0;
                 for (int k = kBins - 1; k > 0; k--) {
-                    acc.grow(bins[k]);
-                    c += cnt[k];
+                    acc.grow(bins[ax][k]);
+                    c += cnt[ax][k];
                     right_area[k] = acc.half_area();
                     right_cnt[k] = c;
                 }
                 acc.reset();
                 c = 0;
                 for (int k = 0; k < kBins - 1; k++) {
-                    acc.grow(bins[k]);
-                    c += cnt[k];
+                    acc.grow(bins[ax][k]);
+                    c += cnt[ax][k];
                     if (c == 0 || right_cnt[k + 1] == 0)
                         continue;
                     float cost = acc.half_area() * (float)c + right_area[k + 1] * (float)right_cnt[k + 1];
@@ -134,6 +150,9 @@ struct Builder
                         best_split = k;
                     }
                 }
+            }
+            if (best_axis >= 0) {
+                for (int k = 0; k < kBins; k++) (k <= best_split ? lb : rb).grow(bins[best_axis][k]);
             }
         }
 
@@ -162,14 +181,27 @@ struct Builder
                 return cp < cq || (cp == cq && p < q);
             });
         }
-        if (mid == b || mid == e)
+        bool boxes_from_bins = best_axis >= 0;
+        if (mid == b || mid == e) {
             mid = b + n / 2;
+            boxes_from_bins = false;
+        }
+        if (!boxes_from_bins) {
+            lb = range_box(b, mid);
+            rb = range_box(mid, e);
+        }
 
-        int32_t me = (int32_t)nodes.size();
-        nodes.emplace_back();
-        Box lb = range_box(b, mid), rb = range_box(mid, e);
-        int32_t l = build(b, mid, lb, depth + 1);
-        int32_t r = build(mid, e, rb, depth + 1);
+        int32_t me = (int32_t)base;
+        int32_t l, r;
+        if (n >= 8192 && depth <= par_depth) { // top of a big tree: left subtree on another thread
+            std::thread t([&] { l = build(b, mid, lb, depth + 1, base + 1); });
+            r = build(mid, e, rb, depth + 1, base + (mid - b));
+            t.join();
+        }
+        else {
+            l = build(b, mid, lb, depth + 1, base + 1);
+            r = build(mid, e, rb, depth + 1, base + (mid - b));
+        }
         nodes[me].box = bounds;
         nodes[me].child[0] = l;
         nodes[me].child[1] = r;
@@ -293,10 +325,12 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
         all.grow(b);
     }
 
+    auto t_boxes = std::chrono::steady_clock::now();
     // 3. build
-    B.nodes.reserve(n ? n : 1);
+    if (const char* e = getenv("CRT_BVH_PAR_DEPTH")) B.par_depth = atoi(e);
     if (n >= 2) {
-        B.build(0, n, all, 1); // the root is always build-node 0
+        B.nodes.resize(n - 1);
+        B.build(0, n, all, 1, 0); // the root is always build-node 0
     }
     else {
         B.nodes.emplace_back();
@@ -305,6 +339,7 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
         B.nodes[0].child[1] = ~0; // single object: left == right, like the reference (Hittable.cuh:326-328)
     }
 
+    auto t_built = std::chrono::steady_clock::now();
     // 4. breadth-first emission; leaves get their final primitive slot in BFS discovery order so that
     //    primitives referenced by neighbouring nodes are neighbours in memory too.
     const uint32_t nn = (uint32_t)B.nodes.size();
@@ -328,16 +363,30 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
             }
         }
     }
-    uint32_t next_prim = 0;
-    double sah = 0.0;
+    // first leaf slot of every packed node (leaves get their slots in BFS order), so that the packing loop below has no
+    // loop-carried state and can be split over threads
+    std::vector<uint32_t> slot0(nn + 1, 0);
+    for (uint32_t q = 0; q < nn; q++) {
+        const BuildNode& bn = B.nodes[order[q]];
+        uint32_t leaves = 0;
+        if (n >= 2) leaves = (bn.child[0] < 0) + (bn.child[1] < 0);
+        else if (n == 1) leaves = 1;
+        slot0[q + 1] = slot0[q] + leaves;
+    }
     const float root_area = all.half_area();
     float extent = 0.f;
     if (n)
         for (int i = 0; i < 3; i++) extent = std::max(extent, std::max(fabsf(all.lo[i]), fabsf(all.hi[i])));
     const float abs_pad = 1e-7f + 4e-7f * extent;
-    for (uint32_t q = 0; q < nn; q++) {
+    const uint32_t n_chunks = nn >= 65536 ? 16u : 1u;
+    std::vector<double> sah_part(n_chunks, 0.0);
+    auto pack_range = [&](uint32_t chunk) {
+    double sah = 0.0;
+    const uint32_t q_lo = (uint32_t)((uint64_t)nn * chunk / n_chunks), q_hi = (uint32_t)((uint64_t)nn * (chunk + 1) / n_chunks);
+    for (uint32_t q = q_lo; q < q_hi; q++) {
         const BuildNode& bn = B.nodes[order[q]];
         CrtPackedNode& pn = out->nodes[q];
+        uint32_t next_prim = slot0[q];
         memset(&pn, 0, sizeof(pn));
         if (root_area > 0.f)
             sah += 1.0 * bn.box.half_area() / root_area;
@@ -412,12 +461,28 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
             }
         }
     }
+    sah_part[chunk] = sah;
+    };
+    if (n_chunks == 1) {
+        pack_range(0);
+    }
+    else {
+        std::vector<std::thread> pool;
+        for (uint32_t c = 1; c < n_chunks; c++) pool.emplace_back(pack_range, c);
+        pack_range(0);
+        for (std::thread& t : pool) t.join();
+    }
+    double sah = 0.0;
+    for (double v : sah_part) sah += v; // fixed chunking, fixed order: the statistic is deterministic
 
     auto t1 = std::chrono::steady_clock::now();
+    if (getenv("CRT_BVH_TIMING"))
+        fprintf(stderr, "[crt] bvh: boxes %.1f ms, build %.1f ms, emit %.1f ms\n", std::chrono::duration<double, std::milli>(t_boxes - t0).count(),
+                std::chrono::duration<double, std::milli>(t_built - t_boxes).count(), std::chrono::duration<double, std::milli>(t1 - t_built).count());
     memset(&out->stats, 0, sizeof(out->stats));
     out->stats.n_prims = n;
     out->stats.n_nodes = nn;
-    out->stats.max_depth = (uint64_t)B.max_depth;
+    out->stats.max_depth = (uint64_t)B.max_depth.load();
     out->stats.sah_cost = sah;
     out->stats.build_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
     out->stats.node_bytes = (uint64_t)nn * sizeof(CrtPackedNode);

@@ -150,6 +150,10 @@ crt_status crt_scene_upload(crt_context* ctx, const crt_scene_desc* scene);
  * LaunchKernel receives (Kernel.cu:178-181). Host-readable (managed or host) memory. */
 crt_status crt_scene_from_reference(crt_context* ctx, const void* world);
 crt_status crt_bvh_get_stats(const crt_context* ctx, crt_bvh_stats* out);
+/* Host-only: build and pack the BVH of `scene` exactly as crt_scene_upload does (no GPU needed), check its invariants (every
+ * primitive inside the boxes of all its ancestors, every active hittable referenced by exactly one leaf, child indices in
+ * range) and report the statistics. CRT_ERR_INVALID with a message if an invariant is broken. */
+crt_status crt_bvh_build_check(const crt_scene_desc* scene, crt_bvh_stats* out);
 
 /* ---- camera ---- */
 crt_status crt_set_camera(crt_context* ctx, const crt_input_struct* inputs);

@@ -81,3 +81,31 @@ def test_c_host_example_builds_and_fails_loudly_without_a_gpu(tmp_path):
         assert data.startswith(b"P6\n64 36\n255\n") and len(data) == len(b"P6\n64 36\n255\n") + 64 * 36 * 3
     else:
         assert r.returncode != 0 and "no CUDA device" in r.stderr
+
+
+@pytest.mark.parametrize("kind,hint,n", [(capi.SCENE_RTIOW, 0, None), (capi.SCENE_REFERENCE_DEFAULT, 0, 17), (capi.SCENE_TEXTURED, 64, None),
+                                         (capi.SCENE_STRESS_10K, 0, 10001), (capi.SCENE_GRID_1M, 300, 90001)])
+def test_host_bvh_build_invariants(kind, hint, n):
+    """The host BVH builder (csrc/scene_pack.cpp, multi-threaded above 32k primitives) on every scene kind: every primitive in
+    exactly one leaf and inside all ancestor boxes."""
+    from cudaraytracer_b200 import Scene
+    s = Scene.generate(kind, 1984, hint)
+    st = capi.BvhStats()
+    rc = capi.load().crt_bvh_build_check(C.byref(s.desc), C.byref(st))
+    assert rc == capi.CRT_OK, capi.load().crt_last_error_string(None)
+    assert st.n_prims == (n or s.n_hittables) and st.n_nodes == max(st.n_prims - 1, 1)
+    assert st.max_depth < 64 and st.sah_cost > 0
+
+
+def test_host_bvh_build_is_deterministic_and_handles_degenerate_input():
+    from cudaraytracer_b200 import Scene
+    tex = [dict(type=capi.CONSTANT, color=(0.5, 0.5, 0.5))]
+    mat = [dict(type=capi.LAMBERTIAN, texture=0)]
+    same = [dict(type=capi.SPHERE, cx=1.0, cy=2.0, cz=3.0, a=0.5, material=0) for _ in range(100)]  # 100 coincident spheres
+    s = Scene.from_arrays(same, mat, tex)
+    st = capi.BvhStats()
+    assert capi.load().crt_bvh_build_check(C.byref(s.desc), C.byref(st)) == capi.CRT_OK
+    assert st.n_prims == 100 and st.max_depth <= 9
+    for n in (0, 1, 2, 3):
+        s = Scene.from_arrays(same[:n], mat, tex)
+        assert capi.load().crt_bvh_build_check(C.byref(s.desc), C.byref(st)) == capi.CRT_OK and st.n_prims == n
