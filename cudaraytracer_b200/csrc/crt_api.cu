@@ -55,7 +55,7 @@ struct crt_context
 
     DevCounters* d_counters = nullptr; // CRT_COUNTER_SHARDS entries
     WfShard* d_shards = nullptr;       // work counters of the pipelined megakernel
-    int pipe_thresh = 20, pipe_rounds = 16, pipe_slots = 0, pipe_check = 1; // CRT_PIPE_THRESH / _ROUNDS / _SLOTS / _CHECK
+    int pipe_thresh = 20, pipe_rounds = 16, pipe_slots = 0, pipe_check = 4, pipe_ext_low = 256; // CRT_PIPE_THRESH / _ROUNDS / _SLOTS / _CHECK
     uint64_t launches = 0;
 
     WavefrontState wf;
@@ -152,6 +152,7 @@ crt_status crt_context_create(int device, crt_context** out)
     if ((env = getenv("CRT_PIPE_ROUNDS")) && atoi(env) > 0) ctx->pipe_rounds = atoi(env);
     if ((env = getenv("CRT_PIPE_SLOTS")) && atoi(env) > 0) ctx->pipe_slots = atoi(env);
     if ((env = getenv("CRT_PIPE_CHECK")) && atoi(env) > 0) ctx->pipe_check = atoi(env);
+    if ((env = getenv("CRT_PIPE_EXT_LOW")) && atoi(env) >= 0) ctx->pipe_ext_low = atoi(env);
     if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
         (e = cudaMalloc(&ctx->d_counters, CRT_COUNTER_SHARDS * sizeof(DevCounters))) != cudaSuccess ||
@@ -696,6 +697,7 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
     W.n_slots = n_slots;
     W.max_rounds = ctx->pipe_rounds;
     W.check_every = ctx->pipe_check;
+    W.ext_low = ctx->pipe_ext_low;
     const uint32_t stride = A.spp_stride ? A.spp_stride : 1u;
     const uint32_t spp_per_pass = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(A.spp_count, 0xF0000000ull / P));
     for (uint32_t done = 0; done < A.spp_count; done += spp_per_pass) {

@@ -33,7 +33,8 @@ struct PipeArgs
     uint32_t n_pixels_cover; // work item w -> sample w / n_pixels_cover, pixel w % n_pixels_cover
     int n_slots;             // N, a power of two
     int max_rounds;          // traversal rounds between two refills at most
-    int check_every;         // a warp looks for shade/generate work every check_every-th iteration
+    int check_every;         // a warp looks for shade/generate work every check_every-th iteration ...
+    int ext_low;             // ... and whenever the EXT queue held fewer rays than this at its last refill
 };
 
 // Control words of the queues (static shared memory). head/tail count reservations and never wrap in practice
@@ -91,18 +92,21 @@ __device__ __forceinline__ void pipe_release() { asm volatile("" ::: "memory"); 
 
 // Warp-level pop of up to `want` entries of queue q (never more than are reserved by producers). Returns the count n and
 // gives lanes with rank < n their slot id. One CAS per call; a lost race returns 0 and the caller simply tries again later.
-__device__ __forceinline__ int pipe_pop(const PipePool& P, PipeCtl* ctl, int q, int want, int rank, bool take, int& slot)
+__device__ __forceinline__ int pipe_pop(const PipePool& P, PipeCtl* ctl, int q, int want, int rank, bool take, int& slot,
+                                        int* left = nullptr)
 {
     unsigned int h = 0;
-    int n = 0;
+    int n = 0, avail = 0;
     if ((threadIdx.x & 31u) == 0u) {
         h = *(volatile unsigned int*)&ctl->head[q];
         const unsigned int t = *(volatile unsigned int*)&ctl->tail[q];
-        n = min(want, (int)(t - h));
+        avail = (int)(t - h);
+        n = min(want, avail);
         if (n > 0 && atomicCAS(&ctl->head[q], h, h + (unsigned int)n) != h) n = 0;
     }
     h = __shfl_sync(0xffffffffu, h, 0);
     n = __shfl_sync(0xffffffffu, n, 0);
+    if (left) *left = __shfl_sync(0xffffffffu, avail, 0) - n; // entries the queue still held when this warp looked
     if (take && rank < n) {
         volatile int* e = pipe_entry(P, q, h + (unsigned int)rank);
         int v;
@@ -255,12 +259,13 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
     bool exhausted = false;
 
     bool refill_short = true;
+    int ext_left = 0;
     for (unsigned it = 0; *(volatile int*)&ctl.live > 0; it++) {
         const unsigned act0 = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
         bool worked = false;
         // ---- shade / generate duty: lanes 1..6 each look at one queue. With 32 warps looking, every A.check_every-th
         //      iteration of a warp is enough to keep the class queues short; a warp that could not refill looks at once ----
-        if (refill_short || (it % (unsigned)A.check_every) == 0u) {
+        if (refill_short || ext_left < A.ext_low || (it % (unsigned)A.check_every) == 0u) {
             int sz = 0;
             if (lane < PQ_COUNT) sz = (int)(*(volatile unsigned int*)&ctl.tail[lane] - *(volatile unsigned int*)&ctl.head[lane]);
             const unsigned full_q = __ballot_sync(0xffffffffu, lane >= 1u && sz >= 32);
@@ -296,7 +301,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         if (m != 0u) {
             int s2 = -1;
             const int rank = __popc(m & lt);
-            const int n = pipe_pop(P, &ctl, PQ_EXT, __popc(m), rank, idle, s2);
+            const int n = pipe_pop(P, &ctl, PQ_EXT, __popc(m), rank, idle, s2, &ext_left);
             if (idle && rank < n) {
                 slot = s2;
                 const float4 a0 = P.a[slot], b0 = P.b[slot];
