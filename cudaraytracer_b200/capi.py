@@ -56,6 +56,15 @@ class InputStruct(C.Structure):
                 ("background_start", C.c_float * 3), ("background_end", C.c_float * 3)]
 
 
+class FlyCam(C.Structure):
+    _fields_ = [("position", C.c_float * 3), ("orientation", C.c_float * 3), ("up", C.c_float * 3), ("far_plane", C.c_float),
+                ("near_plane", C.c_float), ("fov_degrees", C.c_float), ("speed", C.c_float), ("sensitivity", C.c_float),
+                ("yaw", C.c_float), ("pitch", C.c_float)]
+
+
+KEY_W, KEY_A, KEY_S, KEY_D, KEY_SPACE, KEY_LCTRL, KEY_LSHIFT, KEY_C = 1, 2, 4, 8, 16, 32, 64, 128
+
+
 class RenderParams(C.Structure):
     _fields_ = [("spp_begin", C.c_uint32), ("spp_count", C.c_uint32), ("spp_stride", C.c_uint32), ("max_depth", C.c_uint32),
                 ("seed", C.c_uint64), ("variant", C.c_int32), ("jitter", C.c_int32), ("flags", C.c_uint32),
@@ -87,6 +96,9 @@ SIGNATURES = {
     "crt_scene_upload": (C.c_int, [_P, C.POINTER(SceneDesc)]),
     "crt_scene_from_reference": (C.c_int, [_P, _P]),
     "crt_bvh_get_stats": (C.c_int, [_P, C.POINTER(BvhStats)]),
+    "crt_scene_edit_hittable": (C.c_int, [_P, C.c_uint64, C.POINTER(Hittable)]),
+    "crt_scene_edit_material": (C.c_int, [_P, C.c_uint64, C.POINTER(Material)]),
+    "crt_scene_commit": (C.c_int, [_P, C.c_int, C.POINTER(C.c_int)]),
     "crt_bvh_build_check": (C.c_int, [C.POINTER(SceneDesc), C.POINTER(BvhStats)]),
     "crt_set_camera": (C.c_int, [_P, C.POINTER(InputStruct)]),
     "crt_set_lens": (C.c_int, [_P, C.c_float, C.c_float]),
@@ -108,6 +120,11 @@ SIGNATURES = {
     "crt_scene_builder_free": (None, [_P]),
     "crt_camera_look": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float, C.c_float,
                                   C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(InputStruct)]),
+    "crt_flycam_init": (C.c_int, [C.POINTER(FlyCam), C.POINTER(C.c_float)]),
+    "crt_flycam_step": (C.c_int, [C.POINTER(FlyCam), C.c_uint32, C.c_float, C.c_float, C.c_float, C.POINTER(C.c_int)]),
+    "crt_flycam_inputs": (C.c_int, [C.POINTER(FlyCam), C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(InputStruct)]),
+    "crt_load_ppm": (C.c_int, [C.c_char_p, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "crt_free": (None, [_P]),
     "crt_write_ppm": (C.c_int, [C.c_char_p, _P, C.c_uint32, C.c_uint32, C.c_int]),
     # include/crt_legacy.h
     "LaunchKernel": (None, [_P, C.c_uint, C.c_uint, C.c_uint, C.c_uint, _P, _P, InputStruct]),

@@ -6,7 +6,9 @@
 
 #include "kernels.cuh"
 #include "pipeline.cuh"
+#include "refit.cuh"
 
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -36,6 +38,16 @@ struct crt_context
     std::vector<uchar4*> d_texels;
     DevScene scene{};
     bool have_scene = false;
+    // host copy of the uploaded description (edits are staged here) + what the GPU refit needs
+    CrtFlatScene host;               // images[].pixels is only ever tested against NULL after the upload
+    std::vector<int32_t> slot_of;    // hittable index -> primitive slot, -1 if inactive
+    std::vector<uint8_t> dirty;      // per hittable
+    std::vector<uint64_t> dirty_list;
+    bool need_rebuild = false;
+    int* d_parent = nullptr;
+    int* d_leaf_ref = nullptr;
+    unsigned int* d_visits = nullptr;
+    float abs_pad = 0.f, scene_extent = 0.f;
     crt_bvh_stats stats{};
     uint64_t scene_h2d_bytes = 0;
 
@@ -90,17 +102,25 @@ static crt_status cuda_fail(crt_context* ctx, cudaError_t e, const char* what)
         if (e__ != cudaSuccess) return cuda_fail(ctx, e__, #call); \
     } while (0)
 
-static void free_scene(crt_context* ctx)
+static void free_geometry(crt_context* ctx)
 {
     cudaFree(ctx->d_nodes); ctx->d_nodes = nullptr;
     cudaFree(ctx->d_prims); ctx->d_prims = nullptr;
     cudaFree(ctx->d_prim_k); ctx->d_prim_k = nullptr;
     cudaFree(ctx->d_mats); ctx->d_mats = nullptr;
     cudaFree(ctx->d_prim_id); ctx->d_prim_id = nullptr;
+    cudaFree(ctx->d_parent); ctx->d_parent = nullptr;
+    cudaFree(ctx->d_leaf_ref); ctx->d_leaf_ref = nullptr;
+    cudaFree(ctx->d_visits); ctx->d_visits = nullptr;
+    ctx->have_scene = false;
+}
+
+static void free_scene(crt_context* ctx)
+{
+    free_geometry(ctx);
     cudaFree(ctx->d_images); ctx->d_images = nullptr;
     for (uchar4* p : ctx->d_texels) cudaFree(p);
     ctx->d_texels.clear();
-    ctx->have_scene = false;
 }
 
 extern "C" {
@@ -208,13 +228,21 @@ crt_status crt_synchronize(crt_context* ctx)
 // ------------------------------------------------------------------------------------------
 // scene
 // ------------------------------------------------------------------------------------------
-static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, const CrtPackedScene& P)
+static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, const CrtPackedScene& P, bool keep_images)
 {
     CU(cudaSetDevice(ctx->device));
     CU(cudaStreamSynchronize(ctx->stream));
-    free_scene(ctx);
+    if (keep_images) free_geometry(ctx);
+    else free_scene(ctx);
     const size_t nn = P.nodes.size(), np = P.prim_id.size();
     uint64_t h2d = 0;
+    CU(cudaMalloc(&ctx->d_parent, std::max<size_t>(nn, 1) * 4));
+    CU(cudaMalloc(&ctx->d_visits, std::max<size_t>(nn, 1) * 4));
+    CU(cudaMalloc(&ctx->d_leaf_ref, std::max<size_t>(np, 1) * 4));
+    CU(cudaMemcpyAsync(ctx->d_parent, P.parent.data(), nn * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->d_leaf_ref, P.leaf_ref.data(), np * 4, cudaMemcpyHostToDevice, ctx->stream));
+    h2d += (nn + np) * 4;
+    ctx->abs_pad = P.abs_pad;
     CU(cudaMalloc(&ctx->d_nodes, std::max<size_t>(nn, 1) * 64));
     CU(cudaMemcpyAsync(ctx->d_nodes, P.nodes.data(), nn * 64, cudaMemcpyHostToDevice, ctx->stream));
     h2d += nn * 64;
@@ -230,8 +258,8 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
         h2d += np * (16 + 4 + 32 + 4);
     }
     // images: RGB8 -> RGBA8 so a texel is one aligned 32-bit load
-    std::vector<DevImage> himg(sd->n_images);
-    for (uint64_t i = 0; i < sd->n_images; i++) {
+    std::vector<DevImage> himg(keep_images ? 0 : sd->n_images);
+    for (uint64_t i = 0; i < himg.size(); i++) {
         const crt_image& im = sd->images[i];
         himg[i].texels = nullptr;
         himg[i].width = im.width;
@@ -247,9 +275,18 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
         h2d += npx * 4;
         himg[i].texels = d;
     }
-    CU(cudaMalloc(&ctx->d_images, std::max<size_t>(himg.size(), 1) * sizeof(DevImage)));
-    if (!himg.empty()) CU(cudaMemcpy(ctx->d_images, himg.data(), himg.size() * sizeof(DevImage), cudaMemcpyHostToDevice));
+    if (!keep_images) {
+        CU(cudaMalloc(&ctx->d_images, std::max<size_t>(himg.size(), 1) * sizeof(DevImage)));
+        if (!himg.empty()) CU(cudaMemcpy(ctx->d_images, himg.data(), himg.size() * sizeof(DevImage), cudaMemcpyHostToDevice));
+    }
     CU(cudaStreamSynchronize(ctx->stream));
+    // bookkeeping for edits
+    ctx->slot_of.assign(sd->n_hittables, -1);
+    for (size_t sl = 0; sl < np; sl++)
+        if (P.prim_id[sl] >= 0) ctx->slot_of[P.prim_id[sl]] = (int32_t)sl;
+    ctx->dirty.assign(sd->n_hittables, 0);
+    ctx->dirty_list.clear();
+    ctx->need_rebuild = false;
 
     DevScene& S = ctx->scene;
     S.nodes = ctx->d_nodes; S.prims = ctx->d_prims; S.prim_k = ctx->d_prim_k; S.mats = ctx->d_mats;
@@ -273,7 +310,13 @@ crt_status crt_scene_upload(crt_context* ctx, const crt_scene_desc* scene)
     if (!crt_pack_scene(scene, &P, &err)) return crt_set_error(ctx, CRT_ERR_INVALID, err.c_str());
     if (P.stats.max_depth >= CRT_STACK_SIZE)
         return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, "crt_scene_upload: BVH deeper than the traversal stack");
-    return upload_packed(ctx, scene, P);
+    crt_status st = upload_packed(ctx, scene, P, false);
+    if (st != CRT_OK) return st;
+    ctx->host.hittables.assign(scene->hittables, scene->hittables + scene->n_hittables);
+    ctx->host.materials.assign(scene->materials, scene->materials + scene->n_materials);
+    ctx->host.textures.assign(scene->textures, scene->textures + scene->n_textures);
+    ctx->host.images.assign(scene->images, scene->images + scene->n_images);
+    return CRT_OK;
 }
 
 crt_status crt_scene_from_reference(crt_context* ctx, const void* world)
@@ -284,6 +327,110 @@ crt_status crt_scene_from_reference(crt_context* ctx, const void* world)
     if (!crt_flatten_reference_world(world, &flat, &err)) return crt_set_error(ctx, CRT_ERR_INVALID, err.c_str());
     crt_scene_desc d = flat.desc();
     return crt_scene_upload(ctx, &d);
+}
+
+// ---- scene edits (the caller side of the boundary: CudaLayer.cpp:493-494,918-1387 rebuild the BVH after every edit) ----
+static void mark_dirty(crt_context* ctx, uint64_t index)
+{
+    if (!ctx->dirty[index]) {
+        ctx->dirty[index] = 1;
+        ctx->dirty_list.push_back(index);
+    }
+}
+
+crt_status crt_scene_edit_hittable(crt_context* ctx, uint64_t index, const crt_hittable* h)
+{
+    if (!ctx || !h) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_edit_hittable: NULL argument");
+    if (!ctx->have_scene) return crt_set_error(ctx, CRT_ERR_STATE, "crt_scene_edit_hittable: no scene uploaded");
+    if (index >= ctx->host.hittables.size()) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_edit_hittable: index out of range");
+    if (h->type < CRT_SPHERE || h->type > CRT_YZRECT) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_edit_hittable: unknown type");
+    if (h->material < 0 || (uint64_t)h->material >= ctx->host.materials.size())
+        return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_edit_hittable: material index out of range");
+    const crt_hittable old = ctx->host.hittables[index];
+    // switching a primitive on/off or changing its kind changes the tree; everything else is a refit
+    if ((old.active != 0) != (h->active != 0) || (h->active && old.type != h->type)) ctx->need_rebuild = true;
+    ctx->host.hittables[index] = *h;
+    mark_dirty(ctx, index);
+    return CRT_OK;
+}
+
+crt_status crt_scene_edit_material(crt_context* ctx, uint64_t index, const crt_material* m)
+{
+    if (!ctx || !m) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_edit_material: NULL argument");
+    if (!ctx->have_scene) return crt_set_error(ctx, CRT_ERR_STATE, "crt_scene_edit_material: no scene uploaded");
+    if (index >= ctx->host.materials.size()) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_edit_material: index out of range");
+    if (m->type < CRT_LAMBERTIAN || m->type > CRT_DIFFUSELIGHT) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_edit_material: unknown type");
+    if (m->type != CRT_DIELECTRIC && (m->texture < 0 || (uint64_t)m->texture >= ctx->host.textures.size()))
+        return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_edit_material: texture index out of range");
+    ctx->host.materials[index] = *m;
+    for (uint64_t i = 0; i < ctx->host.hittables.size(); i++) // every primitive carries its own packed material record
+        if (ctx->host.hittables[i].material == (int32_t)index) mark_dirty(ctx, i);
+    return CRT_OK;
+}
+
+crt_status crt_scene_commit(crt_context* ctx, int force_rebuild, int* out_rebuilt)
+{
+    if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_scene_commit: ctx is NULL");
+    if (!ctx->have_scene) return crt_set_error(ctx, CRT_ERR_STATE, "crt_scene_commit: no scene uploaded");
+    if (out_rebuilt) *out_rebuilt = 0;
+    if (ctx->dirty_list.empty() && !force_rebuild) return CRT_OK;
+    CU(cudaSetDevice(ctx->device));
+    const crt_scene_desc d = ctx->host.desc();
+    if (force_rebuild || ctx->need_rebuild || ctx->scene.n_prims < 2) {
+        CrtPackedScene P;
+        std::string err;
+        if (!crt_pack_scene(&d, &P, &err)) return crt_set_error(ctx, CRT_ERR_INVALID, err.c_str());
+        if (P.stats.max_depth >= CRT_STACK_SIZE) return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, "crt_scene_commit: BVH deeper than the traversal stack");
+        if (out_rebuilt) *out_rebuilt = 1;
+        return upload_packed(ctx, &d, P, true); // the image textures stay where they are
+    }
+    // refit path: scatter the edited records, then recompute every box bottom-up on the GPU
+    auto t0 = std::chrono::steady_clock::now();
+    std::vector<EditRec> recs;
+    recs.reserve(ctx->dirty_list.size());
+    float extent = 0.f;
+    for (uint64_t idx : ctx->dirty_list) {
+        ctx->dirty[idx] = 0;
+        const crt_hittable& h = ctx->host.hittables[idx];
+        const int32_t slot = ctx->slot_of[idx];
+        if (!h.active || slot < 0) continue;
+        EditRec r;
+        float pr[4], mr[8];
+        crt_pack_prim(h, pr, &r.k);
+        crt_pack_material(&d, ctx->host.materials[h.material], mr);
+        r.prim = make_float4(pr[0], pr[1], pr[2], pr[3]);
+        r.m0 = make_float4(mr[0], mr[1], mr[2], mr[3]);
+        r.m1 = make_float4(mr[4], mr[5], mr[6], mr[7]);
+        r.slot = slot;
+        r.leaf_ref = 0; // looked up on the device (d_leaf_ref[slot])
+        r.child_code = ~(int32_t)(((uint32_t)h.type << CRT_LEAF_TYPE_SHIFT) |
+                                  ((uint32_t)ctx->host.materials[h.material].type << CRT_LEAF_MAT_SHIFT) | (uint32_t)slot);
+        recs.push_back(r);
+        const float reach = fabsf(h.a) + fabsf(h.b);
+        extent = std::max(extent, std::max(fabsf(h.cx), std::max(fabsf(h.cy), fabsf(h.cz))) + reach);
+    }
+    ctx->dirty_list.clear();
+    // the absolute box padding scales with the scene extent (scene_pack.cpp); edits may only grow it
+    ctx->abs_pad = std::max(ctx->abs_pad, 1e-7f + 4e-7f * extent);
+    if (!recs.empty()) {
+        EditRec* d_recs = nullptr;
+        CU(cudaMalloc(&d_recs, recs.size() * sizeof(EditRec)));
+        CU(cudaMemcpyAsync(d_recs, recs.data(), recs.size() * sizeof(EditRec), cudaMemcpyHostToDevice, ctx->stream));
+        const int n = (int)recs.size();
+        k_apply_edits<<<(n + 255) / 256, 256, 0, ctx->stream>>>(d_recs, n, ctx->d_prims, ctx->d_prim_k, ctx->d_mats, ctx->d_nodes, ctx->d_leaf_ref);
+        CU(cudaGetLastError());
+        CU(cudaMemsetAsync(ctx->d_visits, 0, (size_t)ctx->scene.n_nodes * 4, ctx->stream));
+        const int np = ctx->scene.n_prims;
+        k_bvh_refit<<<(np + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_nodes, ctx->d_prims, ctx->d_prim_k, ctx->d_parent, ctx->d_leaf_ref,
+                                                              ctx->d_visits, np, ctx->abs_pad);
+        CU(cudaGetLastError());
+        ctx->launches += 2;
+        CU(cudaStreamSynchronize(ctx->stream));
+        cudaFree(d_recs);
+        ctx->stats.h2d_bytes = recs.size() * sizeof(EditRec);
+    }
+    ctx->stats.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return CRT_OK;
 }
 
 crt_status crt_bvh_build_check(const crt_scene_desc* scene, crt_bvh_stats* out)

@@ -47,12 +47,19 @@ struct CrtPackedScene
     std::vector<float> prim_k;   // 1 float per primitive (rect plane offset; 0 for spheres)
     std::vector<float> mats;     // 8 floats per primitive
     std::vector<int32_t> prim_id;
+    // for the GPU refit (scene edits that keep the topology): where every node / leaf slot hangs, as parent_node * 2 + child
+    std::vector<int32_t> parent;   // per node; -1 for the root
+    std::vector<int32_t> leaf_ref; // per primitive slot
+    float abs_pad = 0.f;           // absolute box padding used by this build (scene_pack.cpp)
     crt_bvh_stats stats;
 };
 
 // Builds the BVH over the ACTIVE hittables (Hittable.cuh:311-320 filters inactive ones) and packs everything.
 // Returns false and fills err on invalid input.
 bool crt_pack_scene(const crt_scene_desc* scene, CrtPackedScene* out, std::string* err);
+// One primitive / one material record in the packed layout (also used by the edit path).
+void crt_pack_prim(const crt_hittable& h, float prim[4], float* k);
+void crt_pack_material(const crt_scene_desc* scene, const crt_material& m, float record[8]);
 
 // Host-side layout mirror of the reference scene graph (ref_abi.h) -> flat description.
 struct CrtFlatScene

@@ -237,6 +237,49 @@ void store_box(float* w, int slot, const Box& b, bool empty, float abs_pad)
 
 } // namespace
 
+void crt_pack_prim(const crt_hittable& h, float pr[4], float* k)
+{
+    const float hw = h.a / 2, hh = h.b / 2; // the reference computes center -/+ (width / 2) (Hittable.cuh:142-146)
+    *k = 0.f;
+    switch (h.type) {
+    case CRT_SPHERE: pr[0] = h.cx; pr[1] = h.cy; pr[2] = h.cz; pr[3] = h.a; break;
+    case CRT_XYRECT: pr[0] = h.cx - hw; pr[1] = h.cx + hw; pr[2] = h.cy - hh; pr[3] = h.cy + hh; *k = h.cz; break;
+    case CRT_XZRECT: pr[0] = h.cx - hw; pr[1] = h.cx + hw; pr[2] = h.cz - hh; pr[3] = h.cz + hh; *k = h.cy; break;
+    default:         pr[0] = h.cy - hh; pr[1] = h.cy + hh; pr[2] = h.cz - hw; pr[3] = h.cz + hw; *k = h.cx; break;
+    }
+}
+
+void crt_pack_material(const crt_scene_desc* sd, const crt_material& m, float mr[8])
+{
+    for (int i = 0; i < 8; i++) mr[i] = 0.f;
+    uint32_t bits = (uint32_t)m.type;
+    float param = m.param;
+    if (m.type == CRT_METAL)
+        param = m.param < 1 ? m.param : 1; // Material.cuh:71
+    if (m.type == CRT_DIFFUSELIGHT)
+        param = (float)m.light_intensity;  // int * Vec3 in the reference (Material.cuh:168-172)
+    if (m.type != CRT_DIELECTRIC) {
+        const crt_texture& t = sd->textures[m.texture];
+        bits |= (uint32_t)t.type << 4;
+        if (t.type == CRT_CONSTANT) {
+            mr[0] = t.color[0]; mr[1] = t.color[1]; mr[2] = t.color[2];
+        }
+        else if (t.type == CRT_CHECKER) {
+            mr[0] = t.odd[0]; mr[1] = t.odd[1]; mr[2] = t.odd[2];
+            mr[4] = t.even[0]; mr[5] = t.even[1]; mr[6] = t.even[2];
+        }
+        else {
+            bool has = t.image >= 0 && sd->images[t.image].pixels != nullptr;
+            bits |= (uint32_t)(has ? t.image + 1 : 0) << 8;
+        }
+    }
+    else {
+        mr[0] = mr[1] = mr[2] = 1.0f; // attenuation (1,1,1), Material.cuh:112
+    }
+    mr[3] = param;
+    memcpy(&mr[7], &bits, 4);
+}
+
 bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* err)
 {
     auto t0 = std::chrono::steady_clock::now();
@@ -349,6 +392,8 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
     out->prim_k.assign(np_alloc, 0.f);
     out->mats.assign(8 * np_alloc, 0.f);
     out->prim_id.assign(np_alloc, -1);
+    out->parent.assign(nn, -1);
+    out->leaf_ref.assign(np_alloc, 0);
     std::vector<int32_t> order;   // BFS order -> build node
     std::vector<int32_t> newidx(nn, -1);
     order.reserve(nn);
@@ -378,6 +423,7 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
     if (n)
         for (int i = 0; i < 3; i++) extent = std::max(extent, std::max(fabsf(all.lo[i]), fabsf(all.hi[i])));
     const float abs_pad = 1e-7f + 4e-7f * extent;
+    out->abs_pad = abs_pad;
     const uint32_t n_chunks = nn >= 65536 ? 16u : 1u;
     std::vector<double> sah_part(n_chunks, 0.0);
     auto pack_range = [&](uint32_t chunk) {
@@ -410,6 +456,7 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
             if (ch >= 0) {
                 store_box(pn.w, c, B.nodes[ch].box, false, abs_pad);
                 pn.child[c] = newidx[ch];
+                out->parent[newidx[ch]] = (int32_t)(q * 2 + c);
             }
             else {
                 uint32_t k = (uint32_t)~ch;          // index into the active list
@@ -420,44 +467,10 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
                     sah += 1.0 * B.pbox[k].half_area() / root_area;
                 pn.child[c] = ~(int32_t)(((uint32_t)h.type << CRT_LEAF_TYPE_SHIFT) |
                                          ((uint32_t)sd->materials[h.material].type << CRT_LEAF_MAT_SHIFT) | slot);
-                float* pr = &out->prims[4 * (size_t)slot];
-                float hw = h.a / 2, hh = h.b / 2;
-                switch (h.type) {
-                case CRT_SPHERE: pr[0] = h.cx; pr[1] = h.cy; pr[2] = h.cz; pr[3] = h.a; break;
-                case CRT_XYRECT: pr[0] = h.cx - hw; pr[1] = h.cx + hw; pr[2] = h.cy - hh; pr[3] = h.cy + hh; out->prim_k[slot] = h.cz; break;
-                case CRT_XZRECT: pr[0] = h.cx - hw; pr[1] = h.cx + hw; pr[2] = h.cz - hh; pr[3] = h.cz + hh; out->prim_k[slot] = h.cy; break;
-                default:         pr[0] = h.cy - hh; pr[1] = h.cy + hh; pr[2] = h.cz - hw; pr[3] = h.cz + hw; out->prim_k[slot] = h.cx; break;
-                }
+                crt_pack_prim(h, &out->prims[4 * (size_t)slot], &out->prim_k[slot]);
                 out->prim_id[slot] = (int32_t)active[k];
-                // material record
-                const crt_material& m = sd->materials[h.material];
-                float* mr = &out->mats[8 * (size_t)slot];
-                uint32_t bits = (uint32_t)m.type;
-                float param = m.param;
-                if (m.type == CRT_METAL)
-                    param = m.param < 1 ? m.param : 1; // Material.cuh:71
-                if (m.type == CRT_DIFFUSELIGHT)
-                    param = (float)m.light_intensity;  // int * Vec3 in the reference (Material.cuh:168-172)
-                if (m.type != CRT_DIELECTRIC) {
-                    const crt_texture& t = sd->textures[m.texture];
-                    bits |= (uint32_t)t.type << 4;
-                    if (t.type == CRT_CONSTANT) {
-                        mr[0] = t.color[0]; mr[1] = t.color[1]; mr[2] = t.color[2];
-                    }
-                    else if (t.type == CRT_CHECKER) {
-                        mr[0] = t.odd[0]; mr[1] = t.odd[1]; mr[2] = t.odd[2];
-                        mr[4] = t.even[0]; mr[5] = t.even[1]; mr[6] = t.even[2];
-                    }
-                    else {
-                        bool has = t.image >= 0 && sd->images[t.image].pixels != nullptr;
-                        bits |= (uint32_t)(has ? t.image + 1 : 0) << 8;
-                    }
-                }
-                else {
-                    mr[0] = mr[1] = mr[2] = 1.0f; // attenuation (1,1,1), Material.cuh:112
-                }
-                mr[3] = param;
-                memcpy(&mr[7], &bits, 4);
+                out->leaf_ref[slot] = (int32_t)(q * 2 + c);
+                crt_pack_material(sd, sd->materials[h.material], &out->mats[8 * (size_t)slot]);
             }
         }
     }

@@ -9,6 +9,7 @@
 #include "crt_internal.h"
 
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -373,5 +374,106 @@ crt_status crt_scene_builder_camera(const crt_scene_builder* b, uint32_t width, 
     const float up[3] = {0.f, 1.f, 0.f};
     return crt_camera_look(b->cam_pos, b->cam_orient, up, b->cam_fov_deg, b->cam_near, b->cam_far, b->bg0, b->bg1, out);
 }
+
+} // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// Scripted fly camera (Renderer/Camera.cpp:37-118) and PPM reader.
+// ------------------------------------------------------------------------------------------
+extern "C" {
+
+crt_status crt_flycam_init(crt_flycam* cam, const float position[3])
+{
+    if (!cam || !position) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_flycam_init: NULL argument");
+    for (int i = 0; i < 3; i++) cam->position[i] = position[i];
+    cam->orientation[0] = 0.f; cam->orientation[1] = 0.f; cam->orientation[2] = -1.f; // Camera.h:41
+    cam->up[0] = 0.f; cam->up[1] = 1.f; cam->up[2] = 0.f;
+    cam->far_plane = 10.0f; cam->near_plane = 0.1f; cam->fov_degrees = 45.0f;         // Camera.h:44-46
+    cam->speed = 0.05f; cam->sensitivity = 0.1f;                                      // Camera.h:6-7
+    cam->yaw = 270.0f; cam->pitch = 0.0f;                                             // Camera.h:59-60
+    return CRT_OK;
+}
+
+crt_status crt_flycam_step(crt_flycam* cam, uint32_t keys, float mouse_dx, float mouse_dy, float scroll, int* moved)
+{
+    if (!cam) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_flycam_step: NULL argument");
+    const crt_flycam before = *cam;
+    float* P = cam->position;
+    const float* O = cam->orientation;
+    const float* U = cam->up;
+    float right[3] = {O[1] * U[2] - O[2] * U[1], O[2] * U[0] - O[0] * U[2], O[0] * U[1] - O[1] * U[0]}; // cross(orientation, up)
+    const float inv = 1.0f / sqrtf(right[0] * right[0] + right[1] * right[1] + right[2] * right[2]);
+    for (int i = 0; i < 3; i++) right[i] *= inv;
+    const float sp = cam->speed; // the speed set by the PREVIOUS call applies to this call's moves (Camera.cpp:40-64)
+    if (keys & CRT_KEY_W) for (int i = 0; i < 3; i++) P[i] += sp * O[i];
+    if (keys & CRT_KEY_A) for (int i = 0; i < 3; i++) P[i] += sp * -right[i];
+    if (keys & CRT_KEY_S) for (int i = 0; i < 3; i++) P[i] += sp * -O[i];
+    if (keys & CRT_KEY_D) for (int i = 0; i < 3; i++) P[i] += sp * right[i];
+    if (keys & CRT_KEY_SPACE) for (int i = 0; i < 3; i++) P[i] += sp * U[i];
+    if (keys & CRT_KEY_LCTRL) for (int i = 0; i < 3; i++) P[i] += sp * -U[i];
+    cam->speed = (keys & CRT_KEY_LSHIFT) ? 0.05f * 2.0f : 0.05f;
+    if (keys & CRT_KEY_C) { P[0] = 0.0f; P[1] = 2.0f; P[2] = 12.0f; }
+    if (mouse_dx != 0.f || mouse_dy != 0.f) { // right button held: yaw/pitch (Camera.cpp:89-109); dy > 0 = cursor moved UP
+        cam->yaw += mouse_dx * cam->sensitivity;
+        cam->pitch += mouse_dy * cam->sensitivity;
+        if (cam->pitch > 89.0f) cam->pitch = 89.0f;
+        if (cam->pitch < -89.0f) cam->pitch = -89.0f;
+        const float k = 0.01745329251994329576923690768489f;
+        float d[3] = {cosf(k * cam->yaw) * cosf(k * cam->pitch), sinf(k * cam->pitch), sinf(k * cam->yaw) * cosf(k * cam->pitch)};
+        const float il = 1.0f / sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+        for (int i = 0; i < 3; i++) cam->orientation[i] = d[i] * il;
+    }
+    if (scroll != 0.f) { // ProcessMouseScroll, Camera.cpp:28-35
+        cam->fov_degrees -= scroll;
+        if (cam->fov_degrees < 1.0f) cam->fov_degrees = 1.0f;
+        if (cam->fov_degrees > 120.0f) cam->fov_degrees = 120.0f;
+    }
+    if (moved) {
+        *moved = 0;
+        for (int i = 0; i < 3; i++)
+            if (before.position[i] != cam->position[i] || before.orientation[i] != cam->orientation[i]) *moved = 1;
+        if (before.fov_degrees != cam->fov_degrees) *moved = 1;
+    }
+    return CRT_OK;
+}
+
+crt_status crt_flycam_inputs(const crt_flycam* cam, const float background_start[3], const float background_end[3], crt_input_struct* out)
+{
+    if (!cam || !out) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_flycam_inputs: NULL argument");
+    return crt_camera_look(cam->position, cam->orientation, cam->up, cam->fov_degrees, cam->near_plane, cam->far_plane, background_start,
+                           background_end, out);
+}
+
+crt_status crt_load_ppm(const char* path, uint8_t** out_pixels, int32_t* out_width, int32_t* out_height)
+{
+    if (!path || !out_pixels || !out_width || !out_height) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_load_ppm: NULL argument");
+    *out_pixels = nullptr;
+    FILE* f = fopen(path, "rb");
+    if (!f) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_load_ppm: cannot open the file");
+    int vals[3], got = 0, c;
+    char magic[3] = {0, 0, 0};
+    bool ok = fread(magic, 1, 2, f) == 2 && magic[0] == 'P' && magic[1] == '6';
+    while (ok && got < 3) { // header tokens, '#' comments allowed
+        c = fgetc(f);
+        if (c == '#') { while ((c = fgetc(f)) != '\n' && c != EOF) { } }
+        else if (c >= '0' && c <= '9') {
+            long v = 0;
+            do { v = v * 10 + (c - '0'); c = fgetc(f); } while (c >= '0' && c <= '9' && v < (1 << 28));
+            vals[got++] = (int)v; // the character after the number is consumed (for maxval it is the single whitespace before the data)
+        }
+        else if (c == EOF) ok = false;
+    }
+    ok = ok && vals[0] > 0 && vals[1] > 0 && vals[2] == 255 && (uint64_t)vals[0] * vals[1] <= (1ull << 30);
+    if (!ok) { fclose(f); return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_load_ppm: not a binary PPM (P6) with maxval 255"); }
+    const size_t n = (size_t)vals[0] * vals[1] * 3;
+    uint8_t* px = (uint8_t*)malloc(n);
+    if (!px) { fclose(f); return crt_set_error(nullptr, CRT_ERR_NOMEM, "crt_load_ppm: out of memory"); }
+    if (fread(px, 1, n, f) != n) { free(px); fclose(f); return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_load_ppm: truncated pixel data"); }
+    fclose(f);
+    *out_pixels = px; *out_width = vals[0]; *out_height = vals[1];
+    return CRT_OK;
+}
+
+void crt_free(void* p) { free(p); }
 
 } // extern "C"

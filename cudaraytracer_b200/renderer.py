@@ -142,6 +142,19 @@ class Renderer:
     def upload(self, scene: Scene):
         self._ck(self.lib.crt_scene_upload(self.ctx, C.byref(scene.desc)))
 
+    def edit_hittable(self, index: int, **fields):
+        """Stage an edit of hittable `index` (fields of crt_hittable: type, active, cx, cy, cz, a, b, material)."""
+        self._ck(self.lib.crt_scene_edit_hittable(self.ctx, index, C.byref(capi.Hittable(**fields))))
+
+    def edit_material(self, index: int, **fields):
+        self._ck(self.lib.crt_scene_edit_material(self.ctx, index, C.byref(capi.Material(**fields))))
+
+    def commit(self, force_rebuild: bool = False) -> bool:
+        """Apply the staged edits: GPU refit, or a host rebuild when the topology changed. Returns True if rebuilt."""
+        rebuilt = C.c_int()
+        self._ck(self.lib.crt_scene_commit(self.ctx, int(force_rebuild), C.byref(rebuilt)))
+        return bool(rebuilt.value)
+
     def bvh_stats(self) -> capi.BvhStats:
         st = capi.BvhStats()
         self._ck(self.lib.crt_bvh_get_stats(self.ctx, C.byref(st)))

@@ -149,6 +149,14 @@ crt_status crt_scene_upload(crt_context* ctx, const crt_scene_desc* scene);
 /* Walk the reference's own pointer graph: `world` is the Hittable of type BVHNODE that
  * LaunchKernel receives (Kernel.cu:178-181). Host-readable (managed or host) memory. */
 crt_status crt_scene_from_reference(crt_context* ctx, const void* world);
+/* ---- scene edits (replaces the reference's rebuild-after-every-edit: `bvh_node->Destroy()` + `new BVHNode(m_List, 0, n)`,
+ * CudaLayer.cpp:493-494,967-968,1375-1377). Edits are staged on the host copy of the uploaded scene; crt_scene_commit applies
+ * them. Moving / resizing a primitive, giving it another material, or editing a material keeps the tree and only REFITS the
+ * boxes on the GPU; (de)activating a primitive (Hittable::isActive, CudaLayer.cpp:1372-1387) or changing its kind rebuilds
+ * the tree on the host (image textures are not re-uploaded). *out_rebuilt tells which happened. ---- */
+crt_status crt_scene_edit_hittable(crt_context* ctx, uint64_t index, const crt_hittable* h);
+crt_status crt_scene_edit_material(crt_context* ctx, uint64_t index, const crt_material* m);
+crt_status crt_scene_commit(crt_context* ctx, int force_rebuild, int* out_rebuilt);
 crt_status crt_bvh_get_stats(const crt_context* ctx, crt_bvh_stats* out);
 /* Host-only: build and pack the BVH of `scene` exactly as crt_scene_upload does (no GPU needed), check its invariants (every
  * primitive inside the boxes of all its ancestors, every active hittable referenced by exactly one leaf, child indices in
@@ -203,8 +211,30 @@ crt_status crt_camera_look(const float position[3], const float orientation[3], 
                            float fov_degrees, float near_plane, float far_plane,
                            const float background_start[3], const float background_end[3], crt_input_struct* out);
 
+/* ---- scripted fly camera: the reference's interactive camera (Renderer/Camera.cpp:37-118, Camera.h:6-7,39-60) without a
+ * window. One crt_flycam_step = one Camera::Inputs call (one frame): `keys` says which keys are held, (mouse_dx, mouse_dy) is
+ * the cursor movement since the last frame while the right button is held (0,0 otherwise), `scroll` the wheel offset
+ * (Camera::ProcessMouseScroll, :28-35). crt_flycam_inputs is the mapping CudaLayer.cpp:413-431 applies after every call. ---- */
+enum { CRT_KEY_W = 1, CRT_KEY_A = 2, CRT_KEY_S = 4, CRT_KEY_D = 8, CRT_KEY_SPACE = 16, CRT_KEY_LCTRL = 32, CRT_KEY_LSHIFT = 64,
+       CRT_KEY_C = 128 /* reset the position to (0, 2, 12) */ };
+typedef struct crt_flycam {
+    float position[3], orientation[3], up[3];
+    float far_plane, near_plane, fov_degrees;
+    float speed, sensitivity, yaw, pitch;
+} crt_flycam;
+crt_status crt_flycam_init(crt_flycam* cam, const float position[3]); /* Camera ctor + defaults: looks down -z, fov 45 */
+/* returns 1 in *moved if the camera changed (the caller then clears the accumulation buffer), else 0 */
+crt_status crt_flycam_step(crt_flycam* cam, uint32_t keys, float mouse_dx, float mouse_dy, float scroll, int* moved);
+crt_status crt_flycam_inputs(const crt_flycam* cam, const float background_start[3], const float background_end[3],
+                             crt_input_struct* out);
+
 /* ---- headless framebuffer writer (replaces the GL blit, CudaLayer.cpp:379-386) ---- */
 crt_status crt_write_ppm(const char* path, const uint32_t* rgba8, uint32_t width, uint32_t height, int flip_rows);
+/* Binary PPM (P6, maxval 255) -> tightly packed RGB8, the layout Image expects (Texture.cuh:76; the reference decodes JPEGs with
+ * stb_image, Utils/RawStbImage.h:11-22, which is third-party code this library does not carry). *out_pixels is malloc'ed;
+ * release it with crt_free. */
+crt_status crt_load_ppm(const char* path, uint8_t** out_pixels, int32_t* out_width, int32_t* out_height);
+void       crt_free(void* p);
 
 #ifdef __cplusplus
 }

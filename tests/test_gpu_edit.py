@@ -1,0 +1,114 @@
+"""GPU tests of the scene-edit path: staged edits + crt_scene_commit = GPU refit (topology kept) or host
+rebuild (topology changed). Bar: after a commit the renderer is indistinguishable from a fresh upload of the edited scene —
+primary-hit IDs bit-exact vs the oracle, accumulation buffers bit-identical to a fresh context."""
+import ctypes as C
+import time
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from cudaraytracer_b200 import Renderer, Scene, capi
+
+pytestmark = pytest.mark.gpu
+
+
+def _lists(scene):
+    d = scene.desc
+    hs = [dict(type=h.type, active=h.active, cx=h.cx, cy=h.cy, cz=h.cz, a=h.a, b=h.b, material=h.material)
+          for h in (d.hittables[i] for i in range(d.n_hittables))]
+    ms = [dict(type=m.type, texture=m.texture, param=m.param, light_intensity=m.light_intensity) for m in (d.materials[i] for i in range(d.n_materials))]
+    ts = [dict(type=t.type, image=t.image, color=tuple(t.color), odd=tuple(t.odd), even=tuple(t.even)) for t in (d.textures[i] for i in range(d.n_textures))]
+    return hs, ms, ts
+
+
+def _fresh(scene, cam, W, H, spp=4):
+    r = Renderer(0)
+    r.upload(scene); r.set_camera(cam); r.resize(W, H)
+    ids = r.primary_ids()
+    r.render(spp=spp, max_depth=50)
+    acc = r.read_accum()
+    r.close()
+    return ids, acc
+
+
+def test_refit_and_rebuild_match_a_fresh_upload():
+    W, H = 200, 113
+    base = Scene.generate(capi.SCENE_RTIOW, 1984)
+    cam = base.default_camera(W, H)
+    hs, ms, ts = _lists(base)
+    r = Renderer(0)
+    r.upload(base); r.set_camera(cam); r.resize(W, H)
+    rng = np.random.default_rng(11)
+    # 1. move / resize 80 spheres, re-assign some materials: topology kept -> refit
+    for i in rng.choice(np.arange(1, len(hs)), 80, replace=False):
+        h = hs[int(i)]
+        h["cx"] += float(rng.uniform(-0.6, 0.6)); h["cz"] += float(rng.uniform(-0.6, 0.6)); h["cy"] += float(rng.uniform(0, 0.4))
+        h["a"] *= float(rng.uniform(0.6, 1.6))
+        if rng.random() < 0.3: h["material"] = int(rng.integers(0, len(ms)))
+        r.edit_hittable(int(i), **h)
+    assert r.commit() is False
+    edited = Scene.from_arrays(hs, ms, ts)
+    ref_ids = O.oracle_render(edited, cam, W, H, 0, 50, want_ids=True, want_rgba=False, want_mean=False)["ids"]
+    ids = r.primary_ids()
+    assert np.array_equal(ids, ref_ids), f"{(ids != ref_ids).sum()} IDs differ from the oracle after the refit"
+    r.render(spp=4, max_depth=50)
+    f_ids, f_acc = _fresh(edited, cam, W, H)
+    assert np.array_equal(f_ids, ids)
+    assert np.array_equal(r.read_accum().view(np.uint32), f_acc.view(np.uint32)), "refit scene renders differently from a fresh upload"
+    # 2. edit a MATERIAL (type change Lambertian -> Metal): every primitive that uses it gets a new record and leaf code
+    ms[hs[5]["material"]] = dict(type=capi.METAL, texture=ms[hs[5]["material"]]["texture"], param=0.1, light_intensity=0)
+    r.edit_material(hs[5]["material"], **ms[hs[5]["material"]])
+    assert r.commit() is False
+    r.clear(); r.render(spp=4, max_depth=50)
+    edited = Scene.from_arrays(hs, ms, ts)
+    _, f_acc = _fresh(edited, cam, W, H)
+    assert np.array_equal(r.read_accum().view(np.uint32), f_acc.view(np.uint32))
+    # 3. delete three spheres (isActive = false, CudaLayer.cpp:1372-1387) and turn one into a rect: topology changes -> rebuild
+    for i in (7, 100, 300):
+        hs[i]["active"] = 0
+        r.edit_hittable(i, **hs[i])
+    hs[50].update(type=capi.XZRECT, a=1.5, b=1.5, cy=0.7)
+    r.edit_hittable(50, **hs[50])
+    assert r.commit() is True
+    edited = Scene.from_arrays(hs, ms, ts)
+    ref_ids = O.oracle_render(edited, cam, W, H, 0, 50, want_ids=True, want_rgba=False, want_mean=False)["ids"]
+    ids = r.primary_ids()
+    assert np.array_equal(ids, ref_ids) and not np.isin(ids, [7, 100, 300]).any()
+    r.clear(); r.render(spp=4, max_depth=50)
+    _, f_acc = _fresh(edited, cam, W, H)
+    assert np.array_equal(r.read_accum().view(np.uint32), f_acc.view(np.uint32))
+    # 4. nothing staged: commit is a no-op; bad edits are refused
+    assert r.commit() is False
+    from cudaraytracer_b200 import CrtError
+    with pytest.raises(CrtError):
+        r.edit_hittable(len(hs), **hs[0])
+    with pytest.raises(CrtError):
+        r.edit_hittable(0, **dict(hs[0], material=len(ms)))
+    r.close()
+
+
+def test_refit_of_a_large_scene_is_much_cheaper_than_a_rebuild():
+    """300 x 300 grid (90 001 spheres): moving 2000 of them and refitting on the GPU vs rebuilding on the host."""
+    W, H = 160, 90
+    s = Scene.generate(capi.SCENE_GRID_1M, 1984, 300)
+    cam = s.default_camera(W, H)
+    hs, ms, ts = _lists(s)
+    r = Renderer(0)
+    r.upload(s); r.set_camera(cam); r.resize(W, H)
+    rng = np.random.default_rng(2)
+    for i in rng.choice(np.arange(1, len(hs)), 2000, replace=False):
+        h = hs[int(i)]
+        h["cy"] += float(rng.uniform(0.0, 3.0)); h["a"] *= float(rng.uniform(0.8, 3.0))
+        r.edit_hittable(int(i), **h)
+    t0 = time.perf_counter(); rebuilt = r.commit(); t_refit = time.perf_counter() - t0
+    assert rebuilt is False
+    ids = r.primary_ids()
+    edited = Scene.from_arrays(hs, ms, ts)
+    ref_ids = O.oracle_render(edited, cam, W, H, 0, 50, want_ids=True, want_rgba=False, want_mean=False, accel=O.BRUTE_FORCE)["ids"]
+    assert np.array_equal(ids, ref_ids)
+    t0 = time.perf_counter(); assert r.commit(force_rebuild=True) is True; t_rebuild = time.perf_counter() - t0
+    assert np.array_equal(r.primary_ids(), ref_ids)
+    print(f"refit {t_refit * 1e3:.2f} ms vs rebuild {t_rebuild * 1e3:.2f} ms")
+    assert t_refit < t_rebuild
+    r.close()
