@@ -442,7 +442,7 @@ crt_status crt_bvh_build_check(const crt_scene_desc* scene, crt_bvh_stats* out)
     *out = P.stats;
     const size_t nn = P.nodes.size(), np = P.stats.n_prims;
     std::vector<int> seen(np ? np : 1, 0);
-    struct Item { int node; float lo[3], hi[3]; };
+    struct Item { int node; double lo[3], hi[3]; };
     std::vector<Item> st;
     Item root;
     root.node = 0;
@@ -456,10 +456,17 @@ crt_status crt_bvh_build_check(const crt_scene_desc* scene, crt_bvh_stats* out)
         if (++visited > nn) return crt_set_error(nullptr, CRT_ERR_INVALID, "bvh check: cycle or shared node");
         const CrtPackedNode& n = P.nodes[it.node];
         for (int c = 0; c < 2; c++) {
-            const float* b = n.w + 6 * c;
+            // stored as centre / half-extent; a child may stick out of its parent by the rounding of the two conversions
+            double b[6];
+            for (int i = 0; i < 3; i++) {
+                b[i] = (double)n.w[6 * c + i] - (double)n.w[6 * c + 3 + i];
+                b[3 + i] = (double)n.w[6 * c + i] + (double)n.w[6 * c + 3 + i];
+            }
             if (np >= 2)
-                for (int i = 0; i < 3; i++)
-                    if (b[i] < it.lo[i] || b[3 + i] > it.hi[i]) return crt_set_error(nullptr, CRT_ERR_INVALID, "bvh check: child box outside its parent's box");
+                for (int i = 0; i < 3; i++) {
+                    const double tol = 1e-6 * (fabs(b[i]) + fabs(b[3 + i])) + 1e-30;
+                    if (b[i] < it.lo[i] - tol || b[3 + i] > it.hi[i] + tol) return crt_set_error(nullptr, CRT_ERR_INVALID, "bvh check: child box outside its parent's box");
+                }
             if (n.child[c] >= 0) {
                 Item ch;
                 ch.node = n.child[c];
@@ -475,7 +482,7 @@ crt_status crt_bvh_build_check(const crt_scene_desc* scene, crt_bvh_stats* out)
                 if ((code >> CRT_LEAF_TYPE_SHIFT) == CRT_SPHERE) {
                     const float r = fabsf(pr[3]);
                     for (int i = 0; i < 3; i++)
-                        if (pr[i] - r < b[i] || pr[i] + r > b[3 + i]) return crt_set_error(nullptr, CRT_ERR_INVALID, "bvh check: sphere outside its leaf box");
+                        if ((double)pr[i] - r < b[i] || (double)pr[i] + r > b[3 + i]) return crt_set_error(nullptr, CRT_ERR_INVALID, "bvh check: sphere outside its leaf box");
                 }
             }
         }

@@ -14,9 +14,11 @@ crt_status crt_set_error(crt_context* ctx, crt_status st, const char* msg);
 // Packed device scene (what the kernels read). Built on the host by scene_pack.cpp.
 //
 // BVH2, one primitive per leaf. Node = 64 bytes = 4 x 128-bit words:
-//   w0 = {c0.lo.x, c0.lo.y, c0.lo.z, c0.hi.x}
-//   w1 = {c0.hi.y, c0.hi.z, c1.lo.x, c1.lo.y}
-//   w2 = {c1.lo.z, c1.hi.x, c1.hi.y, c1.hi.z}
+//   child boxes as CENTRE c and HALF-EXTENT h (rounded outwards): with t_mid = c * (1/d) - o * (1/d) per axis, the slab
+//   interval of an axis is t_mid -/+ h * |1/d| whatever the sign of d, so the test needs no per-plane min/max
+//   w0 = {c0.c.x, c0.c.y, c0.c.z, c0.h.x}
+//   w1 = {c0.h.y, c0.h.z, c1.c.x, c1.c.y}
+//   w2 = {c1.c.z, c1.h.x, c1.h.y, c1.h.z}
 //   w3 = {child0, child1, 0, 0} (int bits)
 // child >= 0: index of an inner node. child < 0: leaf, ~child = (type << 28) | (material type << 26) | prim index.
 // Nodes are stored breadth-first so the first K nodes are the hottest (they are staged in shared memory).

@@ -37,6 +37,14 @@ __global__ void k_apply_edits(const EditRec* __restrict__ e, int n, float4* prim
 __device__ __forceinline__ float refit_pad_lo(float v, float abs_pad) { return v - (fabsf(v) * 4e-6f + abs_pad); }
 __device__ __forceinline__ float refit_pad_hi(float v, float abs_pad) { return v + (fabsf(v) * 4e-6f + abs_pad); }
 
+// Boxes are stored as centre / half-extent (crt_internal.h); h is rounded up so that [c - h, c + h] contains [lo, hi].
+__device__ __forceinline__ void refit_store(float* box, int axis, float lo, float hi)
+{
+    const float c = __fadd_rn(__fmul_rn(0.5f, lo), __fmul_rn(0.5f, hi));
+    box[axis] = c;
+    box[3 + axis] = fmaxf(__fsub_ru(hi, c), __fsub_ru(c, lo));
+}
+
 __global__ void k_bvh_refit(float4* nodes, const float4* __restrict__ prims, const float* __restrict__ prim_k,
                             const int* __restrict__ parent, const int* __restrict__ leaf_ref, unsigned int* visits, int n_prims,
                             float abs_pad)
@@ -62,12 +70,8 @@ __global__ void k_bvh_refit(float4* nodes, const float4* __restrict__ prims, con
         lo[na] = k - 0.0001f; hi[na] = k + 0.0001f;
     }
     float* slot = nd + 6 * (ref & 1);
-    for (int a = 0; a < 3; a++) {
-        lo[a] = refit_pad_lo(lo[a], abs_pad);
-        hi[a] = refit_pad_hi(hi[a], abs_pad);
-        slot[a] = lo[a];
-        slot[3 + a] = hi[a];
-    }
+    for (int a = 0; a < 3; a++)
+        refit_store(slot, a, refit_pad_lo(lo[a], abs_pad), refit_pad_hi(hi[a], abs_pad));
     // climb: the second thread to reach a node owns both of its child boxes
     while (true) {
         const int node = ref >> 1;
@@ -78,10 +82,9 @@ __global__ void k_bvh_refit(float4* nodes, const float4* __restrict__ prims, con
         if (up < 0) return; // the root's own box is not stored anywhere
         const volatile float* c = reinterpret_cast<const volatile float*>(nodes + 4 * (size_t)node);
         float* dst = reinterpret_cast<float*>(nodes + 4 * (size_t)(up >> 1)) + 6 * (up & 1);
-        for (int a = 0; a < 3; a++) {
-            dst[a] = fminf(c[a], c[6 + a]);
-            dst[3 + a] = fmaxf(c[3 + a], c[9 + a]);
-        }
+        for (int a = 0; a < 3; a++) // union of the two child boxes, each end rounded outwards
+            refit_store(dst, a, fminf(__fsub_rd(c[a], c[3 + a]), __fsub_rd(c[6 + a], c[9 + a])),
+                        fmaxf(__fadd_ru(c[a], c[3 + a]), __fadd_ru(c[6 + a], c[9 + a])));
         ref = up;
     }
 }

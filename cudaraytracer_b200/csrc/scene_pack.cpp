@@ -216,20 +216,36 @@ struct Builder
 inline float pad_lo(float v, float abs_pad) { return v - (fabsf(v) * 4e-6f + abs_pad); }
 inline float pad_hi(float v, float abs_pad) { return v + (fabsf(v) * 4e-6f + abs_pad); }
 
+// Boxes are stored as CENTRE + HALF-EXTENT {c.x, c.y, c.z, h.x, h.y, h.z} (crt_internal.h): the slab test then needs no
+// per-plane min/max (trace.cuh). The conversion rounds h UP, so [c - h, c + h] contains the padded [lo, hi].
+void crt_box_to_center_half(const float lo[3], const float hi[3], float out[6])
+{
+    for (int i = 0; i < 3; i++) {
+        const float c = 0.5f * lo[i] + 0.5f * hi[i];
+        const double hd = std::max((double)hi[i] - (double)c, (double)c - (double)lo[i]);
+        float h = (float)hd;
+        if ((double)h < hd) h = nextafterf(h, std::numeric_limits<float>::infinity());
+        out[i] = c;
+        out[3 + i] = h;
+    }
+}
+
 void store_box(float* w, int slot, const Box& b, bool empty, float abs_pad)
 {
     float v[6];
-    if (empty) {
+    if (empty) { // always hit: infinite half-extent
         for (int i = 0; i < 3; i++) {
-            v[i] = std::numeric_limits<float>::infinity();
-            v[3 + i] = -std::numeric_limits<float>::infinity();
+            v[i] = 0.f;
+            v[3 + i] = std::numeric_limits<float>::infinity();
         }
     }
     else {
+        float lo[3], hi[3];
         for (int i = 0; i < 3; i++) {
-            v[i] = pad_lo(b.lo[i], abs_pad);
-            v[3 + i] = pad_hi(b.hi[i], abs_pad);
+            lo[i] = pad_lo(b.lo[i], abs_pad);
+            hi[i] = pad_hi(b.hi[i], abs_pad);
         }
+        crt_box_to_center_half(lo, hi, v);
     }
     for (int i = 0; i < 6; i++)
         w[slot * 6 + i] = v[i];

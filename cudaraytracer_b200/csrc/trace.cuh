@@ -167,7 +167,8 @@ struct TravRay
 {
     float3 o, d;
     float3 id;   // reciprocal direction (components clamped away from zero so that 0 * inf never appears)
-    float3 ood;  // o * id, fast path only: the slab test becomes one FFMA per plane
+    float3 ood;  // o * id: the slab midpoint of an axis is one FFMA, c * id - ood
+    float3 aid;  // |id|: the slab half-width of an axis is h * aid
     float a;     // Dot(dir, dir), Hittable.cuh:83
     float inv_a; // fast path only
 };
@@ -184,16 +185,31 @@ template <bool EXACT> __device__ __forceinline__ TravRay trav_setup(float3 o, fl
     if (EXACT) {
         r.a = dot3_rn(d, d);
         r.inv_a = 0.f;
-        r.id = f3(div_rn(1.0f, dc.x), div_rn(1.0f, dc.y), div_rn(1.0f, dc.z));
-        r.ood = f3(0.f, 0.f, 0.f);
     }
     else {
         r.a = dot3(d, d);
         r.inv_a = fast_rcp(r.a);
-        r.id = f3(fast_rcp(dc.x), fast_rcp(dc.y), fast_rcp(dc.z));
-        r.ood = f3(o.x * r.id.x, o.y * r.id.y, o.z * r.id.z);
     }
+    // The box test only culls (the boxes are padded on the host), so it uses the same fast arithmetic in both paths;
+    // EXACT governs the primitive tests, which decide the result.
+    r.id = f3(fast_rcp(dc.x), fast_rcp(dc.y), fast_rcp(dc.z));
+    r.ood = f3(o.x * r.id.x, o.y * r.id.y, o.z * r.id.z);
+    r.aid = f3(fabsf(r.id.x), fabsf(r.id.y), fabsf(r.id.z));
     return r;
+}
+
+// Slab intervals of the two child boxes of a node (centre / half-extent form): per axis t_mid = c * id - ood and the
+// half-width h * |id|, so near = t_mid - hw, far = t_mid + hw for either sign of the direction: 9 FFMA + 2 three-input
+// min/max per box, instead of 6 FFMA + 10 min/max with lo/hi planes (the ALU pipe that runs min/max was the busiest one).
+__device__ __forceinline__ void slab2(const TravRay& r, float4 w0, float4 w1, float4 w2, float t_min, float t_hit, float& tn0, float& tf0,
+                                      float& tn1, float& tf1)
+{
+    const float mx0 = fmaf(w0.x, r.id.x, -r.ood.x), my0 = fmaf(w0.y, r.id.y, -r.ood.y), mz0 = fmaf(w0.z, r.id.z, -r.ood.z);
+    const float mx1 = fmaf(w1.z, r.id.x, -r.ood.x), my1 = fmaf(w1.w, r.id.y, -r.ood.y), mz1 = fmaf(w2.x, r.id.z, -r.ood.z);
+    tn0 = fmaxf(fmaxf(fmaf(-w0.w, r.aid.x, mx0), fmaf(-w1.x, r.aid.y, my0)), fmaxf(fmaf(-w1.y, r.aid.z, mz0), t_min));
+    tf0 = fminf(fminf(fmaf(w0.w, r.aid.x, mx0), fmaf(w1.x, r.aid.y, my0)), fminf(fmaf(w1.y, r.aid.z, mz0), t_hit));
+    tn1 = fmaxf(fmaxf(fmaf(-w2.y, r.aid.x, mx1), fmaf(-w2.z, r.aid.y, my1)), fmaxf(fmaf(-w2.w, r.aid.z, mz1), t_min));
+    tf1 = fminf(fminf(fmaf(w2.y, r.aid.x, mx1), fmaf(w2.z, r.aid.y, my1)), fminf(fmaf(w2.w, r.aid.z, mz1), t_hit));
 }
 
 // One inner-node visit: slab-test both child boxes against (t_min, t_hit), descend into the nearer hit child and push the
@@ -204,23 +220,8 @@ __device__ __forceinline__ void node_step(const SceneView& S, const TravRay& r, 
     float4 w0, w1, w2;
     int2 ch;
     load_node<SMEM_ALL>(S, cur, w0, w1, w2, ch);
-    float lx0, ly0, lz0, hx0, hy0, hz0, lx1, ly1, lz1, hx1, hy1, hz1;
-    if (EXACT) {
-        lx0 = (w0.x - r.o.x) * r.id.x; ly0 = (w0.y - r.o.y) * r.id.y; lz0 = (w0.z - r.o.z) * r.id.z;
-        hx0 = (w0.w - r.o.x) * r.id.x; hy0 = (w1.x - r.o.y) * r.id.y; hz0 = (w1.y - r.o.z) * r.id.z;
-        lx1 = (w1.z - r.o.x) * r.id.x; ly1 = (w1.w - r.o.y) * r.id.y; lz1 = (w2.x - r.o.z) * r.id.z;
-        hx1 = (w2.y - r.o.x) * r.id.x; hy1 = (w2.z - r.o.y) * r.id.y; hz1 = (w2.w - r.o.z) * r.id.z;
-    }
-    else {
-        lx0 = fmaf(w0.x, r.id.x, -r.ood.x); ly0 = fmaf(w0.y, r.id.y, -r.ood.y); lz0 = fmaf(w0.z, r.id.z, -r.ood.z);
-        hx0 = fmaf(w0.w, r.id.x, -r.ood.x); hy0 = fmaf(w1.x, r.id.y, -r.ood.y); hz0 = fmaf(w1.y, r.id.z, -r.ood.z);
-        lx1 = fmaf(w1.z, r.id.x, -r.ood.x); ly1 = fmaf(w1.w, r.id.y, -r.ood.y); lz1 = fmaf(w2.x, r.id.z, -r.ood.z);
-        hx1 = fmaf(w2.y, r.id.x, -r.ood.x); hy1 = fmaf(w2.z, r.id.y, -r.ood.y); hz1 = fmaf(w2.w, r.id.z, -r.ood.z);
-    }
-    const float tn0 = fmaxf(fmaxf(fminf(lx0, hx0), fminf(ly0, hy0)), fmaxf(fminf(lz0, hz0), t_min));
-    const float tf0 = fminf(fminf(fmaxf(lx0, hx0), fmaxf(ly0, hy0)), fminf(fmaxf(lz0, hz0), t_hit));
-    const float tn1 = fmaxf(fmaxf(fminf(lx1, hx1), fminf(ly1, hy1)), fmaxf(fminf(lz1, hz1), t_min));
-    const float tf1 = fminf(fminf(fmaxf(lx1, hx1), fmaxf(ly1, hy1)), fminf(fmaxf(lz1, hz1), t_hit));
+    float tn0, tf0, tn1, tf1;
+    slab2(r, w0, w1, w2, t_min, t_hit, tn0, tf0, tn1, tf1);
     // The boxes are padded on the host (scene_pack.cpp); <= keeps degenerate (flat) boxes alive.
     const bool h0 = tn0 <= tf0;
     const bool h1 = tn1 <= tf1;
@@ -244,14 +245,8 @@ __device__ __forceinline__ void node_step_all(const SceneView& S, const TravRay&
     float4 w0, w1, w2;
     int2 ch;
     load_node<SMEM_ALL>(S, at ? cur : 0, w0, w1, w2, ch);
-    const float lx0 = fmaf(w0.x, r.id.x, -r.ood.x), ly0 = fmaf(w0.y, r.id.y, -r.ood.y), lz0 = fmaf(w0.z, r.id.z, -r.ood.z);
-    const float hx0 = fmaf(w0.w, r.id.x, -r.ood.x), hy0 = fmaf(w1.x, r.id.y, -r.ood.y), hz0 = fmaf(w1.y, r.id.z, -r.ood.z);
-    const float lx1 = fmaf(w1.z, r.id.x, -r.ood.x), ly1 = fmaf(w1.w, r.id.y, -r.ood.y), lz1 = fmaf(w2.x, r.id.z, -r.ood.z);
-    const float hx1 = fmaf(w2.y, r.id.x, -r.ood.x), hy1 = fmaf(w2.z, r.id.y, -r.ood.y), hz1 = fmaf(w2.w, r.id.z, -r.ood.z);
-    const float tn0 = fmaxf(fmaxf(fminf(lx0, hx0), fminf(ly0, hy0)), fmaxf(fminf(lz0, hz0), t_min));
-    const float tf0 = fminf(fminf(fmaxf(lx0, hx0), fmaxf(ly0, hy0)), fminf(fmaxf(lz0, hz0), t_hit));
-    const float tn1 = fmaxf(fmaxf(fminf(lx1, hx1), fminf(ly1, hy1)), fmaxf(fminf(lz1, hz1), t_min));
-    const float tf1 = fminf(fminf(fmaxf(lx1, hx1), fmaxf(ly1, hy1)), fminf(fmaxf(lz1, hz1), t_hit));
+    float tn0, tf0, tn1, tf1;
+    slab2(r, w0, w1, w2, t_min, t_hit, tn0, tf0, tn1, tf1);
     const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
     const bool swap = tn1 < tn0;
     const int first = (h0 && !(h1 && swap)) ? ch.x : ch.y; // the nearer hit child (or the only one)
