@@ -100,20 +100,36 @@ class ClockSampler:
                 "reasons": sorted(reasons)}
 
 
-def cpu_reference_lib():
+# BVHNode::Hit keeps 16 stack entries with no overflow check (Hittable.cuh:399): the reference's own code, host or CUDA build,
+# smashes its stack on scenes much above 60 k hittables (SURVEY.md appendix probes). Above this size the CPU baseline is the
+# oracle port (same algorithm, 64 entries) and the reference CUDA kernel is reported as unavailable.
+# Image::value casts u * width with u = NaN at sphere poles (Texture.cuh:88-89, acos in Hittable.cuh:119-125): defined on the
+# GPU (-> 0), undefined on the host, where the reference's headers segfault on the textured scene from 4 spp up. Scenes with
+# image textures therefore also use the port, which applies the GPU's conversion (oracle/oracle.c f2i_gpu).
+REFERENCE_MAX_HITTABLES = 60000
+
+
+def cpu_reference_lib(scene):
     import oracle_lib as O
-    if O.have_refhost():
+    if O.have_refhost() and scene.n_hittables <= REFERENCE_MAX_HITTABLES and int(scene.desc.n_images) == 0:
         return "reference", O.refhost_render
     return "port", O.oracle_render
 
 
 def time_cpu_baseline(scene, cam, W, H, depth, sample_spp, threads):
     """The reference's CPU implementation of the path on the host cores, on a bounded sample of the workload."""
-    kind, fn = cpu_reference_lib()
+    kind, fn = cpu_reference_lib(scene)
     t0 = time.perf_counter()
     out = fn(scene, cam, W, H, sample_spp, depth, threads=threads, want_rgba=True, want_mean=False)
     dt = time.perf_counter() - t0
     return kind, out["rays"] / dt / 1e6, dt, out["rays"]
+
+
+def cpu_sample_spp(scene, cam, W, H, depth, spp, cap, threads, budget_s=10.0):
+    """spp of the bounded CPU sample: one calibration pass at 1 spp (also the warm-up of the host code), then as many spp as
+    fit into about budget_s seconds, at most `cap` and at most the workload's own spp."""
+    _, _, t1, _ = time_cpu_baseline(scene, cam, W, H, depth, 1, threads)
+    return max(1, min(spp, cap, int(budget_s / max(t1, 1e-3))))
 
 
 def run_reference_arm(args):
@@ -127,7 +143,7 @@ def run_reference_arm(args):
     cam = scene.default_camera(W, H)
     threads = os.cpu_count() or 1
     # bounded sample: the full frame at a reduced spp (the rate in Mrays/s does not depend on spp)
-    sample_spp = max(1, min(spp, args.cpu_spp))
+    sample_spp = cpu_sample_spp(scene, cam, W, H, depth, spp, args.cpu_spp, threads)
     rates, times = [], []
     kind = "port"
     for i in range(args.warmup + args.steps):
@@ -301,7 +317,7 @@ def run_gpu_arm(args):
         cpu = None
         if world == 1 and not args.no_cpu:
             threads = os.cpu_count() or 1
-            sample_spp = max(1, min(spp, args.cpu_spp))
+            sample_spp = cpu_sample_spp(scene, cam, W, H, depth, spp, args.cpu_spp, threads)
             kind, mr, dt, _ = time_cpu_baseline(scene, cam, W, H, depth, sample_spp, threads)
             cpu = {"value": mr, "unit": "Mrays/s", "cores": threads, "kind": kind, "seconds": dt,
                    "sample": f"{W}x{H} at {sample_spp} spp of {spp} (depth {depth})"}
@@ -309,7 +325,9 @@ def run_gpu_arm(args):
         refk = None
         if world == 1 and not args.no_refkernel:
             import oracle_lib as O
-            if O.have_refkernel():
+            if scene.n_hittables > REFERENCE_MAX_HITTABLES:
+                refk = {"unavailable": "the reference traversal's stack[16] overflows at this scene size (Hittable.cuh:399)"}
+            elif O.have_refkernel():
                 rk_spp = max(1, min(spp, args.refkernel_spp))
                 _, ms = O.refkernel_render(scene, cam, W, H, rk_spp, depth, reps=3)
                 covered = (W // 16 * 16) * (H // 16 * 16)
@@ -349,7 +367,7 @@ def main():
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--variant", default="auto", choices=["auto", "mega", "wavefront", "pipeline"])
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (debug only)")
-    ap.add_argument("--cpu-spp", type=int, default=8, help="spp of the bounded CPU-baseline sample")
+    ap.add_argument("--cpu-spp", type=int, default=32, help="upper bound of the spp of the bounded CPU-baseline sample (about 10 s of host work)")
     ap.add_argument("--refkernel-spp", type=int, default=64, help="spp of the bounded reference-CUDA-kernel sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-refkernel", action="store_true")

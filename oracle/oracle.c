@@ -377,6 +377,19 @@ static inline int world_hit(const oscene* S, const ray* r, float t_min, float t_
 }
 
 /* ---------------------------------------------------------------- textures, Texture.cuh:42-105 */
+/* float -> int as the GPU performs it (cvt.rzi.s32.f32: NaN -> 0, saturating). Image::value (Texture.cuh:88-89) converts
+ * u * width and v * height with a plain cast; GetSphereUV (Hittable.cuh:119-125) yields NaN at a sphere's poles when
+ * |normal.y| rounds above 1 (acos), and the cast of NaN is undefined on the host: the reference's headers compiled for x86
+ * index the texel array with INT_MIN there and crash (seen on the textured scene from 4 spp up). The kernel this oracle
+ * stands for is the CUDA build, so the conversion follows the GPU. */
+static int f2i_gpu(float x)
+{
+    if (x != x) return 0;
+    if (x >= 2147483648.0f) return 2147483647;
+    if (x <= -2147483648.0f) return (-2147483647 - 1);
+    return (int)x;
+}
+
 static v3 texture_value(const oscene* S, const crt_texture* t, float u, float v, v3 p)
 {
     if (t->type == CRT_CONSTANT)
@@ -393,8 +406,8 @@ static v3 texture_value(const oscene* S, const crt_texture* t, float u, float v,
         return V3(0, 1, 1);
     u = clampf(u, 0.0f, 1.0f);
     v = 1.0f - clampf(v, 0.0f, 1.0f);
-    int i = (int)(u * im->width);
-    int j = (int)(v * im->height);
+    int i = f2i_gpu(u * im->width);
+    int j = f2i_gpu(v * im->height);
     if (i >= im->width) i = im->width - 1;
     if (j >= im->height) j = im->height - 1;
     const float color_scale = 1.0f / 255.0f;
