@@ -259,6 +259,7 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
     }
     // images: RGB8 -> RGBA8 so a texel is one aligned 32-bit load
     std::vector<DevImage> himg(keep_images ? 0 : sd->n_images);
+    std::vector<unsigned char*> raw_rgb;
     for (uint64_t i = 0; i < himg.size(); i++) {
         const crt_image& im = sd->images[i];
         himg[i].texels = nullptr;
@@ -266,13 +267,16 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
         himg[i].height = im.height;
         if (!im.pixels || im.width <= 0 || im.height <= 0) continue;
         size_t npx = (size_t)im.width * im.height;
-        std::vector<uchar4> rgba(npx);
-        for (size_t k = 0; k < npx; k++) rgba[k] = make_uchar4(im.pixels[3 * k], im.pixels[3 * k + 1], im.pixels[3 * k + 2], 255);
         uchar4* d = nullptr;
+        unsigned char* raw = nullptr; // RGB8 as given; expanded on the device
         CU(cudaMalloc(&d, npx * 4));
         ctx->d_texels.push_back(d);
-        CU(cudaMemcpy(d, rgba.data(), npx * 4, cudaMemcpyHostToDevice));
-        h2d += npx * 4;
+        CU(cudaMalloc(&raw, (npx * 3 + 15) & ~(size_t)15));
+        raw_rgb.push_back(raw);
+        CU(cudaMemcpyAsync(raw, im.pixels, npx * 3, cudaMemcpyHostToDevice, ctx->stream));
+        k_rgb_to_rgba<<<(unsigned)((npx / 4 + 1 + 255) / 256), 256, 0, ctx->stream>>>(reinterpret_cast<const uint32_t*>(raw), d, npx);
+        CU(cudaGetLastError());
+        h2d += npx * 3;
         himg[i].texels = d;
     }
     if (!keep_images) {
@@ -280,6 +284,7 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
         if (!himg.empty()) CU(cudaMemcpy(ctx->d_images, himg.data(), himg.size() * sizeof(DevImage), cudaMemcpyHostToDevice));
     }
     CU(cudaStreamSynchronize(ctx->stream));
+    for (unsigned char* p : raw_rgb) cudaFree(p);
     // bookkeeping for edits
     ctx->slot_of.assign(sd->n_hittables, -1);
     for (size_t sl = 0; sl < np; sl++)

@@ -191,6 +191,27 @@ __global__ void k_accum_to_float(const long long* __restrict__ accum, float4* __
     out[i] = make_float4(crt_from_fixed(rg.x), crt_from_fixed(rg.y), crt_from_fixed(bn.x), (float)bn.y);
 }
 
+// Image texels arrive as tightly packed RGB8 (stb_image's layout, RawStbImage.h:11-22); the kernels fetch one aligned RGBA8
+// word per lookup. One thread expands 4 texels: three 32-bit loads, one 128-bit store.
+__global__ void k_rgb_to_rgba(const uint32_t* __restrict__ rgb, uchar4* __restrict__ rgba, size_t n_px)
+{
+    const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t p = 4 * g;
+    if (p + 4 <= n_px) {
+        const uint32_t a = rgb[3 * g], b = rgb[3 * g + 1], c = rgb[3 * g + 2];
+        uint4 o;
+        o.x = (a & 0x00ffffffu) | 0xff000000u;
+        o.y = ((a >> 24) | (b << 8)) & 0x00ffffffu | 0xff000000u;
+        o.z = ((b >> 16) | (c << 16)) & 0x00ffffffu | 0xff000000u;
+        o.w = (c >> 8) | 0xff000000u;
+        reinterpret_cast<uint4*>(rgba)[g] = o;
+    }
+    else if (p < n_px) {
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(rgb);
+        for (size_t k = p; k < n_px; k++) rgba[k] = make_uchar4(src[3 * k], src[3 * k + 1], src[3 * k + 2], 255);
+    }
+}
+
 __global__ void k_clear(longlong2* __restrict__ accum, uint32_t n2)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
