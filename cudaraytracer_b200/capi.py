@@ -124,6 +124,10 @@ SIGNATURES = {
     "crt_flycam_step": (C.c_int, [C.POINTER(FlyCam), C.c_uint32, C.c_float, C.c_float, C.c_float, C.POINTER(C.c_int)]),
     "crt_flycam_inputs": (C.c_int, [C.POINTER(FlyCam), C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(InputStruct)]),
     "crt_load_ppm": (C.c_int, [C.c_char_p, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "crt_decode_jpeg": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                  C.POINTER(C.c_int32)]),
+    "crt_load_image": (C.c_int, [C.c_char_p, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                 C.POINTER(C.c_int32)]),
     "crt_free": (None, [_P]),
     "crt_write_ppm": (C.c_int, [C.c_char_p, _P, C.c_uint32, C.c_uint32, C.c_int]),
     # include/crt_legacy.h

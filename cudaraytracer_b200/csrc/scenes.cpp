@@ -13,6 +13,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <string>
 #include <vector>
 
 struct crt_scene_builder
@@ -119,6 +120,25 @@ int AddProceduralImage(crt_scene_builder* b, int w, int h, uint32_t salt)
     return (int)b->images.size() - 1;
 }
 
+// The reference's own texture files when the caller points CRT_ASSET_DIR at its assets/textures directory (the JPEG decoder
+// of jpeg_decode.cpp stands in for stbi_load, RawStbImage.h:11-22); -1 if the variable is unset or the file cannot be decoded.
+int AddImageFromAssetDir(crt_scene_builder* b, const char* file)
+{
+    const char* dir = getenv("CRT_ASSET_DIR");
+    if (!dir || !*dir) return -1;
+    const std::string path = std::string(dir) + "/" + file;
+    uint8_t* px = nullptr;
+    int32_t w = 0, h = 0, n = 0;
+    if (crt_load_image(path.c_str(), &px, &w, &h, &n) != CRT_OK) return -1;
+    b->image_store.emplace_back(px, px + (size_t)w * h * 3);
+    crt_free(px);
+    crt_image im;
+    im.pixels = b->image_store.back().data();
+    im.width = w; im.height = h;
+    b->images.push_back(im);
+    return (int)b->images.size() - 1;
+}
+
 void LookAt(crt_scene_builder* b, float px, float py, float pz, float tx, float ty, float tz)
 {
     float d[3] = {tx - px, ty - py, tz - pz};
@@ -172,8 +192,12 @@ void GenTextured(crt_scene_builder* B, uint64_t seed, uint64_t size_hint)
     if (small < 8) small = 8;
     const float odd[3] = {0.2f, 0.3f, 0.1f}, even[3] = {0.9f, 0.9f, 0.9f}; // CudaLayer.cpp:157-160
     B->image_store.reserve(2);
-    int img_big = AddProceduralImage(B, big_w, big_w / 2, 1);
-    int img_small = AddProceduralImage(B, small, small, 2);
+    // SURVEY.md 8d names assets/textures/8k_earth_nightmap.jpg and UTH-logo-english.jpg; they are used when present
+    // (CRT_ASSET_DIR, default size only), the procedural stand-ins of the same dimensions otherwise
+    int img_big = size_hint ? -1 : AddImageFromAssetDir(B, "8k_earth_nightmap.jpg");
+    if (img_big < 0) img_big = AddProceduralImage(B, big_w, big_w / 2, 1);
+    int img_small = size_hint ? -1 : AddImageFromAssetDir(B, "UTH-logo-english.jpg");
+    if (img_small < 0) img_small = AddProceduralImage(B, small, small, 2);
     AddHittable(B, CRT_SPHERE, 0.f, -1000.f, 0.f, 1000.f, 0.f, AddMaterial(B, CRT_LAMBERTIAN, AddChecker(B, odd, even), 0.f, 0));
     AddHittable(B, CRT_SPHERE, 0.f, 2.f, 0.f, 2.0f, 0.f, AddMaterial(B, CRT_LAMBERTIAN, AddImageTexture(B, img_big), 0.f, 0));
     int k = 0;

@@ -8,6 +8,7 @@ accumulation buffer. All rendering happens in libcrt.so on the GPU.
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -104,6 +105,19 @@ class Scene:
             except Exception:
                 pass
             self._builder = None
+
+
+def load_image(path: str) -> np.ndarray:
+    """JPEG or binary PPM file -> (H, W, 3) uint8, the array Scene.from_arrays takes as an image texture.
+    The library's own decoder (csrc/jpeg_decode.cpp) in place of the reference's stbi_load (Utils/RawStbImage.h:11-22)."""
+    lib = capi.load()
+    px = C.POINTER(C.c_uint8)()
+    w, h, n = C.c_int32(), C.c_int32(), C.c_int32()
+    _check(lib.crt_load_image(os.fsencode(path), C.byref(px), C.byref(w), C.byref(h), C.byref(n)))
+    try:
+        return np.ctypeslib.as_array(px, shape=(h.value, w.value, 3)).copy()
+    finally:
+        lib.crt_free(px)
 
 
 def look_camera(position, orientation, fov_deg=45.0, near=0.1, far=10.0, up=(0.0, 1.0, 0.0),

@@ -234,6 +234,18 @@ crt_status crt_write_ppm(const char* path, const uint32_t* rgba8, uint32_t width
  * stb_image, Utils/RawStbImage.h:11-22, which is third-party code this library does not carry). *out_pixels is malloc'ed;
  * release it with crt_free. */
 crt_status crt_load_ppm(const char* path, uint8_t** out_pixels, int32_t* out_width, int32_t* out_height);
+/* JPEG in memory -> tightly packed RGB8 (csrc/jpeg_decode.cpp). Replaces stbi_load(filename, &w, &h, &n, 0) of LoadImage
+ * (Utils/RawStbImage.h:11-22, CudaLayer.cpp:896): baseline, extended-sequential and progressive Huffman JPEG, 8 bit, 1 or 3
+ * components, any integer sampling ratio, restart intervals; reconstruction arithmetic (integer IDCT, triangle chroma
+ * upsampling, fixed-point YCbCr matrix) bit-exact with the decoder the reference vendors. *out_file_channels (optional)
+ * receives the file's component count (stb's n); the output is RGB8 in both cases, a grey image is replicated into the three
+ * channels (the reference would read a 1-channel buffer with a 3-byte stride, Texture.cuh:76,102).
+ * CRT_ERR_UNSUPPORTED: arithmetic coding, 12-bit, lossless/hierarchical, 4 components. Release with crt_free. */
+crt_status crt_decode_jpeg(const uint8_t* data, uint64_t n_bytes, uint8_t** out_pixels, int32_t* out_width, int32_t* out_height,
+                           int32_t* out_file_channels);
+/* File loader for image textures: JPEG or binary PPM by magic number. */
+crt_status crt_load_image(const char* path, uint8_t** out_pixels, int32_t* out_width, int32_t* out_height,
+                          int32_t* out_file_channels);
 void       crt_free(void* p);
 
 #ifdef __cplusplus
