@@ -620,7 +620,7 @@ static size_t plan_smem(const crt_context* ctx, int blocks_per_sm, DevScene& S, 
     budget = std::min<long>(budget, ctx->smem_optin);
     if (ctx->smem_budget_override >= 0) budget = std::min<long>(ctx->smem_budget_override, ctx->smem_optin);
     budget = std::max<long>(budget, 0);
-    const long node_b = 64;
+    const long node_b = 64; // the megakernel keeps the unpadded word-major node table (trace.cuh)
     const long full = (long)S.n_nodes * node_b + (long)S.n_prims * 48;
     if (full <= budget) {
         S.smem_nodes = S.n_nodes; S.smem_prims = S.n_prims; S.smem_mats = S.n_prims;
@@ -723,7 +723,7 @@ static crt_status render_wavefront(crt_context* ctx, RenderArgs A)
     if (ctx->smem_budget_override >= 0) budget = std::min<long>(budget, ctx->smem_budget_override);
     size_t smem;
     {
-        const long full = (long)ext_scene.n_nodes * 64 + (long)ext_scene.n_prims * 16;
+        const long full = (long)ext_scene.n_nodes * 16 * CRT_SMEM_NODE_F4 + (long)ext_scene.n_prims * 16;
         if (full <= budget) {
             ext_scene.smem_nodes = ext_scene.n_nodes; ext_scene.smem_prims = ext_scene.n_prims; ext_scene.smem_mats = 0;
             all = true;
@@ -731,7 +731,7 @@ static crt_status render_wavefront(crt_context* ctx, RenderArgs A)
         }
         else {
             long rem = budget;
-            ext_scene.smem_nodes = (int)std::min<long>(ext_scene.n_nodes, rem / 64); rem -= (long)ext_scene.smem_nodes * 64;
+            ext_scene.smem_nodes = (int)std::min<long>(ext_scene.n_nodes, rem / (16 * CRT_SMEM_NODE_F4)); rem -= (long)ext_scene.smem_nodes * 16 * CRT_SMEM_NODE_F4;
             ext_scene.smem_prims = (int)std::min<long>(ext_scene.n_prims, rem / 16); rem -= (long)ext_scene.smem_prims * 16;
             ext_scene.smem_mats = 0;
             smem = (size_t)(budget - rem);
@@ -826,13 +826,14 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
 {
     const uint64_t P = (uint64_t)A.cover_w * A.cover_h;
     if (P == 0 || A.spp_count == 0) return CRT_OK;
-    // shared memory: [scene prefix][pool of N slots: 56 B of path state + 7 ring entries]
-    const long per_slot = 3 * 16 + 8 + 4 * PQ_COUNT;
+    // shared memory: [scene prefix][pool of N slots: 56 B of path state + 7 16-bit ring entries]
+    const long per_slot = 3 * 16 + 8 + 2 * PQ_COUNT;
+    const long node_b = 16 * CRT_SMEM_NODE_F4;
     const long budget = (ctx->smem_budget_override >= 0 ? std::min<long>(ctx->smem_budget_override, ctx->smem_optin) : (long)ctx->smem_optin) - 1024;
-    const long full = (long)A.scene.n_nodes * 64 + (long)A.scene.n_prims * 48;
+    const long full = (long)A.scene.n_nodes * node_b + (long)A.scene.n_prims * 48;
     int n_slots = ctx->pipe_slots > 0 ? ctx->pipe_slots : (full + 2048 * per_slot <= budget ? 2048 : 1024);
     while (n_slots & (n_slots - 1)) n_slots &= n_slots - 1; // power of two
-    n_slots = std::max(n_slots, 64);
+    n_slots = std::min(std::max(n_slots, 64), 32768); // ring entries are 16-bit slot ids, 0xffff = empty
     if ((long)n_slots * per_slot > budget) return crt_set_error(ctx, CRT_ERR_INVALID, "render_pipeline: CRT_PIPE_SLOTS does not fit in shared memory");
     bool all = false;
     long rem = budget - (long)n_slots * per_slot;
@@ -842,7 +843,7 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
         rem -= full;
     }
     else {
-        A.scene.smem_nodes = (int)std::min<long>(A.scene.n_nodes, rem / 64); rem -= (long)A.scene.smem_nodes * 64;
+        A.scene.smem_nodes = (int)std::min<long>(A.scene.n_nodes, rem / node_b); rem -= (long)A.scene.smem_nodes * node_b;
         A.scene.smem_prims = (int)std::min<long>(A.scene.n_prims, rem / 16); rem -= (long)A.scene.smem_prims * 16;
         A.scene.smem_mats = (int)std::min<long>(A.scene.n_prims, rem / 32); rem -= (long)A.scene.smem_mats * 32;
     }

@@ -80,7 +80,7 @@ template <bool EXACT, bool COUNT, bool SMEM_ALL>
 __global__ void __launch_bounds__(CRT_BLOCK_THREADS) k_render_mega(const __grid_constant__ RenderArgs A)
 {
     extern __shared__ float4 smem[];
-    const SceneView S = stage_scene(A.scene, smem);
+    const SceneView S = stage_scene<false>(A.scene, smem);
     __syncthreads();
 
     int x, y;
@@ -139,7 +139,7 @@ struct IdArgs
 template <bool SMEM_ALL> __global__ void __launch_bounds__(CRT_BLOCK_THREADS) k_primary_ids(const __grid_constant__ IdArgs A)
 {
     extern __shared__ float4 smem[];
-    const SceneView S = stage_scene(A.scene, smem);
+    const SceneView S = stage_scene<false>(A.scene, smem);
     __syncthreads();
     int x, y;
     tile_pixel((A.width + 15) / 16, x, y);

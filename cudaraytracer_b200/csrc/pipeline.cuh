@@ -21,7 +21,7 @@
 
 #define PIPE_THREADS 1024
 #define PIPE_WARPS (PIPE_THREADS / 32)
-#define PIPE_EMPTY (-1)
+#define PIPE_EMPTY 0xffffu // ring entries are 16-bit slot ids
 
 enum { PQ_EXT = 0, PQ_MISS = 1, PQ_LAMBERTIAN = 2, PQ_METAL = 3, PQ_DIELECTRIC = 4, PQ_LIGHT = 5, PQ_GEN = 6, PQ_COUNT = 7 };
 
@@ -52,14 +52,14 @@ struct PipePool
     float4* b; // {d.y, d.z, t_hit, leaf code (int bits)}
     float4* c; // {throughput rgb, bounce (uint bits)}
     uint2* px; // {pixel, sample}
-    int* ring; // PQ_COUNT rings of n_slots entries
+    unsigned short* ring; // PQ_COUNT rings of n_slots entries (16-bit: the rings are a third of the pool otherwise)
     unsigned int mask;
     int n;
 };
 
-__device__ __forceinline__ volatile int* pipe_entry(const PipePool& P, int q, unsigned int pos)
+__device__ __forceinline__ volatile unsigned short* pipe_entry(const PipePool& P, int q, unsigned int pos)
 {
-    return (volatile int*)(P.ring + q * P.n + (int)(pos & P.mask));
+    return (volatile unsigned short*)(P.ring + q * P.n + (int)(pos & P.mask));
 }
 
 // Warp-aggregated push of `slot` (where pred) into queue q. The pool writes of the pushing lanes must be complete.
@@ -71,7 +71,7 @@ __device__ __forceinline__ void pipe_push(const PipePool& P, PipeCtl* ctl, int q
     const int leader = __ffs(m) - 1;
     if ((int)(threadIdx.x & 31u) == leader) base = atomicAdd(&ctl->tail[q], (unsigned int)__popc(m));
     base = __shfl_sync(0xffffffffu, base, leader);
-    if (pred) *pipe_entry(P, q, base + __popc(m & lane_lt)) = slot;
+    if (pred) *pipe_entry(P, q, base + __popc(m & lane_lt)) = (unsigned short)slot;
 }
 
 // Push where every pushing lane names its own queue: lanes are grouped with match.any, one atomic per distinct queue.
@@ -83,7 +83,7 @@ __device__ __forceinline__ void pipe_push_binned(const PipePool& P, PipeCtl* ctl
     unsigned int base = 0;
     if (pred && (int)(threadIdx.x & 31u) == leader) base = atomicAdd(&ctl->tail[q], (unsigned int)__popc(grp));
     base = __shfl_sync(0xffffffffu, base, leader);
-    if (pred) *pipe_entry(P, q, base + __popc(grp & lane_lt)) = slot;
+    if (pred) *pipe_entry(P, q, base + __popc(grp & lane_lt)) = (unsigned short)slot;
 }
 
 // Orders this thread's shared-memory pool writes before its queue write. Shared-memory accesses of one thread are performed
@@ -108,11 +108,11 @@ __device__ __forceinline__ int pipe_pop(const PipePool& P, PipeCtl* ctl, int q, 
     n = __shfl_sync(0xffffffffu, n, 0);
     if (left) *left = __shfl_sync(0xffffffffu, avail, 0) - n; // entries the queue still held when this warp looked
     if (take && rank < n) {
-        volatile int* e = pipe_entry(P, q, h + (unsigned int)rank);
-        int v;
+        volatile unsigned short* e = pipe_entry(P, q, h + (unsigned int)rank);
+        unsigned int v;
         while ((v = *e) == PIPE_EMPTY) { } // the producer reserved this entry before us; its store is in flight
-        *e = PIPE_EMPTY;
-        slot = v;
+        *e = (unsigned short)PIPE_EMPTY;
+        slot = (int)v;
     }
     return n;
 }
@@ -229,19 +229,19 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
 {
     extern __shared__ float4 smem[];
     __shared__ PipeCtl ctl;
-    const SceneView S = stage_scene(A.R.scene, smem);
+    const SceneView S = stage_scene<true>(A.R.scene, smem);
     PipePool P;
     {
-        float4* p = smem + 4 * (size_t)A.R.scene.smem_nodes + A.R.scene.smem_prims + 2 * (size_t)A.R.scene.smem_mats;
+        float4* p = smem + CRT_SMEM_NODE_F4 * (size_t)A.R.scene.smem_nodes + A.R.scene.smem_prims + 2 * (size_t)A.R.scene.smem_mats;
         P.n = A.n_slots;
         P.mask = (unsigned int)A.n_slots - 1u;
         P.a = p; p += P.n;
         P.b = p; p += P.n;
         P.c = p; p += P.n;
         P.px = reinterpret_cast<uint2*>(p); p += P.n / 2;
-        P.ring = reinterpret_cast<int*>(p);
+        P.ring = reinterpret_cast<unsigned short*>(p);
     }
-    for (int i = threadIdx.x; i < PQ_COUNT * P.n; i += PIPE_THREADS) P.ring[i] = i >= PQ_GEN * P.n ? i - PQ_GEN * P.n : PIPE_EMPTY;
+    for (int i = threadIdx.x; i < PQ_COUNT * P.n; i += PIPE_THREADS) P.ring[i] = (unsigned short)(i >= PQ_GEN * P.n ? i - PQ_GEN * P.n : PIPE_EMPTY);
     if (threadIdx.x <= PQ_COUNT) { ctl.head[threadIdx.x] = 0u; ctl.tail[threadIdx.x] = threadIdx.x == PQ_GEN ? (unsigned int)P.n : 0u; }
     if (threadIdx.x == 0) ctl.live = P.n; // every slot starts in the GEN queue
     __syncthreads();

@@ -24,16 +24,31 @@ struct SceneView
     int smem_nodes, smem_prims, smem_mats;
 };
 
-template <bool SMEM_ALL> __device__ __forceinline__ void load_node(const SceneView& S, int i, float4& w0, float4& w1, float4& w2, int2& ch)
+// Two shared-memory layouts of the node table, both chosen so that lanes at different nodes spread over all eight 16-byte
+// bank groups (the 64-byte stride of the global layout puts word 0 of every node into two of them):
+//   PAD = false  word-major SoA: word k of node i at s_nodes[k * smem_nodes + i]. No wasted bytes: used by the megakernel,
+//                whose several resident CTAs each hold a scene copy.
+//   PAD = true   80-byte nodes: word k of node i at s_nodes[5 * i + k], the fifth word unused. 80 is an odd multiple of 16,
+//                and the four loads of a visit share ONE address register with immediate offsets (the SoA form needs an
+//                address computation per word): used by the one-CTA-per-SM kernels, where instruction issue is the bound.
+#define CRT_SMEM_NODE_F4 5
+
+template <bool SMEM_ALL, bool PAD>
+__device__ __forceinline__ void load_node(const SceneView& S, int i, float4& w0, float4& w1, float4& w2, int2& ch)
 {
     if (SMEM_ALL || i < S.smem_nodes) {
-        // shared-memory copy is SoA by word: word k of node i sits at s_nodes[k * smem_nodes + i], so lanes at
-        // different nodes spread over all eight 16-byte bank groups (the AoS 64-byte stride used only two of them)
-        const float4* p = S.s_nodes + i;
-        const int n = S.smem_nodes;
-        w0 = p[0]; w1 = p[n]; w2 = p[2 * n];
-        float4 w3 = p[3 * n];
-        ch = make_int2(__float_as_int(w3.x), __float_as_int(w3.y));
+        if (PAD) {
+            const float4* p = S.s_nodes + CRT_SMEM_NODE_F4 * i;
+            w0 = p[0]; w1 = p[1]; w2 = p[2];
+            ch = *reinterpret_cast<const int2*>(p + 3);
+        }
+        else {
+            const float4* p = S.s_nodes + i;
+            const int n = S.smem_nodes;
+            w0 = p[0]; w1 = p[n]; w2 = p[2 * n];
+            const float4 w3 = p[3 * n];
+            ch = make_int2(__float_as_int(w3.x), __float_as_int(w3.y));
+        }
     }
     else {
         const float4* p = S.g_nodes + 4 * (size_t)i;
@@ -63,16 +78,17 @@ template <bool SMEM_ALL> __device__ __forceinline__ void load_mat(const SceneVie
 }
 
 // Stages the first smem_* entries of each table into dynamic shared memory. Call from every thread, then __syncthreads().
-__device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem)
+template <bool PAD> __device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem)
 {
     SceneView S;
     S.g_nodes = D.nodes; S.g_prims = D.prims; S.g_prim_k = D.prim_k; S.g_mats = D.mats; S.images = D.images;
     S.smem_nodes = D.smem_nodes; S.smem_prims = D.smem_prims; S.smem_mats = D.smem_mats;
     float4* sn = smem;
-    float4* sp = sn + 4 * (size_t)D.smem_nodes;
+    float4* sp = sn + (PAD ? CRT_SMEM_NODE_F4 : 4) * (size_t)D.smem_nodes;
     float4* sm = sp + D.smem_prims;
     const int tid = threadIdx.x, nt = blockDim.x;
-    for (int i = tid; i < 4 * D.smem_nodes; i += nt) sn[(i & 3) * D.smem_nodes + (i >> 2)] = __ldg(D.nodes + i);
+    for (int i = tid; i < 4 * D.smem_nodes; i += nt)
+        sn[PAD ? CRT_SMEM_NODE_F4 * (i >> 2) + (i & 3) : (i & 3) * D.smem_nodes + (i >> 2)] = __ldg(D.nodes + i);
     for (int i = tid; i < D.smem_prims; i += nt) sp[i] = __ldg(D.prims + i);
     for (int i = tid; i < 2 * D.smem_mats; i += nt) sm[i] = __ldg(D.mats + i);
     S.s_nodes = sn; S.s_prims = sp; S.s_mats = sm;
@@ -214,12 +230,12 @@ __device__ __forceinline__ void slab2(const TravRay& r, float4 w0, float4 w1, fl
 
 // One inner-node visit: slab-test both child boxes against (t_min, t_hit), descend into the nearer hit child and push the
 // other. `cur` >= 0 on entry; on exit it is the next node (>= 0), a leaf (~code, < 0) or CRT_TRAV_DONE.
-template <bool EXACT, bool SMEM_ALL>
+template <bool EXACT, bool SMEM_ALL, bool PAD = false>
 __device__ __forceinline__ void node_step(const SceneView& S, const TravRay& r, float t_min, float t_hit, int& cur, int& sp, int* stack)
 {
     float4 w0, w1, w2;
     int2 ch;
-    load_node<SMEM_ALL>(S, cur, w0, w1, w2, ch);
+    load_node<SMEM_ALL, PAD>(S, cur, w0, w1, w2, ch);
     float tn0, tf0, tn1, tf1;
     slab2(r, w0, w1, w2, t_min, t_hit, tn0, tf0, tn1, tf1);
     // The boxes are padded on the host (scene_pack.cpp); <= keeps degenerate (flat) boxes alive.
@@ -244,7 +260,7 @@ __device__ __forceinline__ void node_step_all(const SceneView& S, const TravRay&
     const bool at = cur >= 0;
     float4 w0, w1, w2;
     int2 ch;
-    load_node<SMEM_ALL>(S, at ? cur : 0, w0, w1, w2, ch);
+    load_node<SMEM_ALL, true>(S, at ? cur : 0, w0, w1, w2, ch);
     float tn0, tf0, tn1, tf1;
     slab2(r, w0, w1, w2, t_min, t_hit, tn0, tf0, tn1, tf1);
     const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;

@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(WF_EXT_THREADS, 1) k_wf_extend(const __grid_co
 {
     extern __shared__ float4 smem[];
     __shared__ int s_cursor;
-    const SceneView S = stage_scene(A.R.scene, smem);
+    const SceneView S = stage_scene<true>(A.R.scene, smem);
     // This CTA's contiguous share of the slot pool; its warps take WF_BATCH slots at a time from a shared-memory cursor.
     const int per = (A.capacity + (int)gridDim.x - 1) / (int)gridDim.x;
     const int lo = min((int)blockIdx.x * per, A.capacity), hi = min(lo + per, A.capacity);
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(WF_EXT_THREADS, 1) k_wf_extend(const __grid_co
         if (act == 0u) break;
         // ---- traverse until fewer than THRESH lanes are busy (or, with nothing left to fetch, until all are done) ----
         do {
-            if (cur >= 0) node_step<false, SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
+            if (cur >= 0) node_step<false, SMEM_ALL, true>(S, r, t_min, h.t, cur, sp, stack);
             if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
             act = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
         } while (more ? __popc(act) >= THRESH : act != 0u);
