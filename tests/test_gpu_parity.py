@@ -321,3 +321,62 @@ def test_small_pool_progressive_and_sharded(monkeypatch, variant):
         assert (a[:48, :96, 3] == 2).all() and (a[48:, :, 3] == 0).all() and (a[:, 96:, 3] == 0).all()
     finally:
         r.close()
+
+
+@pytest.mark.gpu
+def test_edge_case_scenes_every_variant_bit_identical(renderer):
+    """Empty scene, one / two / three hittables (one inactive), rect-only scene: the wavefront and the pipelined kernel are
+    forced onto scenes AUTO would give to the megakernel, and must produce the same buffer."""
+    W, H = 41, 29
+    cam = look_camera((0, 0.3, 5), (0, -0.05, -1))
+    tex = [dict(type=capi.CONSTANT, color=(0.5, 0.6, 0.7)), dict(type=capi.CHECKER, odd=(0.2, 0.3, 0.1), even=(0.9, 0.9, 0.9))]
+    mat = [dict(type=capi.LAMBERTIAN, texture=0), dict(type=capi.DIELECTRIC, param=1.5), dict(type=capi.METAL, texture=1, param=0.1),
+           dict(type=capi.DIFFUSELIGHT, texture=0, light_intensity=3)]
+    hs = [dict(type=capi.SPHERE, cx=0, cy=0, cz=0, a=1.0, material=0, active=1),
+          dict(type=capi.SPHERE, cx=0.5, cy=0, cz=2, a=0.5, material=1, active=0),
+          dict(type=capi.SPHERE, cx=-1.5, cy=0, cz=1, a=0.4, material=1, active=1)]
+    rects = [dict(type=capi.XZRECT, cx=0, cy=-1, cz=0, a=8.0, b=8.0, material=2, active=1),
+             dict(type=capi.XYRECT, cx=0, cy=0, cz=-2, a=3.0, b=2.0, material=3, active=1),
+             dict(type=capi.YZRECT, cx=-2, cy=0, cz=0, a=2.0, b=2.0, material=0, active=1)]
+    scenes = [Scene.from_arrays([], [], [])] + [Scene.from_arrays(hs[:n], mat, tex) for n in (1, 2, 3)]
+    scenes += [Scene.from_arrays(rects, mat, tex), Scene.from_arrays(hs + rects, mat, tex)]
+    for k, sc in enumerate(scenes):
+        _setup(renderer, sc, cam, W, H)
+        renderer.render(spp=5, max_depth=20, variant=capi.VARIANT_MEGAKERNEL)
+        ref = renderer.read_accum()
+        assert (ref[..., 3] == 5).all()
+        for variant in (capi.VARIANT_WAVEFRONT, capi.VARIANT_PIPELINE):
+            renderer.clear()
+            renderer.render(spp=5, max_depth=20, variant=variant)
+            assert np.array_equal(ref.view(np.uint32), renderer.read_accum().view(np.uint32)), (k, variant)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kb", [12, 40])
+def test_partial_shared_memory_staging_bit_identical(monkeypatch, kb):
+    """Only a prefix of the node table in shared memory (the path the 1M-sphere scene takes: mixed shared / 256-bit global
+    node loads, primitives and materials from global memory) on a scene small enough to compare against full staging."""
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    W, H = 120, 67
+    cam = s.default_camera(W, H)
+    full = Renderer(0)
+    try:
+        _setup(full, s, cam, W, H)
+        full.render(spp=4, max_depth=50, variant=capi.VARIANT_MEGAKERNEL)
+        ref = full.read_accum()
+        ids = full.primary_ids()
+    finally:
+        full.close()
+    monkeypatch.setenv("CRT_SMEM_KB", str(kb + 40))   # megakernel / id kernel budget
+    monkeypatch.setenv("CRT_PIPE_SLOTS", "512")        # 35 KB pool ...
+    monkeypatch.setenv("CRT_PIPE_PREFIX_KB", str(kb))  # ... + kb of scene prefix for the pipelined and the extend kernel
+    r = Renderer(0)
+    try:
+        _setup(r, s, cam, W, H)
+        assert np.array_equal(r.primary_ids(), ids)
+        for variant in (capi.VARIANT_MEGAKERNEL, capi.VARIANT_WAVEFRONT, capi.VARIANT_PIPELINE):
+            r.clear()
+            r.render(spp=4, max_depth=50, variant=variant)
+            assert np.array_equal(ref.view(np.uint32), r.read_accum().view(np.uint32)), variant
+    finally:
+        r.close()
