@@ -672,14 +672,18 @@ static int mega_blocks_per_sm(bool exact, bool count)
 // ------------------------------------------------------------------------------------------
 // wavefront driver
 // ------------------------------------------------------------------------------------------
+#define CRT_MAX_DEVICES 64
+
 template <int THRESH, bool ALL> static cudaError_t launch_extend(const WfArgs& W, int grid, size_t smem, cudaStream_t st)
 {
-    static bool configured = false; // per instantiation; the attribute is sticky for the process
-    static size_t configured_smem = 0;
-    if (!configured || smem > configured_smem) {
+    // per instantiation and per device (function attributes belong to a device's context); the attribute is sticky
+    static size_t configured[CRT_MAX_DEVICES] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    size_t& configured_smem = configured[dev & (CRT_MAX_DEVICES - 1)];
+    if (smem > configured_smem) {
         cudaError_t e = cudaFuncSetAttribute(k_wf_extend<THRESH, ALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        configured = true;
         configured_smem = smem;
     }
     k_wf_extend<THRESH, ALL><<<grid, WF_EXT_THREADS, smem, st>>>(W);
@@ -800,7 +804,10 @@ __global__ void k_pipe_init(WfShard* shards, uint32_t work_total)
 
 template <int THRESH, bool ALL> static cudaError_t launch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st)
 {
-    static size_t configured_smem = 0;
+    static size_t configured[CRT_MAX_DEVICES] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    size_t& configured_smem = configured[dev & (CRT_MAX_DEVICES - 1)];
     if (smem > configured_smem) {
         cudaError_t e = cudaFuncSetAttribute(k_render_pipe<THRESH, ALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;

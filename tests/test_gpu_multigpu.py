@@ -52,3 +52,25 @@ def test_c_host_example_renders_a_ppm(tmp_path):
     assert data.startswith(head) and len(data) == len(head) + 96 * 54 * 3
     img = np.frombuffer(data[len(head):], dtype=np.uint8).reshape(54, 96, 3)
     assert img[0].mean() > img[-1].mean() * 0.5 and img.std() > 10  # an actual picture: sky on top (rows flipped on write)
+
+
+def test_two_devices_in_one_process():
+    """Contexts on different GPUs of one process (the per-device launch configuration must not be shared): both render the
+    same bits. Skipped on a one-GPU box; the torchrun path (one process per GPU) is what bench.py uses."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    W, H = 160, 90
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    cam = s.default_camera(W, H)
+    out = []
+    for dev in (0, 1):
+        r = Renderer(dev)
+        r.upload(s); r.set_camera(cam); r.resize(W, H)
+        for variant in (capi.VARIANT_PIPELINE, capi.VARIANT_WAVEFRONT, capi.VARIANT_MEGAKERNEL):
+            r.clear()
+            r.render(spp=3, max_depth=50, variant=variant)
+            out.append(r.read_accum().view(np.uint32).copy())
+        r.close()
+    for a in out[1:]:
+        assert np.array_equal(out[0], a)
