@@ -341,6 +341,7 @@ def run_gpu_arm(args):
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
                 "config": {"workload": f"{args.workload}: {desc}", "scene_hittables": scene.n_hittables, "bvh_nodes": int(stats.n_nodes),
+                           "bvh_builder": {1: "host binned SAH (threaded)", 2: "GPU LBVH"}.get(int(stats.builder), "?"),
                            "variant": args.variant, "variant_resolved": resolved, "spp_per_rank": spp, "spp_total": spp * world,
                            "parallelism": f"spp-sharded x{world}" + (", one NCCL reduce (int64 sum) of the fixed-point accumulation buffer" if world > 1 else ""),
                            "l2": "256 MB buffer written between timed steps (L2 flush)", "rays_per_path": L},

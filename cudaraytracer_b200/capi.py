@@ -17,6 +17,7 @@ CRT_OK = 0
 SPHERE, XYRECT, XZRECT, YZRECT = 0, 1, 2, 3
 LAMBERTIAN, METAL, DIELECTRIC, DIFFUSELIGHT = 0, 1, 2, 3
 CONSTANT, CHECKER, IMAGE = 0, 1, 2
+BUILDER_AUTO, BUILDER_HOST_SAH, BUILDER_GPU_LBVH = 0, 1, 2
 VARIANT_AUTO, VARIANT_MEGAKERNEL, VARIANT_WAVEFRONT, VARIANT_PIPELINE = 0, 1, 2, 3
 JITTER_RANDOM, JITTER_CENTER = 0, 1
 FLAG_EXACT_MATH, FLAG_COUNT_TESTS, FLAG_TRUNCATED_GRID = 1, 2, 4
@@ -79,7 +80,7 @@ class Counters(C.Structure):
 class BvhStats(C.Structure):
     _fields_ = [("n_prims", C.c_uint64), ("n_nodes", C.c_uint64), ("max_depth", C.c_uint64), ("smem_nodes", C.c_uint64),
                 ("sah_cost", C.c_double), ("build_ms", C.c_double), ("node_bytes", C.c_uint64), ("prim_bytes", C.c_uint64),
-                ("h2d_bytes", C.c_uint64)]
+                ("h2d_bytes", C.c_uint64), ("builder", C.c_uint64)]
 
 
 assert C.sizeof(Hittable) == 32 and C.sizeof(Material) == 16 and C.sizeof(Texture) == 48 and C.sizeof(InputStruct) == 72
@@ -93,6 +94,7 @@ SIGNATURES = {
     "crt_abi_version": (C.c_int, []),
     "crt_set_stream": (C.c_int, [_P, _P]),
     "crt_synchronize": (C.c_int, [_P]),
+    "crt_set_bvh_builder": (C.c_int, [_P, C.c_int32]),
     "crt_scene_upload": (C.c_int, [_P, C.POINTER(SceneDesc)]),
     "crt_scene_from_reference": (C.c_int, [_P, _P]),
     "crt_bvh_get_stats": (C.c_int, [_P, C.POINTER(BvhStats)]),

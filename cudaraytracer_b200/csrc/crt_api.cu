@@ -7,6 +7,9 @@
 #include "kernels.cuh"
 #include "pipeline.cuh"
 #include "refit.cuh"
+#include "lbvh.cuh"
+
+#include <cub/device/device_radix_sort.cuh>
 
 #include <chrono>
 #include <cmath>
@@ -27,6 +30,8 @@ struct crt_context
     int sm_count = 0;
     int smem_optin = 0, smem_per_sm = 0;
     int smem_budget_override = -1;
+    int bvh_builder = CRT_BUILDER_AUTO;      // crt_set_bvh_builder / CRT_BVH_BUILDER
+    uint64_t gpu_build_min_prims = 65536;   // AUTO: scenes from this size up are built on the GPU (lbvh.cuh)
     long pipe_prefix_bytes = 24 * 1024; // scene prefix staged by the pipelined kernel when the whole scene does not fit
 
     // scene
@@ -175,6 +180,11 @@ crt_status crt_context_create(int device, crt_context** out)
     if ((env = getenv("CRT_PIPE_CHECK")) && atoi(env) > 0) ctx->pipe_check = atoi(env);
     if ((env = getenv("CRT_PIPE_EXT_LOW")) && atoi(env) >= 0) ctx->pipe_ext_low = atoi(env);
     if ((env = getenv("CRT_PIPE_PREFIX_KB")) && atoi(env) >= 0) ctx->pipe_prefix_bytes = 1024L * atoi(env);
+    if ((env = getenv("CRT_BVH_BUILDER"))) {
+        if (!strcmp(env, "host")) ctx->bvh_builder = CRT_BUILDER_HOST_SAH;
+        else if (!strcmp(env, "gpu")) ctx->bvh_builder = CRT_BUILDER_GPU_LBVH;
+    }
+    if ((env = getenv("CRT_GPU_BUILD_MIN_PRIMS")) && atol(env) >= 2) ctx->gpu_build_min_prims = (uint64_t)atol(env);
     if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
         (e = cudaMalloc(&ctx->d_counters, CRT_COUNTER_SHARDS * sizeof(DevCounters))) != cudaSuccess ||
@@ -230,6 +240,36 @@ crt_status crt_synchronize(crt_context* ctx)
 // ------------------------------------------------------------------------------------------
 // scene
 // ------------------------------------------------------------------------------------------
+// images: uploaded as the RGB8 the caller holds and expanded on the device to RGBA8, so a texel is one aligned 32-bit load.
+// The staging buffers are returned in raw_rgb; the caller frees them after it has synchronised the stream.
+static crt_status upload_images(crt_context* ctx, const crt_scene_desc* sd, std::vector<unsigned char*>& raw_rgb, uint64_t& h2d)
+{
+    std::vector<DevImage> himg(sd->n_images);
+    for (uint64_t i = 0; i < himg.size(); i++) {
+        const crt_image& im = sd->images[i];
+        himg[i].texels = nullptr;
+        himg[i].width = im.width;
+        himg[i].height = im.height;
+        if (!im.pixels || im.width <= 0 || im.height <= 0) continue;
+        size_t npx = (size_t)im.width * im.height;
+        uchar4* d = nullptr;
+        unsigned char* raw = nullptr; // RGB8 as given; expanded on the device
+        CU(cudaMalloc(&d, npx * 4));
+        ctx->d_texels.push_back(d);
+        CU(cudaMalloc(&raw, (npx * 3 + 15) & ~(size_t)15));
+        raw_rgb.push_back(raw);
+        CU(cudaMemcpyAsync(raw, im.pixels, npx * 3, cudaMemcpyHostToDevice, ctx->stream));
+        k_rgb_to_rgba<<<(unsigned)((npx / 4 + 1 + 255) / 256), 256, 0, ctx->stream>>>(reinterpret_cast<const uint32_t*>(raw), d, npx);
+        CU(cudaGetLastError());
+        h2d += npx * 3;
+        himg[i].texels = d;
+    }
+    CU(cudaMalloc(&ctx->d_images, std::max<size_t>(himg.size(), 1) * sizeof(DevImage)));
+    if (!himg.empty()) CU(cudaMemcpyAsync(ctx->d_images, himg.data(), himg.size() * sizeof(DevImage), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream)); // himg is a local
+    return CRT_OK;
+}
+
 static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, const CrtPackedScene& P, bool keep_images)
 {
     CU(cudaSetDevice(ctx->device));
@@ -259,31 +299,10 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
         CU(cudaMemcpyAsync(ctx->d_prim_id, P.prim_id.data(), np * 4, cudaMemcpyHostToDevice, ctx->stream));
         h2d += np * (16 + 4 + 32 + 4);
     }
-    // images: RGB8 -> RGBA8 so a texel is one aligned 32-bit load
-    std::vector<DevImage> himg(keep_images ? 0 : sd->n_images);
     std::vector<unsigned char*> raw_rgb;
-    for (uint64_t i = 0; i < himg.size(); i++) {
-        const crt_image& im = sd->images[i];
-        himg[i].texels = nullptr;
-        himg[i].width = im.width;
-        himg[i].height = im.height;
-        if (!im.pixels || im.width <= 0 || im.height <= 0) continue;
-        size_t npx = (size_t)im.width * im.height;
-        uchar4* d = nullptr;
-        unsigned char* raw = nullptr; // RGB8 as given; expanded on the device
-        CU(cudaMalloc(&d, npx * 4));
-        ctx->d_texels.push_back(d);
-        CU(cudaMalloc(&raw, (npx * 3 + 15) & ~(size_t)15));
-        raw_rgb.push_back(raw);
-        CU(cudaMemcpyAsync(raw, im.pixels, npx * 3, cudaMemcpyHostToDevice, ctx->stream));
-        k_rgb_to_rgba<<<(unsigned)((npx / 4 + 1 + 255) / 256), 256, 0, ctx->stream>>>(reinterpret_cast<const uint32_t*>(raw), d, npx);
-        CU(cudaGetLastError());
-        h2d += npx * 3;
-        himg[i].texels = d;
-    }
     if (!keep_images) {
-        CU(cudaMalloc(&ctx->d_images, std::max<size_t>(himg.size(), 1) * sizeof(DevImage)));
-        if (!himg.empty()) CU(cudaMemcpy(ctx->d_images, himg.data(), himg.size() * sizeof(DevImage), cudaMemcpyHostToDevice));
+        crt_status ist = upload_images(ctx, sd, raw_rgb, h2d);
+        if (ist != CRT_OK) return ist;
     }
     CU(cudaStreamSynchronize(ctx->stream));
     for (unsigned char* p : raw_rgb) cudaFree(p);
@@ -307,17 +326,191 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
     return CRT_OK;
 }
 
+// ---- BVH built on the device (lbvh.cuh) ----
+// *outcome: 0 = nothing touched (scene too small for this path), 1 = gave up after the upload (tree too deep; the image
+// textures of `sd` are on the device), 2 = the scene is in use.
+static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, bool keep_images, int* outcome)
+{
+    *outcome = 0;
+    auto t0 = std::chrono::steady_clock::now();
+    std::vector<uint32_t> active;
+    float cmin[3], cmax[3], abs_pad = 0.f;
+    std::string err;
+    if (!crt_prepare_gpu_build(sd, &active, cmin, cmax, &abs_pad, &err)) return crt_set_error(ctx, CRT_ERR_INVALID, err.c_str());
+    const uint32_t n = (uint32_t)active.size();
+    auto t_prep = std::chrono::steady_clock::now();
+    if (n < 2) return CRT_OK; // the degenerate trees (empty scene, one primitive) are the host builder's business
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (keep_images) free_geometry(ctx);
+    else free_scene(ctx);
+    cudaStream_t st = ctx->stream;
+    uint64_t h2d = 0;
+    // everything that only lives during the build comes out of ONE device allocation (20 cudaMalloc/cudaFree pairs cost more
+    // than the kernels): the raw description, sort keys and values, leaf codes, the unpermuted tree, cub's scratch
+    std::vector<unsigned char> present(std::max<uint64_t>(sd->n_images, 1), 0);
+    for (uint64_t i = 0; i < sd->n_images; i++) present[i] = sd->images[i].pixels && sd->images[i].width > 0 && sd->images[i].height > 0;
+    std::vector<unsigned char*> raw_rgb;
+    const size_t nn = (size_t)n - 1;
+    size_t tmp_bytes = 0;
+    {
+        cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr,
+                                                        (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 63, st);
+        if (e != cudaSuccess) return cuda_fail(ctx, e, "cub::DeviceRadixSort::SortPairs (size query)");
+    }
+    size_t arena_bytes = 0;
+    auto reserve = [&](size_t bytes) { const size_t at = arena_bytes; arena_bytes += (bytes + 255) & ~(size_t)255; return at; };
+    const size_t o_h = reserve(sd->n_hittables * sizeof(crt_hittable)), o_m = reserve(std::max<uint64_t>(sd->n_materials, 1) * sizeof(crt_material)),
+                 o_t = reserve(std::max<uint64_t>(sd->n_textures, 1) * sizeof(crt_texture)), o_ip = reserve(present.size()),
+                 o_act = reserve((size_t)n * 4), o_k0 = reserve((size_t)n * 8), o_k1 = reserve((size_t)n * 8), o_v0 = reserve((size_t)n * 4),
+                 o_v1 = reserve((size_t)n * 4), o_code = reserve((size_t)n * 4), o_perm = reserve(nn * 4), o_nodes2 = reserve(nn * 64),
+                 o_parent2 = reserve(nn * 4), o_stats = reserve(sizeof(LbvhStats)), o_tmp = reserve(std::max<size_t>(tmp_bytes, 16));
+    unsigned char* arena = nullptr;
+    auto cleanup = [&]() {
+        cudaFree(arena);
+        for (unsigned char* p : raw_rgb) cudaFree(p);
+    };
+#define CUB_(call)                                                                     \
+    do {                                                                               \
+        cudaError_t e__ = (call);                                                      \
+        if (e__ != cudaSuccess) { cleanup(); return cuda_fail(ctx, e__, #call); }      \
+    } while (0)
+    CUB_(cudaMalloc(&arena, arena_bytes));
+    crt_hittable* d_h = reinterpret_cast<crt_hittable*>(arena + o_h);
+    crt_material* d_m = reinterpret_cast<crt_material*>(arena + o_m);
+    crt_texture* d_t = reinterpret_cast<crt_texture*>(arena + o_t);
+    unsigned char* d_ip = arena + o_ip;
+    uint32_t* d_act = reinterpret_cast<uint32_t*>(arena + o_act);
+    unsigned long long *d_k0 = reinterpret_cast<unsigned long long*>(arena + o_k0), *d_k1 = reinterpret_cast<unsigned long long*>(arena + o_k1);
+    uint32_t *d_v0 = reinterpret_cast<uint32_t*>(arena + o_v0), *d_v1 = reinterpret_cast<uint32_t*>(arena + o_v1);
+    int* d_code = reinterpret_cast<int*>(arena + o_code);
+    int* d_perm = reinterpret_cast<int*>(arena + o_perm);
+    float4* d_nodes2 = reinterpret_cast<float4*>(arena + o_nodes2);
+    int* d_parent2 = reinterpret_cast<int*>(arena + o_parent2);
+    LbvhStats* d_stats = reinterpret_cast<LbvhStats*>(arena + o_stats);
+    void* d_tmp = arena + o_tmp;
+    CUB_(cudaMemcpyAsync(d_h, sd->hittables, sd->n_hittables * sizeof(crt_hittable), cudaMemcpyHostToDevice, st));
+    CUB_(cudaMemcpyAsync(d_m, sd->materials, sd->n_materials * sizeof(crt_material), cudaMemcpyHostToDevice, st));
+    CUB_(cudaMemcpyAsync(d_t, sd->textures, sd->n_textures * sizeof(crt_texture), cudaMemcpyHostToDevice, st));
+    CUB_(cudaMemcpyAsync(d_ip, present.data(), present.size(), cudaMemcpyHostToDevice, st));
+    CUB_(cudaMemcpyAsync(d_act, active.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    h2d += sd->n_hittables * sizeof(crt_hittable) + sd->n_materials * sizeof(crt_material) + sd->n_textures * sizeof(crt_texture) + (uint64_t)n * 4;
+    // outputs
+    CUB_(cudaMalloc(&ctx->d_nodes, nn * 64));
+    CUB_(cudaMalloc(&ctx->d_parent, nn * 4));
+    CUB_(cudaMalloc(&ctx->d_visits, nn * 4));
+    CUB_(cudaMalloc(&ctx->d_leaf_ref, (size_t)n * 4));
+    CUB_(cudaMalloc(&ctx->d_prims, (size_t)n * 16));
+    CUB_(cudaMalloc(&ctx->d_prim_k, (size_t)n * 4));
+    CUB_(cudaMalloc(&ctx->d_mats, (size_t)n * 32));
+    CUB_(cudaMalloc(&ctx->d_prim_id, (size_t)n * 4));
+
+    auto t_alloc = std::chrono::steady_clock::now();
+    LbvhRaw R;
+    R.hittables = d_h; R.materials = d_m; R.textures = d_t; R.image_present = d_ip; R.active = d_act; R.n = n;
+    float3 c0 = make_float3(cmin[0], cmin[1], cmin[2]), ie;
+    ie.x = cmax[0] > cmin[0] ? 1.0f / (cmax[0] - cmin[0]) : 0.f;
+    ie.y = cmax[1] > cmin[1] ? 1.0f / (cmax[1] - cmin[1]) : 0.f;
+    ie.z = cmax[2] > cmin[2] ? 1.0f / (cmax[2] - cmin[2]) : 0.f;
+    const unsigned gb = (n + 255) / 256, gn = (unsigned)((nn + 255) / 256);
+    k_lbvh_keys<<<gb, 256, 0, st>>>(R, c0, ie, d_k0, d_v0);
+    CUB_(cub::DeviceRadixSort::SortPairs(d_tmp, tmp_bytes, d_k0, d_k1, d_v0, d_v1, (int)n, 0, 63, st));
+    k_lbvh_pack<<<gb, 256, 0, st>>>(R, d_v1, ctx->d_prims, ctx->d_prim_k, ctx->d_mats, ctx->d_prim_id, d_code);
+    k_lbvh_hierarchy<<<gn, 256, 0, st>>>(d_k1, d_code, (int)n, d_nodes2, d_parent2, ctx->d_leaf_ref);
+    CUB_(cudaMemsetAsync(ctx->d_visits, 0, nn * 4, st));
+    k_bvh_refit<<<gb, 256, 0, st>>>(d_nodes2, ctx->d_prims, ctx->d_prim_k, d_parent2, ctx->d_leaf_ref, ctx->d_visits, (int)n, abs_pad);
+    CUB_(cudaMemsetAsync(d_stats, 0, sizeof(LbvhStats), st));
+    k_lbvh_stats<<<gb, 256, 0, st>>>(d_nodes2, d_parent2, ctx->d_leaf_ref, (int)n, d_stats);
+    // top of the tree breadth-first (what the kernels stage in shared memory), the rest keeps the sorted order
+    k_lbvh_identity<<<gn, 256, 0, st>>>(d_perm, (int)nn);
+    k_lbvh_top_order<<<1, 32, 0, st>>>(d_nodes2, (int)nn, LBVH_TOP_MAX, d_perm);
+    k_lbvh_permute<<<gn, 256, 0, st>>>(d_nodes2, ctx->d_nodes, d_perm, d_parent2, ctx->d_parent, (int)nn);
+    k_lbvh_permute_leaf_refs<<<gb, 256, 0, st>>>(ctx->d_leaf_ref, d_perm, (int)n);
+    CUB_(cudaGetLastError());
+    if (!keep_images) {
+        crt_status ist = upload_images(ctx, sd, raw_rgb, h2d);
+        if (ist != CRT_OK) { cleanup(); return ist; }
+    }
+    LbvhStats hs;
+    std::vector<int32_t> prim_id(n);
+    CUB_(cudaMemcpyAsync(&hs, d_stats, sizeof(hs), cudaMemcpyDeviceToHost, st));
+    CUB_(cudaMemcpyAsync(prim_id.data(), ctx->d_prim_id, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    CUB_(cudaStreamSynchronize(st));
+    auto t_gpu = std::chrono::steady_clock::now();
+    cleanup();
+#undef CUB_
+    if (hs.max_depth >= CRT_STACK_SIZE) { // pathological key distribution: let the SAH builder (depth-bounded by its splits) do it
+        free_geometry(ctx);
+        *outcome = 1;
+        return CRT_OK;
+    }
+    ctx->abs_pad = abs_pad;
+    ctx->slot_of.assign(sd->n_hittables, -1);
+    for (size_t sl = 0; sl < n; sl++) ctx->slot_of[prim_id[sl]] = (int32_t)sl;
+    ctx->dirty.assign(sd->n_hittables, 0);
+    ctx->dirty_list.clear();
+    ctx->need_rebuild = false;
+    DevScene& S = ctx->scene;
+    S.nodes = ctx->d_nodes; S.prims = ctx->d_prims; S.prim_k = ctx->d_prim_k; S.mats = ctx->d_mats;
+    S.prim_id = ctx->d_prim_id; S.images = ctx->d_images;
+    S.n_nodes = (int)nn; S.n_prims = (int)n;
+    S.smem_nodes = S.smem_prims = S.smem_mats = 0;
+    memset(&ctx->stats, 0, sizeof(ctx->stats));
+    ctx->stats.n_prims = n;
+    ctx->stats.n_nodes = nn;
+    ctx->stats.max_depth = (uint64_t)hs.max_depth;
+    ctx->stats.sah_cost = hs.root_area > 0.f ? 1.0 + (double)hs.area_sum / hs.root_area : 0.0;
+    ctx->stats.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    ctx->stats.node_bytes = (uint64_t)nn * 64;
+    ctx->stats.prim_bytes = (uint64_t)n * (16 + 4 + 32 + 4);
+    ctx->stats.h2d_bytes = h2d;
+    ctx->stats.builder = CRT_BUILDER_GPU_LBVH;
+    ctx->scene_h2d_bytes = h2d;
+    ctx->have_scene = true;
+    *outcome = 2;
+    if (getenv("CRT_BVH_TIMING")) {
+        auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        fprintf(stderr, "[crt] gpu bvh: host prepare %.1f ms, free + alloc + enqueue copies %.1f ms, kernels + copies + sync %.1f ms, free + bookkeeping %.1f ms\n",
+                ms(t0, t_prep), ms(t_prep, t_alloc), ms(t_alloc, t_gpu), ms(t_gpu, std::chrono::steady_clock::now()));
+    }
+    return CRT_OK;
+}
+
+// Builds the BVH of `sd` with the builder the context is set to and makes it the scene in use.
+static crt_status build_and_upload(crt_context* ctx, const crt_scene_desc* sd, bool keep_images, const char* who)
+{
+    uint64_t n_active_bound = sd ? sd->n_hittables : 0;
+    const bool gpu = ctx->bvh_builder == CRT_BUILDER_GPU_LBVH || (ctx->bvh_builder == CRT_BUILDER_AUTO && n_active_bound >= ctx->gpu_build_min_prims);
+    if (gpu && sd && sd->hittables) {
+        int outcome = 0;
+        crt_status st = upload_gpu_built(ctx, sd, keep_images, &outcome);
+        if (st != CRT_OK || outcome == 2) return st;
+        if (outcome == 1) keep_images = true; // the textures are already on the device
+    }
+    CrtPackedScene P;
+    std::string err;
+    if (!crt_pack_scene(sd, &P, &err)) return crt_set_error(ctx, CRT_ERR_INVALID, err.c_str());
+    if (P.stats.max_depth >= CRT_STACK_SIZE)
+        return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, (std::string(who) + ": BVH deeper than the traversal stack").c_str());
+    crt_status st = upload_packed(ctx, sd, P, keep_images);
+    if (st == CRT_OK) ctx->stats.builder = CRT_BUILDER_HOST_SAH;
+    return st;
+}
+
 extern "C" {
+
+crt_status crt_set_bvh_builder(crt_context* ctx, int32_t builder)
+{
+    if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_set_bvh_builder: ctx is NULL");
+    if (builder < CRT_BUILDER_AUTO || builder > CRT_BUILDER_GPU_LBVH) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_set_bvh_builder: unknown builder");
+    ctx->bvh_builder = builder;
+    return CRT_OK;
+}
 
 crt_status crt_scene_upload(crt_context* ctx, const crt_scene_desc* scene)
 {
     if (!ctx || !scene) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_upload: NULL argument");
-    CrtPackedScene P;
-    std::string err;
-    if (!crt_pack_scene(scene, &P, &err)) return crt_set_error(ctx, CRT_ERR_INVALID, err.c_str());
-    if (P.stats.max_depth >= CRT_STACK_SIZE)
-        return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, "crt_scene_upload: BVH deeper than the traversal stack");
-    crt_status st = upload_packed(ctx, scene, P, false);
+    crt_status st = build_and_upload(ctx, scene, false, "crt_scene_upload");
     if (st != CRT_OK) return st;
     ctx->host.hittables.assign(scene->hittables, scene->hittables + scene->n_hittables);
     ctx->host.materials.assign(scene->materials, scene->materials + scene->n_materials);
@@ -384,12 +577,8 @@ crt_status crt_scene_commit(crt_context* ctx, int force_rebuild, int* out_rebuil
     CU(cudaSetDevice(ctx->device));
     const crt_scene_desc d = ctx->host.desc();
     if (force_rebuild || ctx->need_rebuild || ctx->scene.n_prims < 2) {
-        CrtPackedScene P;
-        std::string err;
-        if (!crt_pack_scene(&d, &P, &err)) return crt_set_error(ctx, CRT_ERR_INVALID, err.c_str());
-        if (P.stats.max_depth >= CRT_STACK_SIZE) return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, "crt_scene_commit: BVH deeper than the traversal stack");
         if (out_rebuilt) *out_rebuilt = 1;
-        return upload_packed(ctx, &d, P, true); // the image textures stay where they are
+        return build_and_upload(ctx, &d, true, "crt_scene_commit"); // the image textures stay where they are
     }
     // refit path: scatter the edited records, then recompute every box bottom-up on the GPU
     auto t0 = std::chrono::steady_clock::now();

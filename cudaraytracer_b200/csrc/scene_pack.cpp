@@ -296,6 +296,111 @@ void crt_pack_material(const crt_scene_desc* sd, const crt_material& m, float mr
     memcpy(&mr[7], &bits, 4);
 }
 
+// Validation of one ACTIVE hittable and of everything it references (shared by the host and the GPU build paths).
+static bool check_hittable(const crt_scene_desc* sd, uint64_t i, std::string* err)
+{
+    const crt_hittable& h = sd->hittables[i];
+    if (h.type < CRT_SPHERE || h.type > CRT_YZRECT) {
+        *err = "scene: hittable " + std::to_string(i) + " has unknown type " + std::to_string(h.type);
+        return false;
+    }
+    if (h.material < 0 || (uint64_t)h.material >= sd->n_materials) {
+        *err = "scene: hittable " + std::to_string(i) + " has material index out of range";
+        return false;
+    }
+    const crt_material& m = sd->materials[h.material];
+    if (m.type < CRT_LAMBERTIAN || m.type > CRT_DIFFUSELIGHT) {
+        *err = "scene: material " + std::to_string(h.material) + " has unknown type";
+        return false;
+    }
+    if (m.type != CRT_DIELECTRIC) {
+        if (m.texture < 0 || (uint64_t)m.texture >= sd->n_textures) {
+            *err = "scene: material " + std::to_string(h.material) + " has texture index out of range";
+            return false;
+        }
+        const crt_texture& t = sd->textures[m.texture];
+        if (t.type < CRT_CONSTANT || t.type > CRT_IMAGE) {
+            *err = "scene: texture " + std::to_string(m.texture) + " has unknown type";
+            return false;
+        }
+        if (t.type == CRT_IMAGE && t.image >= 0 && (uint64_t)t.image >= sd->n_images) {
+            *err = "scene: texture " + std::to_string(m.texture) + " has image index out of range";
+            return false;
+        }
+    }
+    return true;
+}
+
+// Host-side preparation of a GPU build (lbvh.cuh): validates, lists the active hittables and measures the scene (bounds of
+// the box centres for the Morton grid, largest coordinate magnitude for the absolute box padding). Threaded for large scenes.
+bool crt_prepare_gpu_build(const crt_scene_desc* sd, std::vector<uint32_t>* active, float cmin[3], float cmax[3], float* abs_pad,
+                           std::string* err)
+{
+    if (!sd || (!sd->hittables && sd->n_hittables)) {
+        *err = "scene: NULL hittable list";
+        return false;
+    }
+    if (sd->n_hittables > (uint64_t)CRT_LEAF_INDEX_MASK) {
+        *err = "scene: too many hittables (limit 2^26 - 1)";
+        return false;
+    }
+    const uint64_t n = sd->n_hittables;
+    unsigned nt = n >= 65536 ? std::min(16u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+    struct Part { std::vector<uint32_t> act; float cmin[3], cmax[3], extent; bool ok; std::string err; };
+    std::vector<Part> parts(nt);
+    auto work = [&](unsigned t) {
+        Part& P = parts[t];
+        P.ok = true;
+        P.extent = 0.f;
+        for (int a = 0; a < 3; a++) { P.cmin[a] = std::numeric_limits<float>::infinity(); P.cmax[a] = -std::numeric_limits<float>::infinity(); }
+        const uint64_t i0 = n * t / nt, i1 = n * (t + 1) / nt;
+        P.act.reserve((size_t)(i1 - i0));
+        for (uint64_t i = i0; i < i1; i++) {
+            const crt_hittable& h = sd->hittables[i];
+            if (!h.active) continue;
+            if (!check_hittable(sd, i, &P.err)) { P.ok = false; return; }
+            P.act.push_back((uint32_t)i);
+            float lo[3], hi[3];
+            const float hw = h.a / 2, hh = h.b / 2, r = fabsf(h.a);
+            switch (h.type) {
+            case CRT_SPHERE: lo[0] = h.cx - r; hi[0] = h.cx + r; lo[1] = h.cy - r; hi[1] = h.cy + r; lo[2] = h.cz - r; hi[2] = h.cz + r; break;
+            case CRT_XYRECT: lo[0] = h.cx - hw; hi[0] = h.cx + hw; lo[1] = h.cy - hh; hi[1] = h.cy + hh; lo[2] = h.cz - 0.0001f; hi[2] = h.cz + 0.0001f; break;
+            case CRT_XZRECT: lo[0] = h.cx - hw; hi[0] = h.cx + hw; lo[2] = h.cz - hh; hi[2] = h.cz + hh; lo[1] = h.cy - 0.0001f; hi[1] = h.cy + 0.0001f; break;
+            default:         lo[1] = h.cy - hh; hi[1] = h.cy + hh; lo[2] = h.cz - hw; hi[2] = h.cz + hw; lo[0] = h.cx - 0.0001f; hi[0] = h.cx + 0.0001f; break;
+            }
+            for (int a = 0; a < 3; a++) {
+                const float c = 0.5f * lo[a] + 0.5f * hi[a];
+                P.cmin[a] = std::min(P.cmin[a], c);
+                P.cmax[a] = std::max(P.cmax[a], c);
+                P.extent = std::max(P.extent, std::max(fabsf(lo[a]), fabsf(hi[a])));
+            }
+        }
+    };
+    if (nt == 1) work(0);
+    else {
+        std::vector<std::thread> pool;
+        for (unsigned t = 1; t < nt; t++) pool.emplace_back(work, t);
+        work(0);
+        for (std::thread& t : pool) t.join();
+    }
+    float extent = 0.f;
+    for (int a = 0; a < 3; a++) { cmin[a] = std::numeric_limits<float>::infinity(); cmax[a] = -std::numeric_limits<float>::infinity(); }
+    size_t total = 0;
+    for (const Part& P : parts) {
+        if (!P.ok) { *err = P.err; return false; }
+        total += P.act.size();
+    }
+    active->clear();
+    active->reserve(total);
+    for (const Part& P : parts) {
+        active->insert(active->end(), P.act.begin(), P.act.end());
+        extent = std::max(extent, P.extent);
+        for (int a = 0; a < 3; a++) { cmin[a] = std::min(cmin[a], P.cmin[a]); cmax[a] = std::max(cmax[a], P.cmax[a]); }
+    }
+    *abs_pad = 1e-7f + 4e-7f * extent; // same rule as the host build below
+    return true;
+}
+
 bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* err)
 {
     auto t0 = std::chrono::steady_clock::now();
@@ -311,37 +416,10 @@ bool crt_pack_scene(const crt_scene_desc* sd, CrtPackedScene* out, std::string* 
     std::vector<uint32_t> active;
     active.reserve(sd->n_hittables);
     for (uint64_t i = 0; i < sd->n_hittables; i++) {
-        const crt_hittable& h = sd->hittables[i];
-        if (!h.active)
+        if (!sd->hittables[i].active)
             continue;
-        if (h.type < CRT_SPHERE || h.type > CRT_YZRECT) {
-            *err = "scene: hittable " + std::to_string(i) + " has unknown type " + std::to_string(h.type);
+        if (!check_hittable(sd, i, err))
             return false;
-        }
-        if (h.material < 0 || (uint64_t)h.material >= sd->n_materials) {
-            *err = "scene: hittable " + std::to_string(i) + " has material index out of range";
-            return false;
-        }
-        const crt_material& m = sd->materials[h.material];
-        if (m.type < CRT_LAMBERTIAN || m.type > CRT_DIFFUSELIGHT) {
-            *err = "scene: material " + std::to_string(h.material) + " has unknown type";
-            return false;
-        }
-        if (m.type != CRT_DIELECTRIC) {
-            if (m.texture < 0 || (uint64_t)m.texture >= sd->n_textures) {
-                *err = "scene: material " + std::to_string(h.material) + " has texture index out of range";
-                return false;
-            }
-            const crt_texture& t = sd->textures[m.texture];
-            if (t.type < CRT_CONSTANT || t.type > CRT_IMAGE) {
-                *err = "scene: texture " + std::to_string(m.texture) + " has unknown type";
-                return false;
-            }
-            if (t.type == CRT_IMAGE && t.image >= 0 && (uint64_t)t.image >= sd->n_images) {
-                *err = "scene: texture " + std::to_string(m.texture) + " has image index out of range";
-                return false;
-            }
-        }
         active.push_back((uint32_t)i);
     }
     const uint32_t n = (uint32_t)active.size();

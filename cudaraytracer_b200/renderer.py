@@ -153,6 +153,10 @@ class Renderer:
     def set_stream(self, cuda_stream: int):
         self._ck(self.lib.crt_set_stream(self.ctx, C.c_void_p(cuda_stream)))
 
+    def set_bvh_builder(self, builder: int):
+        """capi.BUILDER_AUTO / BUILDER_HOST_SAH (threaded SAH on the host) / BUILDER_GPU_LBVH (Morton LBVH on the device)."""
+        self._ck(self.lib.crt_set_bvh_builder(self.ctx, builder))
+
     def upload(self, scene: Scene):
         self._ck(self.lib.crt_scene_upload(self.ctx, C.byref(scene.desc)))
 
@@ -164,7 +168,7 @@ class Renderer:
         self._ck(self.lib.crt_scene_edit_material(self.ctx, index, C.byref(capi.Material(**fields))))
 
     def commit(self, force_rebuild: bool = False) -> bool:
-        """Apply the staged edits: GPU refit, or a host rebuild when the topology changed. Returns True if rebuilt."""
+        """Apply the staged edits: GPU refit, or a rebuild (host SAH / GPU LBVH) when the topology changed. Returns True if rebuilt."""
         rebuilt = C.c_int()
         self._ck(self.lib.crt_scene_commit(self.ctx, int(force_rebuild), C.byref(rebuilt)))
         return bool(rebuilt.value)

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CRT_ABI_VERSION 2
+#define CRT_ABI_VERSION 3
 
 typedef enum crt_status {
     CRT_OK = 0,
@@ -131,7 +131,16 @@ typedef struct crt_bvh_stats {
     double build_ms;
     uint64_t node_bytes, prim_bytes;
     uint64_t h2d_bytes; /* bytes copied host -> device by the last scene upload (nodes, primitives, materials, texels) */
+    uint64_t builder;   /* CRT_BUILDER_HOST_SAH or CRT_BUILDER_GPU_LBVH: which builder made the tree in use */
 } crt_bvh_stats;
+
+/* Which builder crt_scene_upload / crt_scene_commit use. Both replace the BVHNode constructor of the reference
+ * (Hittable.cuh:303-385), which runs on the host at start-up and after every GUI edit (CudaLayer.cpp:247-256,493-494).
+ *   HOST_SAH  threaded binned-SAH builder (csrc/scene_pack.cpp): the best trees, 190 ms for 1 M spheres on 16 cores.
+ *   GPU_LBVH  Morton-code linear BVH built entirely on the device (csrc/lbvh.cuh): a few ms for 1 M spheres.
+ *   AUTO      GPU_LBVH from 65536 active hittables up (CRT_GPU_BUILD_MIN_PRIMS), HOST_SAH below.
+ * The environment variable CRT_BVH_BUILDER=host|gpu overrides the default of new contexts. */
+enum { CRT_BUILDER_AUTO = 0, CRT_BUILDER_HOST_SAH = 1, CRT_BUILDER_GPU_LBVH = 2 };
 
 typedef struct crt_context crt_context;
 
@@ -145,6 +154,7 @@ crt_status crt_set_stream(crt_context* ctx, void* cuda_stream);
 crt_status crt_synchronize(crt_context* ctx);
 
 /* ---- scene (replaces CudaLayer::GenerateWorld + BVHNode ctor, CudaLayer.cpp:103-256, Hittable.cuh:303-385) ---- */
+crt_status crt_set_bvh_builder(crt_context* ctx, int32_t builder);
 crt_status crt_scene_upload(crt_context* ctx, const crt_scene_desc* scene);
 /* Walk the reference's own pointer graph: `world` is the Hittable of type BVHNODE that
  * LaunchKernel receives (Kernel.cu:178-181). Host-readable (managed or host) memory. */
