@@ -111,10 +111,10 @@ def test_refit_of_a_large_scene_is_much_cheaper_than_a_rebuild():
     assert np.array_equal(ids, ref_ids)
     t0 = time.perf_counter(); assert r.commit(force_rebuild=True) is True; t_rebuild = time.perf_counter() - t0
     assert np.array_equal(r.primary_ids(), ref_ids)
-    r.set_bvh_builder(capi.BUILDER_GPU_LBVH)
+    r.set_bvh_builder(capi.BUILDER_GPU_PLOC)
     r.commit(force_rebuild=True)  # first use: allocations, cub's kernels
     t0 = time.perf_counter(); assert r.commit(force_rebuild=True) is True; t_gpu = time.perf_counter() - t0
-    assert r.bvh_stats().builder == capi.BUILDER_GPU_LBVH
+    assert r.bvh_stats().builder == capi.BUILDER_GPU_PLOC
     assert np.array_equal(r.primary_ids(), ref_ids)
     print(f"refit {t_refit * 1e3:.2f} ms vs host rebuild {t_rebuild * 1e3:.2f} ms vs GPU rebuild {t_gpu * 1e3:.2f} ms")
     assert t_refit < t_rebuild and t_gpu < t_rebuild

@@ -1,5 +1,5 @@
-"""GPU tests of the device-side BVH builder (csrc/lbvh.cuh): the tree is different from the host SAH tree, the closest hit
-is not. Primary-hit IDs bit-exact against the oracle, accumulation buffers bit-identical to the host-built tree's, edits
+"""GPU tests of the device-side BVH builders (csrc/lbvh.cuh: Morton LBVH and PLOC clustering): the tree is different from the
+host SAH tree, the closest hit is not. Primary-hit IDs bit-exact against the oracle, accumulation buffers bit-identical to the host-built tree's, edits
 (refit and topology change) on a GPU-built tree, fall-back for degenerate scenes. All through the C ABI."""
 import numpy as np
 import pytest
@@ -19,20 +19,25 @@ def _setup(r, scene, cam, W, H):
     r.resize(W, H)
 
 
+GPU_BUILDERS = [capi.BUILDER_GPU_LBVH, capi.BUILDER_GPU_PLOC]
+
+
+@pytest.mark.parametrize("builder", GPU_BUILDERS, ids=["lbvh", "ploc"])
 @pytest.mark.parametrize("name,kind,hint,W,H", SCENES)
-def test_gpu_built_tree_same_hits_as_host_tree(name, kind, hint, W, H):
+def test_gpu_built_tree_same_hits_as_host_tree(name, kind, hint, W, H, builder):
     s = Scene.generate(kind, 1984, hint)
     cam = s.default_camera(W, H)
     host, gpu = Renderer(0), Renderer(0)
     try:
         host.set_bvh_builder(capi.BUILDER_HOST_SAH)
-        gpu.set_bvh_builder(capi.BUILDER_GPU_LBVH)
+        gpu.set_bvh_builder(builder)
         _setup(host, s, cam, W, H)
         _setup(gpu, s, cam, W, H)
         sh, sg = host.bvh_stats(), gpu.bvh_stats()
-        assert sh.builder == capi.BUILDER_HOST_SAH and sg.builder == capi.BUILDER_GPU_LBVH
+        assert sh.builder == capi.BUILDER_HOST_SAH and sg.builder == builder
         assert sg.n_prims == sh.n_prims and sg.n_nodes == sg.n_prims - 1 and 0 < sg.max_depth < 64
-        assert sg.sah_cost >= 0.99 * sh.sah_cost  # SAH is the better tree by its own measure (statistic only)
+        print(f"{name}: SAH statistic host {sh.sah_cost:.3f} vs GPU builder {builder} {sg.sah_cost:.3f}; depth {sh.max_depth} vs {sg.max_depth}")
+        assert sg.sah_cost < 3.0 * sh.sah_cost
         ids = gpu.primary_ids()
         assert np.array_equal(ids, host.primary_ids())
         if s.n_hittables <= 20000:
@@ -68,14 +73,15 @@ def test_gpu_built_large_grid_ids_vs_brute_force():
         r.close()
 
 
-def test_edits_on_a_gpu_built_tree():
+@pytest.mark.parametrize("builder", GPU_BUILDERS, ids=["lbvh", "ploc"])
+def test_edits_on_a_gpu_built_tree(builder):
     """Refit (moved / resized spheres, material switch) and a topology change (deactivate, type change) with the GPU builder."""
     s = Scene.generate(capi.SCENE_RTIOW, 1984)
     W, H = 128, 72
     cam = s.default_camera(W, H)
     r, fresh = Renderer(0), Renderer(0)
     try:
-        r.set_bvh_builder(capi.BUILDER_GPU_LBVH)
+        r.set_bvh_builder(builder)
         _setup(r, s, cam, W, H)
         h = s.hittable_array().copy()
         edited = []
@@ -89,7 +95,7 @@ def test_edits_on_a_gpu_built_tree():
         r.edit_hittable(7, **f2)
         edited.append((7, f2))
         assert r.commit() is True   # rebuild, on the GPU
-        assert r.bvh_stats().builder == capi.BUILDER_GPU_LBVH and r.bvh_stats().n_prims == len(h) - 1
+        assert r.bvh_stats().builder == builder and r.bvh_stats().n_prims == len(h) - 1
         # the same scene built from scratch by the host builder
         hs = [dict(type=int(x["type"]), active=int(x["active"]), cx=float(x["cx"]), cy=float(x["cy"]), cz=float(x["cz"]), a=float(x["a"]),
                    b=float(x["b"]), material=int(x["material"])) for x in h]
@@ -112,13 +118,14 @@ def test_edits_on_a_gpu_built_tree():
         r.close(); fresh.close()
 
 
-def test_degenerate_scenes_fall_back_to_the_host_builder():
+@pytest.mark.parametrize("builder", GPU_BUILDERS, ids=["lbvh", "ploc"])
+def test_degenerate_scenes_fall_back_to_the_host_builder(builder):
     cam = look_camera((0, 0, 5), (0, 0, -1))
     tex = [dict(type=capi.CONSTANT, color=(0.5, 0.5, 0.5))]
     mat = [dict(type=capi.LAMBERTIAN, texture=0)]
     r = Renderer(0)
     try:
-        r.set_bvh_builder(capi.BUILDER_GPU_LBVH)
+        r.set_bvh_builder(builder)
         for hs in ([], [dict(type=capi.SPHERE, cx=0, cy=0, cz=0, a=1.0, material=0, active=1)]):
             sc = Scene.from_arrays(hs, mat, tex)
             _setup(r, sc, cam, 40, 30)
@@ -129,7 +136,7 @@ def test_degenerate_scenes_fall_back_to_the_host_builder():
         same = [dict(type=capi.SPHERE, cx=0, cy=0, cz=0, a=0.2 + 0.1 * k, material=0, active=1) for k in range(9)]
         sc = Scene.from_arrays(same, mat, tex)
         _setup(r, sc, cam, 40, 30)
-        assert r.bvh_stats().builder == capi.BUILDER_GPU_LBVH
+        assert r.bvh_stats().builder == builder
         ref = O.oracle_render(sc, cam, 40, 30, 0, 5, want_ids=True, want_rgba=False, want_mean=False)["ids"]
         assert np.array_equal(r.primary_ids(), ref)
         bad = Scene.from_arrays([dict(type=capi.SPHERE, cx=0, cy=0, cz=0, a=1.0, material=3)] * 3, mat, tex)
