@@ -338,9 +338,9 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
     *outcome = 0;
     auto t0 = std::chrono::steady_clock::now();
     std::vector<uint32_t> active;
-    float cmin[3], cmax[3], abs_pad = 0.f;
+    float cmin[3], cmax[3], blo[3], bhi[3], abs_pad = 0.f;
     std::string err;
-    if (!crt_prepare_gpu_build(sd, &active, cmin, cmax, &abs_pad, &err)) return crt_set_error(ctx, CRT_ERR_INVALID, err.c_str());
+    if (!crt_prepare_gpu_build(sd, &active, cmin, cmax, blo, bhi, &abs_pad, &err)) return crt_set_error(ctx, CRT_ERR_INVALID, err.c_str());
     const uint32_t n = (uint32_t)active.size();
     auto t_prep = std::chrono::steady_clock::now();
     if (n < 2) return CRT_OK; // the degenerate trees (empty scene, one primitive) are the host builder's business
@@ -359,7 +359,7 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
     size_t tmp_bytes = 0;
     {
         cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr,
-                                                        (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 63, st);
+                                                        (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 64, st);
         if (e != cudaSuccess) return cuda_fail(ctx, e, "cub::DeviceRadixSort::SortPairs (size query)");
         size_t scan_bytes = 0;
         e = cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr, (int)n, st);
@@ -424,8 +424,10 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
     ie.y = cmax[1] > cmin[1] ? 1.0f / (cmax[1] - cmin[1]) : 0.f;
     ie.z = cmax[2] > cmin[2] ? 1.0f / (cmax[2] - cmin[2]) : 0.f;
     const unsigned gb = (n + 255) / 256, gn = (unsigned)((nn + 255) / 256);
-    k_lbvh_keys<<<gb, 256, 0, st>>>(R, c0, ie, d_k0, d_v0);
-    CUB_(cub::DeviceRadixSort::SortPairs(d_tmp, tmp_bytes, d_k0, d_k1, d_v0, d_v1, (int)n, 0, 63, st));
+    const float sx = bhi[0] - blo[0], sy = bhi[1] - blo[1], sz = bhi[2] - blo[2];
+    const float big_area = 0.25f * (sx * sy + sy * sz + sz * sx); // of the half-area; NaN / inf: nothing qualifies, or everything
+    k_lbvh_keys<<<gb, 256, 0, st>>>(R, c0, ie, big_area, d_k0, d_v0);
+    CUB_(cub::DeviceRadixSort::SortPairs(d_tmp, tmp_bytes, d_k0, d_k1, d_v0, d_v1, (int)n, 0, 64, st));
     k_lbvh_pack<<<gb, 256, 0, st>>>(R, d_v1, ctx->d_prims, ctx->d_prim_k, ctx->d_mats, ctx->d_prim_id, d_code);
     bool ploc_done = false;
     int ploc_steps = 0;

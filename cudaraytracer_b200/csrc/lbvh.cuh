@@ -57,8 +57,13 @@ __device__ __forceinline__ unsigned long long lbvh_spread3(unsigned int v)
     return x;
 }
 
-// cmin / inv_extent: centroid bounds of the scene (computed on the host while it validates the hittable list)
-__global__ void k_lbvh_keys(LbvhRaw R, float3 cmin, float3 inv_extent, unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals)
+// cmin / inv_extent: centroid bounds of the scene (computed on the host while it validates the hittable list).
+// A primitive whose box has at least `big_area` surface (a quarter of the scene box's: a ground sphere, a room wall) gets the
+// otherwise unused top key bit: such boxes overlap everything, and wherever their centre happens to fall on the curve they
+// would inflate every ancestor up to the root. With the top bit they hang directly under the root, next to the tree of the
+// ordinary primitives — where the SAH builder puts them too.
+__global__ void k_lbvh_keys(LbvhRaw R, float3 cmin, float3 inv_extent, float big_area, unsigned long long* __restrict__ keys,
+                            uint32_t* __restrict__ vals)
 {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= R.n) return;
@@ -74,7 +79,9 @@ __global__ void k_lbvh_keys(LbvhRaw R, float3 cmin, float3 inv_extent, unsigned 
         t = t <= 1.f ? t : 1.f;
         q[a] = min((unsigned int)(t * 2097152.0f), 2097151u);
     }
-    keys[k] = lbvh_spread3(q[0]) << 2 | lbvh_spread3(q[1]) << 1 | lbvh_spread3(q[2]);
+    const float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+    const bool big = dx * dy + dy * dz + dz * dx >= big_area;
+    keys[k] = big ? (1ull << 63 | k) : (lbvh_spread3(q[0]) << 2 | lbvh_spread3(q[1]) << 1 | lbvh_spread3(q[2]));
     vals[k] = k;
 }
 

@@ -333,8 +333,8 @@ static bool check_hittable(const crt_scene_desc* sd, uint64_t i, std::string* er
 
 // Host-side preparation of a GPU build (lbvh.cuh): validates, lists the active hittables and measures the scene (bounds of
 // the box centres for the Morton grid, largest coordinate magnitude for the absolute box padding). Threaded for large scenes.
-bool crt_prepare_gpu_build(const crt_scene_desc* sd, std::vector<uint32_t>* active, float cmin[3], float cmax[3], float* abs_pad,
-                           std::string* err)
+bool crt_prepare_gpu_build(const crt_scene_desc* sd, std::vector<uint32_t>* active, float cmin[3], float cmax[3], float blo[3],
+                           float bhi[3], float* abs_pad, std::string* err)
 {
     if (!sd || (!sd->hittables && sd->n_hittables)) {
         *err = "scene: NULL hittable list";
@@ -346,13 +346,16 @@ bool crt_prepare_gpu_build(const crt_scene_desc* sd, std::vector<uint32_t>* acti
     }
     const uint64_t n = sd->n_hittables;
     unsigned nt = n >= 65536 ? std::min(16u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
-    struct Part { std::vector<uint32_t> act; float cmin[3], cmax[3], extent; bool ok; std::string err; };
+    struct Part { std::vector<uint32_t> act; float cmin[3], cmax[3], blo[3], bhi[3], extent; bool ok; std::string err; };
     std::vector<Part> parts(nt);
     auto work = [&](unsigned t) {
         Part& P = parts[t];
         P.ok = true;
         P.extent = 0.f;
-        for (int a = 0; a < 3; a++) { P.cmin[a] = std::numeric_limits<float>::infinity(); P.cmax[a] = -std::numeric_limits<float>::infinity(); }
+        for (int a = 0; a < 3; a++) {
+            P.cmin[a] = P.blo[a] = std::numeric_limits<float>::infinity();
+            P.cmax[a] = P.bhi[a] = -std::numeric_limits<float>::infinity();
+        }
         const uint64_t i0 = n * t / nt, i1 = n * (t + 1) / nt;
         P.act.reserve((size_t)(i1 - i0));
         for (uint64_t i = i0; i < i1; i++) {
@@ -372,6 +375,8 @@ bool crt_prepare_gpu_build(const crt_scene_desc* sd, std::vector<uint32_t>* acti
                 const float c = 0.5f * lo[a] + 0.5f * hi[a];
                 P.cmin[a] = std::min(P.cmin[a], c);
                 P.cmax[a] = std::max(P.cmax[a], c);
+                P.blo[a] = std::min(P.blo[a], lo[a]);
+                P.bhi[a] = std::max(P.bhi[a], hi[a]);
                 P.extent = std::max(P.extent, std::max(fabsf(lo[a]), fabsf(hi[a])));
             }
         }
@@ -384,7 +389,10 @@ bool crt_prepare_gpu_build(const crt_scene_desc* sd, std::vector<uint32_t>* acti
         for (std::thread& t : pool) t.join();
     }
     float extent = 0.f;
-    for (int a = 0; a < 3; a++) { cmin[a] = std::numeric_limits<float>::infinity(); cmax[a] = -std::numeric_limits<float>::infinity(); }
+    for (int a = 0; a < 3; a++) {
+        cmin[a] = blo[a] = std::numeric_limits<float>::infinity();
+        cmax[a] = bhi[a] = -std::numeric_limits<float>::infinity();
+    }
     size_t total = 0;
     for (const Part& P : parts) {
         if (!P.ok) { *err = P.err; return false; }
@@ -395,7 +403,10 @@ bool crt_prepare_gpu_build(const crt_scene_desc* sd, std::vector<uint32_t>* acti
     for (const Part& P : parts) {
         active->insert(active->end(), P.act.begin(), P.act.end());
         extent = std::max(extent, P.extent);
-        for (int a = 0; a < 3; a++) { cmin[a] = std::min(cmin[a], P.cmin[a]); cmax[a] = std::max(cmax[a], P.cmax[a]); }
+        for (int a = 0; a < 3; a++) {
+            cmin[a] = std::min(cmin[a], P.cmin[a]); cmax[a] = std::max(cmax[a], P.cmax[a]);
+            blo[a] = std::min(blo[a], P.blo[a]); bhi[a] = std::max(bhi[a], P.bhi[a]);
+        }
     }
     *abs_pad = 1e-7f + 4e-7f * extent; // same rule as the host build below
     return true;
