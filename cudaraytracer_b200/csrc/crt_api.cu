@@ -55,6 +55,8 @@ struct crt_context
     int* d_parent = nullptr;
     int* d_leaf_ref = nullptr;
     unsigned int* d_visits = nullptr;
+    void* d_edit_recs = nullptr;     // staging for crt_scene_commit's refit path (grow-only: no allocation per commit)
+    size_t edit_recs_cap = 0;
     float abs_pad = 0.f, scene_extent = 0.f;
     crt_bvh_stats stats{};
     uint64_t scene_h2d_bytes = 0;
@@ -216,6 +218,7 @@ void crt_context_destroy(crt_context* ctx)
     cudaFree(ctx->d_ids);
     cudaFree(ctx->d_counters);
     cudaFree(ctx->d_shards);
+    cudaFree(ctx->d_edit_recs);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -649,8 +652,15 @@ crt_status crt_scene_commit(crt_context* ctx, int force_rebuild, int* out_rebuil
     // the absolute box padding scales with the scene extent (scene_pack.cpp); edits may only grow it
     ctx->abs_pad = std::max(ctx->abs_pad, 1e-7f + 4e-7f * extent);
     if (!recs.empty()) {
-        EditRec* d_recs = nullptr;
-        CU(cudaMalloc(&d_recs, recs.size() * sizeof(EditRec)));
+        if (recs.size() > ctx->edit_recs_cap) {
+            cudaFree(ctx->d_edit_recs);
+            ctx->d_edit_recs = nullptr;
+            ctx->edit_recs_cap = 0;
+            const size_t cap = std::max<size_t>(4096, recs.size() + recs.size() / 2);
+            CU(cudaMalloc(&ctx->d_edit_recs, cap * sizeof(EditRec)));
+            ctx->edit_recs_cap = cap;
+        }
+        EditRec* d_recs = static_cast<EditRec*>(ctx->d_edit_recs);
         CU(cudaMemcpyAsync(d_recs, recs.data(), recs.size() * sizeof(EditRec), cudaMemcpyHostToDevice, ctx->stream));
         const int n = (int)recs.size();
         k_apply_edits<<<(n + 255) / 256, 256, 0, ctx->stream>>>(d_recs, n, ctx->d_prims, ctx->d_prim_k, ctx->d_mats, ctx->d_nodes, ctx->d_leaf_ref);
@@ -661,8 +671,7 @@ crt_status crt_scene_commit(crt_context* ctx, int force_rebuild, int* out_rebuil
                                                               ctx->d_visits, np, ctx->abs_pad);
         CU(cudaGetLastError());
         ctx->launches += 2;
-        CU(cudaStreamSynchronize(ctx->stream));
-        cudaFree(d_recs);
+        CU(cudaStreamSynchronize(ctx->stream)); // recs is a local
         ctx->stats.h2d_bytes = recs.size() * sizeof(EditRec);
     }
     ctx->stats.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
