@@ -219,10 +219,14 @@ def run_gpu_arm(args):
 
     def e2e_step():
         """Through the C ABI with HOST buffers: scene upload (BVH build + H2D), camera, render, (reduce), resolve, D2H."""
+        t0 = time.perf_counter()
         r.upload(scene)
+        t1 = time.perf_counter()
         r.set_camera(cam)
         accum.zero_()
         r.render(spp=spp, max_depth=depth, spp_begin=rank, spp_stride=world, variant=variant)
+        if os.environ.get("BENCH_DEBUG"):
+            print(f"[e2e] upload {1e3 * (t1 - t0):.1f} ms, render {r.last_render_ms():.1f} ms (library events)", file=sys.stderr)
         if world > 1:
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
         if rank == 0:
