@@ -132,6 +132,7 @@ SIGNATURES = {
                                  C.POINTER(C.c_int32)]),
     "crt_free": (None, [_P]),
     "crt_write_ppm": (C.c_int, [C.c_char_p, _P, C.c_uint32, C.c_uint32, C.c_int]),
+    "crt_write_png": (C.c_int, [C.c_char_p, _P, C.c_uint32, C.c_uint32, C.c_int]),
     # include/crt_legacy.h
     "LaunchKernel": (None, [_P, C.c_uint, C.c_uint, C.c_uint, C.c_uint, _P, _P, InputStruct]),
     "LaunchRandInit": (None, [_P]),

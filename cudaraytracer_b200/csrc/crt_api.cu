@@ -1306,4 +1306,80 @@ crt_status crt_write_ppm(const char* path, const uint32_t* rgba8, uint32_t width
     return CRT_OK;
 }
 
+// PNG (ISO/IEC 15948), 8-bit RGB, filter 0 on every row, the zlib stream made of STORED deflate blocks: readable by every
+// decoder, no compressor needed. The reference links stb_image_write for this (Utils/RawStbImage.h:8-9) and never calls it.
+crt_status crt_write_png(const char* path, const uint32_t* rgba8, uint32_t width, uint32_t height, int flip_rows)
+{
+    if (!path || !rgba8 || !width || !height) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_write_png: bad argument");
+    static uint32_t crc_table[256];
+    static std::once_flag once;
+    std::call_once(once, [] {
+        for (uint32_t n = 0; n < 256; n++) {
+            uint32_t c = n;
+            for (int k = 0; k < 8; k++) c = (c & 1u) ? 0xedb88320u ^ (c >> 1) : c >> 1;
+            crc_table[n] = c;
+        }
+    });
+    auto be32 = [](unsigned char* p, uint32_t v) { p[0] = (unsigned char)(v >> 24); p[1] = (unsigned char)(v >> 16); p[2] = (unsigned char)(v >> 8); p[3] = (unsigned char)v; };
+    // raw scanlines: filter byte + RGB
+    const size_t stride = 1 + (size_t)width * 3;
+    std::vector<unsigned char> raw(stride * height);
+    for (uint32_t r = 0; r < height; r++) {
+        const uint32_t* src = rgba8 + (size_t)(flip_rows ? height - 1 - r : r) * width;
+        unsigned char* row = raw.data() + stride * r;
+        row[0] = 0;
+        for (uint32_t x = 0; x < width; x++) {
+            row[1 + 3 * x] = src[x] & 255; row[2 + 3 * x] = (src[x] >> 8) & 255; row[3 + 3 * x] = (src[x] >> 16) & 255;
+        }
+    }
+    // zlib: header, stored blocks of at most 65535 bytes, Adler-32 of the raw data
+    std::vector<unsigned char> z;
+    z.reserve(raw.size() + raw.size() / 65535 * 5 + 16);
+    z.push_back(0x78); z.push_back(0x01);
+    uint32_t a = 1, b = 0;
+    for (size_t off = 0; off < raw.size();) {
+        const size_t n = std::min<size_t>(65535, raw.size() - off);
+        z.push_back(off + n == raw.size() ? 1 : 0);
+        z.push_back((unsigned char)(n & 255)); z.push_back((unsigned char)(n >> 8));
+        z.push_back((unsigned char)(~n & 255)); z.push_back((unsigned char)((~n >> 8) & 255));
+        z.insert(z.end(), raw.begin() + off, raw.begin() + off + n);
+        for (size_t i = 0; i < n;) { // Adler-32 in runs short enough not to overflow 32 bits
+            const size_t run = std::min<size_t>(5552, n - i);
+            for (size_t k = 0; k < run; k++) { a += raw[off + i + k]; b += a; }
+            a %= 65521u; b %= 65521u;
+            i += run;
+        }
+        off += n;
+    }
+    unsigned char ad[4];
+    be32(ad, b << 16 | a);
+    z.insert(z.end(), ad, ad + 4);
+    FILE* f = fopen(path, "wb");
+    if (!f) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_write_png: cannot open output file");
+    auto chunk = [&](const char type[4], const unsigned char* data, size_t n) {
+        unsigned char head[8];
+        be32(head, (uint32_t)n);
+        memcpy(head + 4, type, 4);
+        uint32_t c = 0xffffffffu;
+        for (int i = 4; i < 8; i++) c = crc_table[(c ^ head[i]) & 255] ^ (c >> 8);
+        for (size_t i = 0; i < n; i++) c = crc_table[(c ^ data[i]) & 255] ^ (c >> 8);
+        unsigned char tail[4];
+        be32(tail, c ^ 0xffffffffu);
+        fwrite(head, 1, 8, f);
+        if (n) fwrite(data, 1, n, f);
+        fwrite(tail, 1, 4, f);
+    };
+    static const unsigned char sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    fwrite(sig, 1, 8, f);
+    unsigned char ihdr[13];
+    be32(ihdr, width); be32(ihdr + 4, height);
+    ihdr[8] = 8; ihdr[9] = 2; ihdr[10] = 0; ihdr[11] = 0; ihdr[12] = 0; // 8 bit, truecolour, deflate, adaptive filtering, no interlace
+    chunk("IHDR", ihdr, 13);
+    chunk("IDAT", z.data(), z.size());
+    chunk("IEND", nullptr, 0);
+    const bool ok = ferror(f) == 0;
+    fclose(f);
+    return ok ? CRT_OK : crt_set_error(nullptr, CRT_ERR_INVALID, "crt_write_png: write error");
+}
+
 } // extern "C"

@@ -244,3 +244,8 @@ def unpack_rgba8(img: np.ndarray) -> np.ndarray:
 def write_ppm(path: str, img: np.ndarray, flip_rows: bool = True):
     img = np.ascontiguousarray(img, dtype=np.uint32)
     _check(capi.load().crt_write_ppm(path.encode(), img.ctypes.data_as(C.c_void_p), img.shape[1], img.shape[0], int(flip_rows)))
+
+
+def write_png(path: str, img: np.ndarray, flip_rows: bool = True):
+    img = np.ascontiguousarray(img, dtype=np.uint32)
+    _check(capi.load().crt_write_png(path.encode(), img.ctypes.data_as(C.c_void_p), img.shape[1], img.shape[0], int(flip_rows)))

@@ -243,6 +243,8 @@ crt_status crt_flycam_inputs(const crt_flycam* cam, const float background_start
 
 /* ---- headless framebuffer writer (replaces the GL blit, CudaLayer.cpp:379-386) ---- */
 crt_status crt_write_ppm(const char* path, const uint32_t* rgba8, uint32_t width, uint32_t height, int flip_rows);
+/* The same frame as an 8-bit RGB PNG (stored deflate blocks: no compression, readable everywhere). */
+crt_status crt_write_png(const char* path, const uint32_t* rgba8, uint32_t width, uint32_t height, int flip_rows);
 /* Binary PPM (P6, maxval 255) -> tightly packed RGB8, the layout Image expects (Texture.cuh:76; the reference decodes JPEGs with
  * stb_image, Utils/RawStbImage.h:11-22, which is third-party code this library does not carry). *out_pixels is malloc'ed;
  * release it with crt_free. */

@@ -244,3 +244,39 @@ def test_textured_scene_takes_the_reference_assets_when_pointed_at_them(monkeypa
     p = s2.desc
     assert (p.images[0].width, p.images[0].height) == (8192, 4096)
     assert not np.array_equal(np.ctypeslib.as_array(p.images[1].pixels, shape=(1241, 1241, 3)), want)
+
+
+def test_png_writer_round_trip(tmp_path):
+    """crt_write_png: chunk CRCs, a zlib stream every inflater accepts, the pixels of the frame (rows flipped on request)."""
+    import struct
+    import zlib
+    from cudaraytracer_b200 import write_png
+    rng = np.random.default_rng(5)
+    for (W, H) in [(1, 1), (37, 23), (300, 250)]:  # the last one needs more than one stored block (225 750 raw bytes)
+        rgb = rng.integers(0, 256, (H, W, 3), dtype=np.uint32)
+        img = rgb[..., 0] | rgb[..., 1] << 8 | rgb[..., 2] << 16 | np.uint32(0xFF000000)
+        for flip in (False, True):
+            path = str(tmp_path / f"f_{W}_{int(flip)}.png")
+            write_png(path, img, flip_rows=flip)
+            data = open(path, "rb").read()
+            assert data[:8] == b"\x89PNG\r\n\x1a\n"
+            pos, chunks = 8, []
+            while pos < len(data):
+                n, typ = struct.unpack(">I4s", data[pos:pos + 8])
+                body = data[pos + 8:pos + 8 + n]
+                (crc,) = struct.unpack(">I", data[pos + 8 + n:pos + 12 + n])
+                assert crc == zlib.crc32(typ + body) & 0xFFFFFFFF
+                chunks.append((typ, body))
+                pos += 12 + n
+            assert [c[0] for c in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+            assert struct.unpack(">IIBBBBB", chunks[0][1]) == (W, H, 8, 2, 0, 0, 0)
+            raw = np.frombuffer(zlib.decompress(chunks[1][1]), dtype=np.uint8).reshape(H, 1 + 3 * W)
+            assert (raw[:, 0] == 0).all()
+            want = rgb[::-1] if flip else rgb
+            assert np.array_equal(raw[:, 1:].reshape(H, W, 3), want.astype(np.uint8))
+            try:
+                from PIL import Image
+                assert np.array_equal(np.asarray(Image.open(path).convert("RGB")), want.astype(np.uint8))
+            except ImportError:
+                pass
+    assert capi.load().crt_write_png(b"/nonexistent/dir/x.png", img.ctypes.data_as(C.c_void_p), 300, 250, 0) != 0
