@@ -55,6 +55,7 @@ struct crt_context
     int* d_parent = nullptr;
     int* d_leaf_ref = nullptr;
     unsigned int* d_visits = nullptr;
+    int32_t top_hittable[CRT_MAX_TOP] = {-1, -1, -1, -1}; // hittable index behind each peeled leaf (their codes carry the material type)
     void* d_edit_recs = nullptr;     // staging for crt_scene_commit's refit path (grow-only: no allocation per commit)
     size_t edit_recs_cap = 0;
     float abs_pad = 0.f, scene_extent = 0.f;
@@ -277,6 +278,20 @@ static crt_status upload_images(crt_context* ctx, const crt_scene_desc* sd, std:
     return CRT_OK;
 }
 
+// Records the peeled top of the tree in the device scene. prim_id: leaf slot -> hittable index (host copy).
+static void install_peel(crt_context* ctx, const CrtPackedNode* top_nodes, size_t n_top_nodes, uint64_t n_prims, const int32_t* prim_id)
+{
+    DevScene& S = ctx->scene;
+    int32_t entry = 0, codes[CRT_MAX_TOP] = {0, 0, 0, 0};
+    const int n = getenv("CRT_NO_PEEL") ? 0 : crt_peel_top(top_nodes, n_top_nodes, n_prims, CRT_MAX_TOP, &entry, codes);
+    S.entry = entry;
+    S.n_top = n;
+    for (int k = 0; k < CRT_MAX_TOP; k++) {
+        S.top_code[k] = k < n ? codes[k] : 0;
+        ctx->top_hittable[k] = k < n ? prim_id[codes[k] & CRT_LEAF_INDEX_MASK] : -1;
+    }
+}
+
 static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, const CrtPackedScene& P, bool keep_images)
 {
     CU(cudaSetDevice(ctx->device));
@@ -326,6 +341,7 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
     S.prim_id = ctx->d_prim_id; S.images = ctx->d_images;
     S.n_nodes = (int)nn; S.n_prims = (int)np;
     S.smem_nodes = S.smem_prims = S.smem_mats = 0;
+    install_peel(ctx, P.nodes.data(), nn, np, P.prim_id.data());
     ctx->stats = P.stats;
     ctx->stats.h2d_bytes = h2d;
     ctx->scene_h2d_bytes = h2d;
@@ -475,6 +491,9 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
     }
     LbvhStats hs;
     std::vector<int32_t> prim_id(n);
+    CrtPackedNode top_nodes[16]; // the chain of huge leaves under the root lives in the first few breadth-first nodes
+    const size_t n_top_nodes = std::min<size_t>(16, nn);
+    CUB_(cudaMemcpyAsync(top_nodes, ctx->d_nodes, n_top_nodes * sizeof(CrtPackedNode), cudaMemcpyDeviceToHost, st));
     CUB_(cudaMemcpyAsync(&hs, d_stats, sizeof(hs), cudaMemcpyDeviceToHost, st));
     CUB_(cudaMemcpyAsync(prim_id.data(), ctx->d_prim_id, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
     CUB_(cudaStreamSynchronize(st));
@@ -497,6 +516,7 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
     S.prim_id = ctx->d_prim_id; S.images = ctx->d_images;
     S.n_nodes = (int)nn; S.n_prims = (int)n;
     S.smem_nodes = S.smem_prims = S.smem_mats = 0;
+    install_peel(ctx, top_nodes, n_top_nodes, n, prim_id.data());
     memset(&ctx->stats, 0, sizeof(ctx->stats));
     ctx->stats.n_prims = n;
     ctx->stats.n_nodes = nn;
@@ -645,6 +665,8 @@ crt_status crt_scene_commit(crt_context* ctx, int force_rebuild, int* out_rebuil
         r.child_code = ~(int32_t)(((uint32_t)h.type << CRT_LEAF_TYPE_SHIFT) |
                                   ((uint32_t)ctx->host.materials[h.material].type << CRT_LEAF_MAT_SHIFT) | (uint32_t)slot);
         recs.push_back(r);
+        for (int k = 0; k < ctx->scene.n_top; k++) // a peeled leaf is named by its code in the kernel arguments, not by the node
+            if (ctx->top_hittable[k] == (int32_t)idx) ctx->scene.top_code[k] = ~r.child_code;
         const float reach = fabsf(h.a) + fabsf(h.b);
         extent = std::max(extent, std::max(fabsf(h.cx), std::max(fabsf(h.cy), fabsf(h.cz))) + reach);
     }

@@ -56,6 +56,12 @@ struct CrtPackedScene
     crt_bvh_stats stats;
 };
 
+// Peels the chain of huge leaves off the top of a packed tree (DevScene::entry / top_code, device_common.cuh): starting at
+// the root, while a node has exactly one leaf child whose box is at least a quarter of the node's own, that leaf is recorded
+// (its code, and the slot in it) and the walk goes on in the other child. `nodes` are the first `n_nodes` packed nodes of the
+// tree (the chain is at the top, so a short prefix is enough). Returns the number of peeled leaves (<= max_top).
+int crt_peel_top(const CrtPackedNode* nodes, size_t n_nodes, uint64_t n_prims, int max_top, int32_t* entry, int32_t* codes);
+
 // Builds the BVH over the ACTIVE hittables (Hittable.cuh:311-320 filters inactive ones) and packs everything.
 // Returns false and fills err on invalid input.
 bool crt_pack_scene(const crt_scene_desc* scene, CrtPackedScene* out, std::string* err);

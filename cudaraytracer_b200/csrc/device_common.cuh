@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #define CRT_STACK_SIZE 64
+#define CRT_MAX_TOP 4
 #define CRT_BLOCK_THREADS 256
 
 
@@ -24,6 +25,11 @@ struct DevScene
     const DevImage* images;
     int n_nodes, n_prims;
     int smem_nodes, smem_prims, smem_mats; // how many of each the kernels stage in shared memory
+    // Primitives peeled off the top of the tree (trace.cuh trav_begin): a chain root = {huge leaf, rest} (the ground sphere of
+    // every benchmark scene) costs every ray an inner-node visit whose outcome is known. Such leaves are tested when a ray
+    // starts, and the traversal starts at `entry`, the first node below the chain.
+    int entry, n_top;
+    int top_code[CRT_MAX_TOP];
 };
 
 struct DevCamera

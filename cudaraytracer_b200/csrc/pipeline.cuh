@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
                 r = trav_setup<false>(f3(a0.x, a0.y, a0.z), f3(a0.w, b0.x, b0.y));
                 h.t = 3.402823466e+38f;
                 h.leaf = -1;
-                cur = 0;
+                cur = trav_begin<false, SMEM_ALL>(S, r, t_min, h);
                 sp = 0;
             }
             refill_short = n < __popc(m);

@@ -296,6 +296,33 @@ void crt_pack_material(const crt_scene_desc* sd, const crt_material& m, float mr
     memcpy(&mr[7], &bits, 4);
 }
 
+int crt_peel_top(const CrtPackedNode* nodes, size_t n_nodes, uint64_t n_prims, int max_top, int32_t* entry, int32_t* codes)
+{
+    *entry = 0;
+    if (n_prims < 3 || !n_nodes) return 0; // one / two primitives: nothing below a peeled leaf
+    int n_top = 0;
+    size_t node = 0;
+    while (n_top < max_top && node < n_nodes) {
+        const CrtPackedNode& nd = nodes[node];
+        const bool leaf0 = nd.child[0] < 0, leaf1 = nd.child[1] < 0;
+        if (leaf0 == leaf1) break; // two inner children: the tree proper starts here; two leaves: nothing below
+        const int lc = leaf0 ? 0 : 1;
+        // boxes are {c.xyz, h.xyz}: the node's own box is the union of its two child boxes
+        const float* a = nd.w + 6 * lc;
+        const float* b = nd.w + 6 * (1 - lc);
+        float ext[3];
+        for (int i = 0; i < 3; i++)
+            ext[i] = 0.5f * (std::max(a[i] + a[3 + i], b[i] + b[3 + i]) - std::min(a[i] - a[3 + i], b[i] - b[3 + i]));
+        const float area_leaf = a[3] * a[4] + a[4] * a[5] + a[5] * a[3], area_node = ext[0] * ext[1] + ext[1] * ext[2] + ext[2] * ext[0];
+        if (!(area_leaf >= 0.25f * area_node)) break; // a small leaf next to the root: its box test culls it, keep it in the tree
+        codes[n_top++] = ~nd.child[lc];
+        node = (size_t)nd.child[1 - lc];
+        *entry = (int32_t)node;
+    }
+    if (node >= n_nodes) { *entry = 0; return 0; } // chain longer than the prefix we were given: do not peel
+    return n_top;
+}
+
 // Validation of one ACTIVE hittable and of everything it references (shared by the host and the GPU build paths).
 static bool check_hittable(const crt_scene_desc* sd, uint64_t i, std::string* err)
 {

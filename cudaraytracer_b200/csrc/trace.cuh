@@ -22,6 +22,8 @@ struct SceneView
     const float4* s_mats;
     const DevImage* images;
     int smem_nodes, smem_prims, smem_mats;
+    int entry, n_top;
+    int top_code[CRT_MAX_TOP];
 };
 
 // 32 bytes through the read-only path in one instruction (PTX 8.8 ld.global.nc.v8, 32-byte aligned address).
@@ -94,6 +96,8 @@ template <bool PAD> __device__ __forceinline__ SceneView stage_scene(const DevSc
     SceneView S;
     S.g_nodes = D.nodes; S.g_prims = D.prims; S.g_prim_k = D.prim_k; S.g_mats = D.mats; S.images = D.images;
     S.smem_nodes = D.smem_nodes; S.smem_prims = D.smem_prims; S.smem_mats = D.smem_mats;
+    S.entry = D.entry; S.n_top = D.n_top;
+    for (int k = 0; k < CRT_MAX_TOP; k++) S.top_code[k] = D.top_code[k];
     float4* sn = smem;
     float4* sp = sn + (PAD ? CRT_SMEM_NODE_F4 : 4) * (size_t)D.smem_nodes;
     float4* sm = sp + D.smem_prims;
@@ -298,6 +302,25 @@ __device__ __forceinline__ void leaf_step(const SceneView& S, const TravRay& r, 
     cur = sp ? stack[--sp] : CRT_TRAV_DONE;
 }
 
+// Start of a closest-hit query: the primitives peeled off the top of the tree (DevScene::top_code) are tested here, without
+// their boxes, and the descent starts below them. Returns the node to start at.
+template <bool EXACT, bool SMEM_ALL>
+__device__ __forceinline__ int trav_begin(const SceneView& S, const TravRay& r, float t_min, Hit& h)
+{
+#pragma unroll
+    for (int k = 0; k < CRT_MAX_TOP; k++) {
+        if (k < S.n_top) {
+            const int code = S.top_code[k];
+            float t;
+            if (leaf_test<EXACT, SMEM_ALL>(S, code, r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) {
+                h.t = t;
+                h.leaf = code;
+            }
+        }
+    }
+    return S.entry;
+}
+
 // Closest hit in (t_min, t_max). Near-first ordered descent with a per-thread stack.
 template <bool EXACT, bool COUNT, bool SMEM_ALL>
 __device__ __forceinline__ Hit closest_hit(const SceneView& S, float3 o, float3 d, float t_min, float t_max, unsigned& n_box,
@@ -309,7 +332,8 @@ __device__ __forceinline__ Hit closest_hit(const SceneView& S, float3 o, float3 
     const TravRay r = trav_setup<EXACT>(o, d);
     int stack[CRT_STACK_SIZE];
     int sp = 0;
-    int cur = 0; // >= 0: inner node, < 0: leaf (~code), CRT_TRAV_DONE: finished
+    int cur = trav_begin<EXACT, SMEM_ALL>(S, r, t_min, h); // >= 0: inner node, < 0: leaf (~code), CRT_TRAV_DONE: finished
+    if (COUNT) n_prim += (unsigned)S.n_top;
     while (true) {
         node_step<EXACT, SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
         if (COUNT) n_box += 2;
