@@ -68,7 +68,7 @@ struct Builder
     std::atomic<int> max_depth{0};
     int par_depth = 10; // levels whose left subtree gets its own thread (CRT_BVH_PAR_DEPTH; 0 = single-threaded build)
 
-    static constexpr int kBins = 16;
+    static constexpr int kBins = 64;
 
     Box range_box(uint32_t b, uint32_t e) const
     {
