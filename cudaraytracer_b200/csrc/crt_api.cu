@@ -56,6 +56,9 @@ struct crt_context
     int* d_leaf_ref = nullptr;
     unsigned int* d_visits = nullptr;
     int32_t top_hittable[CRT_MAX_TOP] = {-1, -1, -1, -1}; // hittable index behind each peeled leaf (their codes carry the material type)
+    size_t cap_nodes = 0, cap_prims = 0; // element capacity of the geometry arrays (re-uploads of a same-sized scene reuse them)
+    unsigned char* build_arena = nullptr; // scratch of the GPU builder, kept between builds (grow-only)
+    size_t build_arena_bytes = 0;
     void* d_edit_recs = nullptr;     // staging for crt_scene_commit's refit path (grow-only: no allocation per commit)
     size_t edit_recs_cap = 0;
     float abs_pad = 0.f, scene_extent = 0.f;
@@ -123,15 +126,44 @@ static void free_geometry(crt_context* ctx)
     cudaFree(ctx->d_parent); ctx->d_parent = nullptr;
     cudaFree(ctx->d_leaf_ref); ctx->d_leaf_ref = nullptr;
     cudaFree(ctx->d_visits); ctx->d_visits = nullptr;
+    ctx->cap_nodes = ctx->cap_prims = 0;
     ctx->have_scene = false;
+}
+
+// Device arrays for a tree of nn nodes over np primitives. A scene of the same size (the usual re-upload: the same scene
+// again, or after an edit) keeps the allocations: cudaMalloc / cudaFree of hundreds of MB synchronise the device and have
+// been seen to stall for hundreds of ms when several processes share the box.
+static crt_status ensure_geometry(crt_context* ctx, size_t nn, size_t np)
+{
+    nn = std::max<size_t>(nn, 1);
+    np = std::max<size_t>(np, 1);
+    ctx->have_scene = false;
+    if (ctx->d_nodes && nn <= ctx->cap_nodes && np <= ctx->cap_prims && nn * 2 > ctx->cap_nodes && np * 2 > ctx->cap_prims) return CRT_OK;
+    free_geometry(ctx);
+    CU(cudaMalloc(&ctx->d_nodes, nn * 64));
+    CU(cudaMalloc(&ctx->d_parent, nn * 4));
+    CU(cudaMalloc(&ctx->d_visits, nn * 4));
+    CU(cudaMalloc(&ctx->d_leaf_ref, np * 4));
+    CU(cudaMalloc(&ctx->d_prims, np * 16));
+    CU(cudaMalloc(&ctx->d_prim_k, np * 4));
+    CU(cudaMalloc(&ctx->d_mats, np * 32));
+    CU(cudaMalloc(&ctx->d_prim_id, np * 4));
+    ctx->cap_nodes = nn;
+    ctx->cap_prims = np;
+    return CRT_OK;
+}
+
+static void free_images(crt_context* ctx)
+{
+    cudaFree(ctx->d_images); ctx->d_images = nullptr;
+    for (uchar4* p : ctx->d_texels) cudaFree(p);
+    ctx->d_texels.clear();
 }
 
 static void free_scene(crt_context* ctx)
 {
     free_geometry(ctx);
-    cudaFree(ctx->d_images); ctx->d_images = nullptr;
-    for (uchar4* p : ctx->d_texels) cudaFree(p);
-    ctx->d_texels.clear();
+    free_images(ctx);
 }
 
 extern "C" {
@@ -220,6 +252,7 @@ void crt_context_destroy(crt_context* ctx)
     cudaFree(ctx->d_counters);
     cudaFree(ctx->d_shards);
     cudaFree(ctx->d_edit_recs);
+    cudaFree(ctx->build_arena);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -296,24 +329,19 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
 {
     CU(cudaSetDevice(ctx->device));
     CU(cudaStreamSynchronize(ctx->stream));
-    if (keep_images) free_geometry(ctx);
-    else free_scene(ctx);
+    if (!keep_images) free_images(ctx);
     const size_t nn = P.nodes.size(), np = P.prim_id.size();
     uint64_t h2d = 0;
-    CU(cudaMalloc(&ctx->d_parent, std::max<size_t>(nn, 1) * 4));
-    CU(cudaMalloc(&ctx->d_visits, std::max<size_t>(nn, 1) * 4));
-    CU(cudaMalloc(&ctx->d_leaf_ref, std::max<size_t>(np, 1) * 4));
+    {
+        crt_status gst = ensure_geometry(ctx, nn, np);
+        if (gst != CRT_OK) return gst;
+    }
     CU(cudaMemcpyAsync(ctx->d_parent, P.parent.data(), nn * 4, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->d_leaf_ref, P.leaf_ref.data(), np * 4, cudaMemcpyHostToDevice, ctx->stream));
     h2d += (nn + np) * 4;
     ctx->abs_pad = P.abs_pad;
-    CU(cudaMalloc(&ctx->d_nodes, std::max<size_t>(nn, 1) * 64));
     CU(cudaMemcpyAsync(ctx->d_nodes, P.nodes.data(), nn * 64, cudaMemcpyHostToDevice, ctx->stream));
     h2d += nn * 64;
-    CU(cudaMalloc(&ctx->d_prims, std::max<size_t>(np, 1) * 16));
-    CU(cudaMalloc(&ctx->d_prim_k, std::max<size_t>(np, 1) * 4));
-    CU(cudaMalloc(&ctx->d_mats, std::max<size_t>(np, 1) * 32));
-    CU(cudaMalloc(&ctx->d_prim_id, std::max<size_t>(np, 1) * 4));
     if (np) {
         CU(cudaMemcpyAsync(ctx->d_prims, P.prims.data(), np * 16, cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaMemcpyAsync(ctx->d_prim_k, P.prim_k.data(), np * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -365,8 +393,7 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
     if (n < 2) return CRT_OK; // the degenerate trees (empty scene, one primitive) are the host builder's business
     CU(cudaSetDevice(ctx->device));
     CU(cudaStreamSynchronize(ctx->stream));
-    if (keep_images) free_geometry(ctx);
-    else free_scene(ctx);
+    if (!keep_images) free_images(ctx);
     cudaStream_t st = ctx->stream;
     uint64_t h2d = 0;
     // everything that only lives during the build comes out of ONE device allocation (20 cudaMalloc/cudaFree pairs cost more
@@ -395,9 +422,7 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
                  o_c0 = reserve(ploc ? (size_t)n * sizeof(PlocCluster) : 0), o_c1 = reserve(ploc ? (size_t)n * sizeof(PlocCluster) : 0),
                  o_nn = reserve(ploc ? (size_t)n * 4 : 0), o_flags = reserve(ploc ? (size_t)n * 8 : 0), o_scan = reserve(ploc ? (size_t)n * 8 : 0),
                  o_counts = reserve(16);
-    unsigned char* arena = nullptr;
     auto cleanup = [&]() {
-        cudaFree(arena);
         for (unsigned char* p : raw_rgb) cudaFree(p);
     };
 #define CUB_(call)                                                                     \
@@ -405,7 +430,14 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
         cudaError_t e__ = (call);                                                      \
         if (e__ != cudaSuccess) { cleanup(); return cuda_fail(ctx, e__, #call); }      \
     } while (0)
-    CUB_(cudaMalloc(&arena, arena_bytes));
+    if (arena_bytes > ctx->build_arena_bytes) { // kept between builds: see ensure_geometry
+        cudaFree(ctx->build_arena);
+        ctx->build_arena = nullptr;
+        ctx->build_arena_bytes = 0;
+        CUB_(cudaMalloc(&ctx->build_arena, arena_bytes));
+        ctx->build_arena_bytes = arena_bytes;
+    }
+    unsigned char* arena = ctx->build_arena;
     crt_hittable* d_h = reinterpret_cast<crt_hittable*>(arena + o_h);
     crt_material* d_m = reinterpret_cast<crt_material*>(arena + o_m);
     crt_texture* d_t = reinterpret_cast<crt_texture*>(arena + o_t);
@@ -419,21 +451,16 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
     int* d_parent2 = reinterpret_cast<int*>(arena + o_parent2);
     LbvhStats* d_stats = reinterpret_cast<LbvhStats*>(arena + o_stats);
     void* d_tmp = arena + o_tmp;
+    {
+        crt_status gst = ensure_geometry(ctx, nn, n);
+        if (gst != CRT_OK) { cleanup(); return gst; }
+    }
     CUB_(cudaMemcpyAsync(d_h, sd->hittables, sd->n_hittables * sizeof(crt_hittable), cudaMemcpyHostToDevice, st));
     CUB_(cudaMemcpyAsync(d_m, sd->materials, sd->n_materials * sizeof(crt_material), cudaMemcpyHostToDevice, st));
     CUB_(cudaMemcpyAsync(d_t, sd->textures, sd->n_textures * sizeof(crt_texture), cudaMemcpyHostToDevice, st));
     CUB_(cudaMemcpyAsync(d_ip, present.data(), present.size(), cudaMemcpyHostToDevice, st));
     CUB_(cudaMemcpyAsync(d_act, active.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
     h2d += sd->n_hittables * sizeof(crt_hittable) + sd->n_materials * sizeof(crt_material) + sd->n_textures * sizeof(crt_texture) + (uint64_t)n * 4;
-    // outputs
-    CUB_(cudaMalloc(&ctx->d_nodes, nn * 64));
-    CUB_(cudaMalloc(&ctx->d_parent, nn * 4));
-    CUB_(cudaMalloc(&ctx->d_visits, nn * 4));
-    CUB_(cudaMalloc(&ctx->d_leaf_ref, (size_t)n * 4));
-    CUB_(cudaMalloc(&ctx->d_prims, (size_t)n * 16));
-    CUB_(cudaMalloc(&ctx->d_prim_k, (size_t)n * 4));
-    CUB_(cudaMalloc(&ctx->d_mats, (size_t)n * 32));
-    CUB_(cudaMalloc(&ctx->d_prim_id, (size_t)n * 4));
 
     auto t_alloc = std::chrono::steady_clock::now();
     LbvhRaw R;
