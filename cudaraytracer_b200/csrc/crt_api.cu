@@ -1089,32 +1089,30 @@ __global__ void k_pipe_init(WfShard* shards, uint32_t work_total)
     shards[i].end = b + per + (i < extra ? 1u : 0u);
 }
 
-template <int THRESH, bool ALL> static cudaError_t launch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st)
+template <int NSLOTS, bool ALL> static cudaError_t launch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st)
 {
     static size_t configured[CRT_MAX_DEVICES] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     size_t& configured_smem = configured[dev & (CRT_MAX_DEVICES - 1)];
     if (smem > configured_smem) {
-        cudaError_t e = cudaFuncSetAttribute(k_render_pipe<THRESH, ALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(k_render_pipe<NSLOTS, ALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured_smem = smem;
     }
-    k_render_pipe<THRESH, ALL><<<grid, PIPE_THREADS, smem, st>>>(W);
+    k_render_pipe<NSLOTS, ALL><<<grid, PIPE_THREADS, smem, st>>>(W);
     return cudaGetLastError();
 }
 
-static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st, int thresh, bool all)
+// the two pool sizes the planner picks have kernels with the size compiled in; anything else (CRT_PIPE_SLOTS) runs the generic one
+static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st, bool all)
 {
-#define CRT_PIPE_CASE(T) case T: return all ? launch_pipe<T, true>(W, grid, smem, st) : launch_pipe<T, false>(W, grid, smem, st)
-    switch (thresh) {
-        CRT_PIPE_CASE(12);
-        CRT_PIPE_CASE(16);
-        CRT_PIPE_CASE(24);
-        CRT_PIPE_CASE(28);
-        CRT_PIPE_CASE(32);
+#define CRT_PIPE_CASE(N) case N: return all ? launch_pipe<N, true>(W, grid, smem, st) : launch_pipe<N, false>(W, grid, smem, st)
+    switch (W.n_slots) {
+        CRT_PIPE_CASE(1024);
+        CRT_PIPE_CASE(2048);
     default:
-        CRT_PIPE_CASE(20);
+        CRT_PIPE_CASE(0);
     }
 #undef CRT_PIPE_CASE
 }
@@ -1158,6 +1156,7 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
     W.stat = ctx->d_counters;
     W.n_pixels_cover = (uint32_t)P;
     W.n_slots = n_slots;
+    W.thresh = std::min(std::max(ctx->pipe_thresh, 1), 32);
     W.max_rounds = ctx->pipe_rounds;
     W.check_every = ctx->pipe_check;
     W.ext_low = ctx->pipe_ext_low;
@@ -1171,7 +1170,7 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
         W.R.spp_stride = stride;
         k_pipe_init<<<1, WF_SHARDS, 0, ctx->stream>>>(ctx->d_shards, (uint32_t)(P * spp));
         CU(cudaGetLastError());
-        CU(dispatch_pipe(W, ctx->sm_count, smem, ctx->stream, ctx->pipe_thresh, all));
+        CU(dispatch_pipe(W, ctx->sm_count, smem, ctx->stream, all));
         const uint32_t npx = A.cover_w * A.cover_h;
         k_wf_add_count<<<(npx + 255) / 256, 256, 0, ctx->stream>>>(A.accum, A.width, A.cover_w, A.cover_h, (long long)spp);
         CU(cudaGetLastError());

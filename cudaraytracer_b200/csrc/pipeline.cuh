@@ -32,6 +32,7 @@ struct PipeArgs
     DevCounters* stat;       // CRT_COUNTER_SHARDS ray/path counters
     uint32_t n_pixels_cover; // work item w -> sample w / n_pixels_cover, pixel w % n_pixels_cover
     int n_slots;             // N, a power of two
+    int thresh;              // traversal leaves its loop when fewer lanes than this are busy (a refill is due)
     int max_rounds;          // traversal rounds between two refills at most
     int check_every;         // a warp looks for shade/generate work every check_every-th iteration ...
     int ext_low;             // ... and whenever the EXT queue held fewer rays than this at its last refill
@@ -224,23 +225,24 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
     pipe_push(P, ctl, PQ_GEN, ended, slot, lt);
 }
 
-template <int THRESH, bool SMEM_ALL>
+// NSLOTS > 0: the pool size is a compile-time constant. The pool sits at the START of dynamic shared memory, so every pool
+// and ring address is `constant + index`: with a run-time N behind the scene tables the compiler re-derived those addresses from
+// kernel parameters at each use (3.7 % of the executed instructions, profiles/r01_j). NSLOTS == 0 takes N from the arguments.
+template <int NSLOTS, bool SMEM_ALL>
 __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_constant__ PipeArgs A)
 {
     extern __shared__ float4 smem[];
     __shared__ PipeCtl ctl;
-    const SceneView S = stage_scene<true>(A.R.scene, smem);
     PipePool P;
-    {
-        float4* p = smem + CRT_SMEM_NODE_F4 * (size_t)A.R.scene.smem_nodes + A.R.scene.smem_prims + 2 * (size_t)A.R.scene.smem_mats;
-        P.n = A.n_slots;
-        P.mask = (unsigned int)A.n_slots - 1u;
-        P.a = p; p += P.n;
-        P.b = p; p += P.n;
-        P.c = p; p += P.n;
-        P.px = reinterpret_cast<uint2*>(p); p += P.n / 2;
-        P.ring = reinterpret_cast<unsigned short*>(p);
-    }
+    P.n = NSLOTS > 0 ? NSLOTS : A.n_slots;
+    P.mask = (unsigned int)P.n - 1u;
+    P.a = smem;
+    P.b = smem + P.n;
+    P.c = smem + 2 * P.n;
+    P.px = reinterpret_cast<uint2*>(smem + 3 * P.n);
+    P.ring = reinterpret_cast<unsigned short*>(smem + 3 * P.n + P.n / 2);
+    // 70 bytes per slot: N is a multiple of 64, so the scene tables that follow stay 16-byte aligned
+    const SceneView S = stage_scene<true>(A.R.scene, smem + (3 * P.n + P.n / 2) + (PQ_COUNT * P.n) / 8);
     for (int i = threadIdx.x; i < PQ_COUNT * P.n; i += PIPE_THREADS) P.ring[i] = (unsigned short)(i >= PQ_GEN * P.n ? i - PQ_GEN * P.n : PIPE_EMPTY);
     if (threadIdx.x <= PQ_COUNT) { ctl.head[threadIdx.x] = 0u; ctl.tail[threadIdx.x] = threadIdx.x == PQ_GEN ? (unsigned int)P.n : 0u; }
     if (threadIdx.x == 0) ctl.live = P.n; // every slot starts in the GEN queue
@@ -319,7 +321,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
             continue;
         }
         // ---- traverse: until fewer than THRESH lanes are busy (a refill is due) or it is time to look at the queues ----
-        const int leave_below = refill_short ? 1 : THRESH; // EXT ran dry: leaving early would only spin
+        const int leave_below = refill_short ? 1 : A.thresh; // EXT ran dry: leaving early would only spin
         int rounds_left = A.max_rounds;
         while (true) { // two node visits per vote
             node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
