@@ -34,7 +34,7 @@ struct PipeArgs
     int n_slots;             // N, a power of two
     int thresh;              // traversal leaves its loop when fewer lanes than this are busy (a refill is due)
     int max_rounds;          // traversal rounds between two refills at most
-    int check_every;         // a warp looks for shade/generate work every check_every-th iteration ...
+    int check_mask;          // a warp looks for shade/generate work when (iteration & check_mask) == 0 (every 2^k-th) ...
     int ext_low;             // ... and whenever the EXT queue held fewer rays than this at its last refill
 };
 
@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         bool worked = false;
         // ---- shade / generate duty: lanes 1..6 each look at one queue. With 32 warps looking, every A.check_every-th
         //      iteration of a warp is enough to keep the class queues short; a warp that could not refill looks at once ----
-        if (refill_short || ext_left < A.ext_low || (it % (unsigned)A.check_every) == 0u) {
+        if (refill_short || ext_left < A.ext_low || (it & (unsigned)A.check_mask) == 0u) {
             int sz = 0;
             if (lane < PQ_COUNT) sz = (int)(*(volatile unsigned int*)&ctl.tail[lane] - *(volatile unsigned int*)&ctl.head[lane]);
             const unsigned full_q = __ballot_sync(0xffffffffu, lane >= 1u && sz >= 32);
