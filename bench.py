@@ -197,7 +197,14 @@ def run_gpu_arm(args):
     r.resize(W, H)
     # the progressive accumulation buffer: int64 x {R, G, B, samples}, Q31.32 sums (order-free, so the NCCL sum is exact)
     accum = torch.zeros((H, W, 4), dtype=torch.int64, device=dev)
-    r.set_accum_device_buffer(accum.data_ptr())
+    peer = None
+    tiles = args.closeout == "tiles"
+    if args.closeout in ("peer", "tiles"):
+        # the ranks keep their library-owned buffers, mapped into each other (CUDA IPC): no reduce-to-root (multigpu.PeerFrame)
+        from cudaraytracer_b200.multigpu import PeerFrame
+        peer = PeerFrame(r, rank, world)
+    else:
+        r.set_accum_device_buffer(accum.data_ptr())
     rgba = torch.zeros((H, W), dtype=torch.int32, device=dev)
     host_rgba = torch.zeros((H, W), dtype=torch.int32).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2: written between timed steps
@@ -210,6 +217,16 @@ def run_gpu_arm(args):
 
     def device_step():
         """Scene resident in HBM: clear + render this rank's samples (+ reduce) + resolve on rank 0."""
+        if tiles:  # image-tile sharding: ALL samples of this rank's row slabs; nothing to sum, 4 B/pixel to the root's frame
+            r.clear()
+            r.render(spp=spp * world, max_depth=depth, variant=variant, row_tiles=capi.row_tiles(rank, world, args.tile_rows))
+            peer.close_frame_tiles(args.tile_rows)
+            return
+        if peer is not None:
+            r.clear()
+            r.render(spp=spp, max_depth=depth, spp_begin=rank, spp_stride=world, variant=variant)
+            peer.close_frame()  # fence, sum + resolve of this rank's rows into the root's frame over NVLink, fence
+            return
         accum.zero_()
         r.render(spp=spp, max_depth=depth, spp_begin=rank, spp_stride=world, variant=variant)
         if world > 1:
@@ -223,6 +240,17 @@ def run_gpu_arm(args):
         r.upload(scene)
         t1 = time.perf_counter()
         r.set_camera(cam)
+        if peer is not None:
+            r.clear()
+            if tiles:
+                r.render(spp=spp * world, max_depth=depth, variant=variant, row_tiles=capi.row_tiles(rank, world, args.tile_rows))
+                peer.close_frame_tiles(args.tile_rows)
+            else:
+                r.render(spp=spp, max_depth=depth, spp_begin=rank, spp_stride=world, variant=variant)
+                peer.close_frame()
+            if rank == 0:
+                r.read_rgba(host_rgba.numpy().view(np.uint32))  # D2H of the root's frame (synchronises the root's stream)
+            return
         accum.zero_()
         r.render(spp=spp, max_depth=depth, spp_begin=rank, spp_stride=world, variant=variant)
         if os.environ.get("BENCH_DEBUG"):
@@ -283,7 +311,7 @@ def run_gpu_arm(args):
         # roofline of the dominant kernel (k_render_mega: > 99 % of the step): algorithmic flops per ray measured
         # on our own BVH by a counting launch (F_ray = 21 N_box + 26 N_sph + 50)
         r.reset_counters()
-        accum.zero_()
+        r.clear() if peer is not None else accum.zero_()
         r.render(spp=min(spp, 4), max_depth=depth, flags=capi.FLAG_COUNT_TESTS, variant=capi.VARIANT_MEGAKERNEL)
         cc = r.counters()
         n_box, n_sph = cc.box_tests / cc.rays, cc.prim_tests / cc.rays
@@ -293,7 +321,7 @@ def run_gpu_arm(args):
         peak_tflops = FP32_LANES * 2 * sm_mhz * 1e6 / 1e12
         # kernel-only duration: the render launch of the last step, measured by the library's own events
         r.reset_counters()
-        accum.zero_()
+        r.clear() if peer is not None else accum.zero_()
         r.render(spp=spp, max_depth=depth, spp_begin=rank, spp_stride=world, variant=variant)
         k_ms = r.last_render_ms()
         kc = r.counters()
@@ -347,7 +375,10 @@ def run_gpu_arm(args):
                 "config": {"workload": f"{args.workload}: {desc}", "scene_hittables": scene.n_hittables, "bvh_nodes": int(stats.n_nodes),
                            "bvh_builder": {1: "host binned SAH (threaded)", 2: "GPU LBVH"}.get(int(stats.builder), "?"),
                            "variant": args.variant, "variant_resolved": resolved, "spp_per_rank": spp, "spp_total": spp * world,
-                           "parallelism": f"spp-sharded x{world}" + (", one NCCL reduce (int64 sum) of the fixed-point accumulation buffer" if world > 1 else ""),
+                           "parallelism": f"spp-sharded x{world}" + ("" if world == 1 else ", one NCCL reduce (int64 sum) of the fixed-point accumulation buffer" if peer is None
+                                                                     else ", close-out in one kernel per rank over peer memory (sum + resolve of its rows, no reduce-to-root)" if not tiles
+                                                                     else f", image-tile sharded instead (slabs of {args.tile_rows} rows, every rank resolves its rows into the root's frame over peer memory)"),
+                           "closeout": args.closeout,
                            "l2": "256 MB buffer written between timed steps (L2 flush)", "rays_per_path": L},
                 "spp_per_s_1080p": (spp * world) / (ms_per_step / 1e3) * (W * H) / (1920 * 1080),
                 "roofline": roofline, "cpu_baseline": cpu,
@@ -355,6 +386,8 @@ def run_gpu_arm(args):
                         "d2h_bytes_per_step": W * H * 4, "ms_per_step": sum(e_times) / len(e_times)},
                 "gpu_launches": launches, "clocks": clocks, "reference_kernel": refk}
     barrier()
+    if peer is not None:
+        peer.release()
     r.close()
     if world > 1:
         dist.destroy_process_group()
@@ -371,6 +404,10 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--variant", default="auto", choices=["auto", "mega", "wavefront", "pipeline"])
+    ap.add_argument("--closeout", default="nccl", choices=["nccl", "peer", "tiles"],
+                    help="multi-GPU frame close-out: NCCL reduce to rank 0 + resolve; sum + resolve over peer memory in one kernel per "
+                         "rank; or image-tile sharding (each rank renders all samples of its row slabs and resolves them into the root's frame)")
+    ap.add_argument("--tile-rows", type=int, default=16, help="rows per slab of --closeout tiles")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (debug only)")
     ap.add_argument("--cpu-spp", type=int, default=32, help="upper bound of the spp of the bounded CPU-baseline sample (about 10 s of host work)")
     ap.add_argument("--refkernel-spp", type=int, default=64, help="spp of the bounded reference-CUDA-kernel sample")

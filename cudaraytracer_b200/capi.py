@@ -21,6 +21,16 @@ BUILDER_AUTO, BUILDER_HOST_SAH, BUILDER_GPU_LBVH, BUILDER_GPU_PLOC = 0, 1, 2, 3
 VARIANT_AUTO, VARIANT_MEGAKERNEL, VARIANT_WAVEFRONT, VARIANT_PIPELINE = 0, 1, 2, 3
 JITTER_RANDOM, JITTER_CENTER = 0, 1
 FLAG_EXACT_MATH, FLAG_COUNT_TESTS, FLAG_TRUNCATED_GRID = 1, 2, 4
+BUFFER_ACCUM, BUFFER_RGBA = 0, 1
+
+
+def row_tiles(rank: int, world: int, rows_per_tile: int = 16) -> int:
+    """CRT_ROW_TILES of include/crt.h."""
+    if not (0 <= rank < world <= 255 and 1 <= rows_per_tile <= 65535):
+        raise ValueError("row_tiles: need 0 <= rank < world <= 255 and 1 <= rows_per_tile <= 65535")
+    return (rows_per_tile << 16) | (world << 8) | rank
+
+IPC_HANDLE_BYTES = 64
 SCENE_RTIOW, SCENE_TEXTURED, SCENE_GRID_1M, SCENE_STRESS_10K, SCENE_REFERENCE_DEFAULT = 1, 2, 3, 4, 5
 
 
@@ -69,7 +79,7 @@ KEY_W, KEY_A, KEY_S, KEY_D, KEY_SPACE, KEY_LCTRL, KEY_LSHIFT, KEY_C = 1, 2, 4, 8
 class RenderParams(C.Structure):
     _fields_ = [("spp_begin", C.c_uint32), ("spp_count", C.c_uint32), ("spp_stride", C.c_uint32), ("max_depth", C.c_uint32),
                 ("seed", C.c_uint64), ("variant", C.c_int32), ("jitter", C.c_int32), ("flags", C.c_uint32),
-                ("reserved_", C.c_uint32)]
+                ("row_tiles", C.c_uint32)]
 
 
 class Counters(C.Structure):
@@ -112,6 +122,13 @@ SIGNATURES = {
     "crt_resolve": (C.c_int, [_P, _P]),
     "crt_resolve_device": (C.c_int, [_P, _P]),
     "crt_read_accum": (C.c_int, [_P, _P]),
+    "crt_resolve_rows": (C.c_int, [_P, C.c_uint32, _P]),
+    "crt_read_rgba": (C.c_int, [_P, _P]),
+    "crt_rgba_device_ptr": (_P, [_P]),
+    "crt_ipc_export": (C.c_int, [_P, C.c_int32, _P]),
+    "crt_ipc_open": (C.c_int, [_P, _P, C.POINTER(_P)]),
+    "crt_ipc_close": (C.c_int, [_P, _P]),
+    "crt_resolve_peers": (C.c_int, [_P, C.POINTER(_P), C.c_int32, C.c_uint32, C.c_uint32, _P, _P]),
     "crt_primary_ids": (C.c_int, [_P, C.c_int32, C.c_uint64, _P]),
     "crt_get_counters": (C.c_int, [_P, C.POINTER(Counters)]),
     "crt_reset_counters": (C.c_int, [_P]),

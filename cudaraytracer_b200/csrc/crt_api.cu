@@ -90,6 +90,8 @@ struct crt_context
     int wf_thresh = 24;         // extend refills a warp when fewer lanes than this are traversing (CRT_WF_THRESH)
     int wf_batch_iters = 32;    // extend+shade iterations enqueued between two reads of the active count
 
+    std::vector<void*> ipc_open; // peer mappings opened by crt_ipc_open
+
     std::string err;
 };
 
@@ -246,6 +248,7 @@ void crt_context_destroy(crt_context* ctx)
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     free_scene(ctx);
     wavefront_free(ctx->wf);
+    for (void* p : ctx->ipc_open) cudaIpcCloseMemHandle(p);
     cudaFree(ctx->d_accum_own);
     cudaFree(ctx->d_accum_f);
     cudaFree(ctx->d_rgba);
@@ -1070,7 +1073,7 @@ static crt_status render_wavefront(crt_context* ctx, RenderArgs A)
             if (w.h_alive[0] == 0u && w.h_alive[1] == 0u) break; // no live path and no unclaimed (pixel, sample) item
         }
         const uint32_t npx = A.cover_w * A.cover_h;
-        k_wf_add_count<<<(npx + 255) / 256, 256, 0, ctx->stream>>>(A.accum, A.width, A.cover_w, A.cover_h, (long long)spp);
+        k_wf_add_count<<<(npx + 255) / 256, 256, 0, ctx->stream>>>(A.accum, A.width, A.cover_w, A.cover_h, (long long)spp, A.tile_rows, A.tile_rank, A.tile_world);
         ctx->launches++;
         CU(cudaGetLastError());
     }
@@ -1180,11 +1183,27 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
         CU(cudaGetLastError());
         CU(dispatch_pipe(W, ctx->sm_count, smem, ctx->stream, all));
         const uint32_t npx = A.cover_w * A.cover_h;
-        k_wf_add_count<<<(npx + 255) / 256, 256, 0, ctx->stream>>>(A.accum, A.width, A.cover_w, A.cover_h, (long long)spp);
+        k_wf_add_count<<<(npx + 255) / 256, 256, 0, ctx->stream>>>(A.accum, A.width, A.cover_w, A.cover_h, (long long)spp, A.tile_rows, A.tile_rank, A.tile_world);
         CU(cudaGetLastError());
         ctx->launches += 3;
     }
     return CRT_OK;
+}
+
+// Decodes crt_render_params::row_tiles (CRT_ROW_TILES) and returns how many of the `rows` image rows belong to the shard:
+// slabs of tile_rows rows are dealt out round robin, slab t to rank t % world; the last slab may be short.
+static uint32_t crt_row_tiles_local_rows(uint32_t row_tiles, uint32_t rows, uint32_t* tile_rows, uint32_t* tile_rank, uint32_t* tile_world,
+                                         const char** why)
+{
+    const uint32_t rank = row_tiles & 0xffu, world = (row_tiles >> 8) & 0xffu, tr = row_tiles >> 16;
+    *why = nullptr;
+    if (world == 0 || rank >= world || tr == 0) {
+        *why = "row_tiles: need 0 <= rank < world <= 255 and rows_per_tile >= 1 (CRT_ROW_TILES)";
+        return 0;
+    }
+    *tile_rows = tr; *tile_rank = rank; *tile_world = world;
+    const uint32_t full = rows / tr, rem = rows % tr;
+    return (full / world + (rank < full % world ? 1u : 0u)) * tr + (full % world == rank ? rem : 0u);
 }
 
 extern "C" {
@@ -1208,6 +1227,11 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
     A.width = ctx->width; A.height = ctx->height;
     A.cover_w = ctx->width; A.cover_h = ctx->height;
     if (p->flags & CRT_FLAG_TRUNCATED_GRID) { A.cover_w = ctx->width / 16 * 16; A.cover_h = ctx->height / 16 * 16; }
+    if (p->row_tiles) { // this call renders one row-tile shard: cover_h becomes its local row count
+        const char* why = nullptr;
+        A.cover_h = crt_row_tiles_local_rows(p->row_tiles, A.cover_h, &A.tile_rows, &A.tile_rank, &A.tile_world, &why);
+        if (why) return crt_set_error(ctx, CRT_ERR_INVALID, why);
+    }
     A.spp_begin = p->spp_begin; A.spp_count = p->spp_count; A.spp_stride = p->spp_stride ? p->spp_stride : 1;
     A.max_depth = p->max_depth;
     A.seed_lo = (uint32_t)p->seed; A.seed_hi = (uint32_t)(p->seed >> 32);
@@ -1257,7 +1281,26 @@ crt_status crt_resolve_device(crt_context* ctx, void* device_out_rgba8)
     if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_resolve_device: no framebuffer");
     CU(cudaSetDevice(ctx->device));
     uint32_t n = ctx->width * ctx->height;
-    k_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_accum, (uint32_t*)device_out_rgba8, ctx->width, ctx->width, ctx->height);
+    k_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_accum, (uint32_t*)device_out_rgba8, ctx->width, ctx->width, ctx->height, 0u, 0u, 0u);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return CRT_OK;
+}
+
+crt_status crt_resolve_rows(crt_context* ctx, uint32_t row_tiles, void* device_out_rgba8)
+{
+    if (!ctx || !device_out_rgba8) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_rows: NULL argument");
+    if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_resolve_rows: no framebuffer");
+    uint32_t tr = 0, rank = 0, world = 0, rows = ctx->height;
+    if (row_tiles) {
+        const char* why = nullptr;
+        rows = crt_row_tiles_local_rows(row_tiles, ctx->height, &tr, &rank, &world, &why);
+        if (why) return crt_set_error(ctx, CRT_ERR_INVALID, why);
+    }
+    const uint32_t n = ctx->width * rows;
+    if (n == 0) return CRT_OK;
+    CU(cudaSetDevice(ctx->device));
+    k_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_accum, (uint32_t*)device_out_rgba8, ctx->width, ctx->width, rows, tr, rank, world);
     ctx->launches++;
     CU(cudaGetLastError());
     return CRT_OK;
@@ -1270,6 +1313,103 @@ crt_status crt_resolve(crt_context* ctx, uint32_t* out_rgba8)
     if (s != CRT_OK) return s;
     CU(cudaMemcpyAsync(out_rgba8, ctx->d_rgba, (size_t)ctx->width * ctx->height * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
+    return CRT_OK;
+}
+
+crt_status crt_read_rgba(crt_context* ctx, uint32_t* out_rgba8)
+{
+    if (!ctx || !out_rgba8) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_read_rgba: NULL argument");
+    if (!ctx->d_rgba) return crt_set_error(ctx, CRT_ERR_STATE, "crt_read_rgba: no framebuffer");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(out_rgba8, ctx->d_rgba, (size_t)ctx->width * ctx->height * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return CRT_OK;
+}
+
+void* crt_rgba_device_ptr(crt_context* ctx)
+{
+    return ctx ? (void*)ctx->d_rgba : nullptr;
+}
+
+// ---- peer memory: the multi-GPU close-out without a reduce-to-root (kernels.cuh: k_resolve_peers) ----
+crt_status crt_ipc_export(crt_context* ctx, int32_t which, uint8_t out_handle[CRT_IPC_HANDLE_BYTES])
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == CRT_IPC_HANDLE_BYTES, "cudaIpcMemHandle_t is 64 bytes");
+    if (!ctx || !out_handle) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_ipc_export: NULL argument");
+    void* p = nullptr;
+    if (which == CRT_BUFFER_ACCUM) {
+        // only the library's own allocation is the base of a cudaMalloc block, which is what an IPC handle names
+        if (ctx->d_accum != ctx->d_accum_own)
+            return crt_set_error(ctx, CRT_ERR_STATE, "crt_ipc_export: a caller-owned accumulation buffer is set; export that one yourself");
+        p = ctx->d_accum_own;
+    }
+    else if (which == CRT_BUFFER_RGBA) p = ctx->d_rgba;
+    else return crt_set_error(ctx, CRT_ERR_INVALID, "crt_ipc_export: which must be CRT_BUFFER_ACCUM or CRT_BUFFER_RGBA");
+    if (!p) return crt_set_error(ctx, CRT_ERR_STATE, "crt_ipc_export: no framebuffer (crt_framebuffer_resize)");
+    CU(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, p));
+    memcpy(out_handle, &h, CRT_IPC_HANDLE_BYTES);
+    return CRT_OK;
+}
+
+crt_status crt_ipc_open(crt_context* ctx, const uint8_t handle[CRT_IPC_HANDLE_BYTES], void** out_device_ptr)
+{
+    if (!ctx || !handle || !out_device_ptr) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_ipc_open: NULL argument");
+    *out_device_ptr = nullptr;
+    CU(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, CRT_IPC_HANDLE_BYTES);
+    void* p = nullptr;
+    CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess)); // maps the exporter's block; enables peer access if needed
+    ctx->ipc_open.push_back(p);
+    *out_device_ptr = p;
+    return CRT_OK;
+}
+
+crt_status crt_ipc_close(crt_context* ctx, void* device_ptr)
+{
+    if (!ctx || !device_ptr) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_ipc_close: NULL argument");
+    for (size_t i = 0; i < ctx->ipc_open.size(); i++) {
+        if (ctx->ipc_open[i] != device_ptr) continue;
+        CU(cudaSetDevice(ctx->device));
+        CU(cudaStreamSynchronize(ctx->stream));
+        ctx->ipc_open.erase(ctx->ipc_open.begin() + (long)i);
+        CU(cudaIpcCloseMemHandle(device_ptr));
+        return CRT_OK;
+    }
+    return crt_set_error(ctx, CRT_ERR_INVALID, "crt_ipc_close: not a pointer returned by crt_ipc_open on this context");
+}
+
+crt_status crt_resolve_peers(crt_context* ctx, const void* const* peer_accum, int32_t n_peers, uint32_t row_begin, uint32_t row_end,
+                             void* device_out_rgba8, void* device_out_sum)
+{
+    if (!ctx || !peer_accum || !device_out_rgba8) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_peers: NULL argument");
+    if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_resolve_peers: no framebuffer");
+    if (n_peers < 1 || n_peers > CRT_MAX_PEERS) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_peers: 1 <= n_peers <= 16");
+    if (row_begin > row_end || row_end > ctx->height) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_peers: bad row range");
+    PeerAccum P;
+    memset(&P, 0, sizeof(P));
+    P.n = n_peers;
+    for (int g = 0; g < n_peers; g++) {
+        if (!peer_accum[g] || ((uintptr_t)peer_accum[g] & 31u) != 0)
+            return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_peers: every peer buffer must be a 32-byte aligned device pointer");
+        P.p[g] = (const long long*)peer_accum[g];
+    }
+    if (((uintptr_t)device_out_sum & 31u) != 0) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_peers: the sum buffer must be 32-byte aligned");
+    const uint32_t n = (row_end - row_begin) * ctx->width;
+    if (n == 0) return CRT_OK;
+    CU(cudaSetDevice(ctx->device));
+    const dim3 grid((n + 255) / 256);
+    uint32_t* out = (uint32_t*)device_out_rgba8;
+    long long* sum = (long long*)device_out_sum;
+    const uint32_t first = row_begin * ctx->width;
+    if (n_peers <= 2) k_resolve_peers<2><<<grid, 256, 0, ctx->stream>>>(P, out, sum, first, n);
+    else if (n_peers <= 4) k_resolve_peers<4><<<grid, 256, 0, ctx->stream>>>(P, out, sum, first, n);
+    else if (n_peers <= 8) k_resolve_peers<8><<<grid, 256, 0, ctx->stream>>>(P, out, sum, first, n);
+    else k_resolve_peers<CRT_MAX_PEERS><<<grid, 256, 0, ctx->stream>>>(P, out, sum, first, n);
+    ctx->launches++;
+    CU(cudaGetLastError());
     return CRT_OK;
 }
 

@@ -82,7 +82,18 @@ struct RenderArgs
     uint32_t spp_begin, spp_count, spp_stride, max_depth;
     uint32_t seed_lo, seed_hi;
     int jitter;
+    // row-tile sharding (crt_render_params::row_tiles): this launch renders only the rows of slabs tile_rank, tile_rank +
+    // tile_world, ... (slabs of tile_rows rows); cover_h then counts the LOCAL rows. tile_world <= 1: the whole frame.
+    uint32_t tile_rows, tile_rank, tile_world;
 };
+
+// local row of a launch -> image row (identity unless the launch is row-tile sharded)
+__device__ __forceinline__ int crt_image_row(uint32_t tile_rows, uint32_t tile_rank, uint32_t tile_world, int lr)
+{
+    if (tile_world <= 1u) return lr;
+    const uint32_t t = (uint32_t)lr / tile_rows;
+    return (int)((t * tile_world + tile_rank) * tile_rows + ((uint32_t)lr - t * tile_rows));
+}
 
 // ------------------------------------------------------------------------------------------
 // Philox4x32-10 (Salmon et al., SC'11). Stateless: counter = (pixel, sample, bounce, stream), key = seed.

@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(CRT_BLOCK_THREADS) k_render_mega(const __grid_
     int x, y;
     tile_pixel((A.cover_w + 15) / 16, x, y);
     const bool inside = (uint32_t)x < A.cover_w && (uint32_t)y < A.cover_h;
+    y = crt_image_row(A.tile_rows, A.tile_rank, A.tile_world, y);
     const uint32_t pixel = (uint32_t)y * A.width + (uint32_t)x;
 
     long long acc_r = 0, acc_g = 0, acc_b = 0; // this launch's samples; added to the buffer once at the end
@@ -160,14 +161,8 @@ template <bool SMEM_ALL> __global__ void __launch_bounds__(CRT_BLOCK_THREADS) k_
 // Kernel.cu:151-157 + RgbToInt :12-19: col / spp -> 255 * sqrtf -> clamp [0,255] -> truncate -> A<<24|B<<16|G<<8|R.
 // The FP32 sum is the one crt_read_accum reports (fixed point -> binary32, one rounding); IEEE division and square root
 // so the result is bit-identical to the host oracle for the same buffer.
-__global__ void k_resolve(const long long* __restrict__ accum, uint32_t* __restrict__ out, uint32_t width, uint32_t cover_w, uint32_t cover_h)
+__device__ __forceinline__ uint32_t resolve_pack(longlong2 rg, longlong2 bn)
 {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= cover_w * cover_h) return;
-    uint32_t x = i % cover_w, y = i / cover_w;
-    uint32_t pixel = y * width + x;
-    const longlong2* px = reinterpret_cast<const longlong2*>(accum + 4 * (size_t)pixel);
-    longlong2 rg = px[0], bn = px[1];
     float4 a = make_float4(crt_from_fixed(rg.x), crt_from_fixed(rg.y), crt_from_fixed(bn.x), (float)bn.y);
     uint32_t packed = 0xFF000000u;
     if (a.w > 0.f) {
@@ -179,7 +174,68 @@ __global__ void k_resolve(const long long* __restrict__ accum, uint32_t* __restr
         b = (b < 0.0f) ? 0.0f : ((b > 255.0f) ? 255.0f : b);
         packed = (255u << 24) | ((uint32_t)(int)b << 16) | ((uint32_t)(int)g << 8) | (uint32_t)(int)r;
     }
-    out[pixel] = packed;
+    return packed;
+}
+
+// (tile_rows, tile_rank, tile_world): resolve only the rows of a row-tile shard (cover_h = its local row count); out may be a
+// peer mapping of the root's frame.
+__global__ void k_resolve(const long long* __restrict__ accum, uint32_t* __restrict__ out, uint32_t width, uint32_t cover_w, uint32_t cover_h,
+                          uint32_t tile_rows, uint32_t tile_rank, uint32_t tile_world)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cover_w * cover_h) return;
+    uint32_t x = i % cover_w, y = (uint32_t)crt_image_row(tile_rows, tile_rank, tile_world, (int)(i / cover_w));
+    uint32_t pixel = y * width + x;
+    const longlong2* px = reinterpret_cast<const longlong2*>(accum + 4 * (size_t)pixel);
+    out[pixel] = resolve_pack(px[0], px[1]);
+}
+
+// Multi-GPU frame close-out in ONE kernel over peer memory (NVLink): sum of the ranks' accumulation buffers + resolve + store
+// of the packed pixels into the root's frame, for the pixel range this rank owns. Replaces reduce-to-root (every byte of every
+// buffer into ONE GPU) + k_resolve on the root: each GPU pulls 1/G of each peer's buffer (the ingress is spread over all
+// NVLink ports of the switch) and only 4 bytes per pixel travel to the root. P.p[g] are peer mappings (cudaIpcOpenMemHandle)
+// or local pointers; the sum is integer, hence exact and the same bits as the NCCL sum. The n loads of a pixel are
+// independent and issued back to back (the loop is unrolled under a predicate), L2-only (ld.cg): the peers rewrite these
+// addresses every frame and L1 is not coherent with them.
+#define CRT_MAX_PEERS 16
+struct PeerAccum
+{
+    const long long* p[CRT_MAX_PEERS];
+    int n;
+};
+
+// NP = compile-time bound of P.n (2, 4, 8 or 16): the loads live in registers, and a 16-wide array for two peers left one
+// 256-thread block per SM (172 registers) - 2.4 MB in flight on the whole chip, latency-bound at 0.6 TB/s (profiles/r01_m).
+template <int NP>
+__global__ void __launch_bounds__(256) k_resolve_peers(const __grid_constant__ PeerAccum P, uint32_t* __restrict__ out,
+                                                       long long* __restrict__ sum_out, uint32_t first_pixel, uint32_t n_pixels)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pixels) return;
+    const size_t pixel = (size_t)first_pixel + i;
+    longlong2 rg[NP], bn[NP];
+#pragma unroll
+    for (int g = 0; g < NP; g++) {
+        if (g < P.n) {
+            const longlong2* px = reinterpret_cast<const longlong2*>(P.p[g] + 4 * pixel);
+            rg[g] = __ldcg(px);
+            bn[g] = __ldcg(px + 1);
+        }
+    }
+    longlong2 srg = make_longlong2(0, 0), sbn = make_longlong2(0, 0);
+#pragma unroll
+    for (int g = 0; g < NP; g++) {
+        if (g < P.n) {
+            srg.x += rg[g].x; srg.y += rg[g].y;
+            sbn.x += bn[g].x; sbn.y += bn[g].y;
+        }
+    }
+    if (sum_out) {
+        longlong2* so = reinterpret_cast<longlong2*>(sum_out + 4 * pixel);
+        so[0] = srg;
+        so[1] = sbn;
+    }
+    out[pixel] = resolve_pack(srg, sbn);
 }
 
 __global__ void k_accum_to_float(const long long* __restrict__ accum, float4* __restrict__ out, uint32_t n)

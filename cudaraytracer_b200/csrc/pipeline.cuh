@@ -121,8 +121,9 @@ __device__ __forceinline__ int pipe_pop(const PipePool& P, PipeCtl* ctl, int q, 
 __device__ __forceinline__ void pipe_item(const PipeArgs& A, uint32_t w, int& x, int& y, uint32_t& pixel, uint32_t& sample)
 {
     const uint32_t s = w / A.n_pixels_cover, q = w - s * A.n_pixels_cover;
-    y = (int)(q / A.R.cover_w);
-    x = (int)(q - (uint32_t)y * A.R.cover_w);
+    const int lr = (int)(q / A.R.cover_w);
+    x = (int)(q - (uint32_t)lr * A.R.cover_w);
+    y = crt_image_row(A.R.tile_rows, A.R.tile_rank, A.R.tile_world, lr);
     pixel = (uint32_t)y * A.R.width + (uint32_t)x;
     sample = A.R.spp_begin + s * A.R.spp_stride;
 }

@@ -56,8 +56,9 @@ struct WfArgs
 __device__ __forceinline__ void wf_item(const WfArgs& A, uint32_t w, int& x, int& y, uint32_t& pixel, uint32_t& sample)
 {
     const uint32_t s = w / A.n_pixels_cover, q = w - s * A.n_pixels_cover;
-    y = (int)(q / A.R.cover_w);
-    x = (int)(q - (uint32_t)y * A.R.cover_w);
+    const int lr = (int)(q / A.R.cover_w);
+    x = (int)(q - (uint32_t)lr * A.R.cover_w);
+    y = crt_image_row(A.R.tile_rows, A.R.tile_rank, A.R.tile_world, lr);
     pixel = (uint32_t)y * A.R.width + (uint32_t)x;
     sample = A.R.spp_begin + s * A.R.spp_stride;
 }
@@ -286,11 +287,12 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS) k_wf_shade(const __grid_cons
 }
 
 // Adds `spp` to the sample count of every covered pixel (the wavefront's atomics only touch R, G, B).
-__global__ void k_wf_add_count(long long* __restrict__ accum, uint32_t width, uint32_t cover_w, uint32_t cover_h, long long spp)
+__global__ void k_wf_add_count(long long* __restrict__ accum, uint32_t width, uint32_t cover_w, uint32_t cover_h, long long spp,
+                               uint32_t tile_rows, uint32_t tile_rank, uint32_t tile_world)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= cover_w * cover_h) return;
-    uint32_t x = i % cover_w, y = i / cover_w;
+    uint32_t x = i % cover_w, y = (uint32_t)crt_image_row(tile_rows, tile_rank, tile_world, (int)(i / cover_w));
     accum[4 * ((size_t)y * width + x) + 3] += spp;
 }
 

@@ -33,6 +33,14 @@ def tile_shard(rank: int, world: int, height: int, rows_per_tile: int = 16) -> l
     return slabs
 
 
+def row_shard(rank: int, world: int, height: int) -> Tuple[int, int]:
+    """Rows [begin, end) whose reduction + resolve `rank` owns in the peer-memory close-out: contiguous slabs that cover
+    range(height) exactly once, sizes differing by at most one row (a rank may own no row when world > height)."""
+    if world < 1 or not (0 <= rank < world) or height < 0:
+        raise ValueError("row_shard: need 0 <= rank < world and height >= 0")
+    return rank * height // world, (rank + 1) * height // world
+
+
 def reduce_accum(accum, dst: int = 0, group=None):
     """Sum-reduce the int64 accumulation tensors of all ranks onto `dst` (in place). Exact for any rank count and order."""
     import torch
@@ -54,3 +62,68 @@ def render_sharded(renderer, accum, spp_total: int, max_depth: int, rank: int, w
         renderer.render(spp=count, max_depth=max_depth, spp_begin=begin, spp_stride=stride, seed=seed, variant=variant)
     reduce_accum(accum, dst=dst, group=group)
     return count
+
+
+class PeerFrame:
+    """The frame close-out over peer memory (include/crt.h: crt_resolve_peers) instead of reduce-to-root + resolve.
+
+    Every rank keeps accumulating into its renderer's OWN buffer; at construction the ranks exchange CUDA IPC handles of those
+    buffers (and of the root's RGBA8 frame) through torch.distributed and map them. close() then runs, on every rank, one kernel
+    that sums the rows this rank owns over all ranks' buffers (int64: the same bits as the NCCL sum), resolves them and stores
+    the packed pixels into the root's frame over NVLink. Two one-element all-reduces on the launching stream order it after
+    every rank's render and before anybody's next clear; nothing synchronises with the host. torch.distributed stays the
+    plumbing (handle exchange, the two stream-ordered barriers); the data moves inside our kernel."""
+
+    def __init__(self, renderer, rank: int, world: int, dst: int = 0, group=None):
+        import torch
+        import torch.distributed as dist
+        from . import capi
+
+        self.r, self.rank, self.world, self.dst, self.group = renderer, rank, world, dst, group
+        self.rows = row_shard(rank, world, renderer.height)
+        mine = (renderer.ipc_export(capi.BUFFER_ACCUM), renderer.ipc_export(capi.BUFFER_RGBA) if rank == dst else b"")
+        handles = [None] * world
+        if world > 1:
+            dist.all_gather_object(handles, mine, group=group)
+        else:
+            handles[0] = mine
+        self._opened = []
+
+        def mapped(handle, local_ptr, owner):
+            if owner == rank:
+                return local_ptr
+            p = renderer.ipc_open(handle)
+            self._opened.append(p)
+            return p
+
+        self.peer_ptrs = [mapped(handles[g][0], renderer.accum_ptr(), g) for g in range(world)]
+        self.out_ptr = mapped(handles[dst][1], renderer.rgba_ptr(), dst)
+        self._token = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", torch.cuda.current_device()))
+
+    def _fence(self):
+        """Stream-ordered barrier: completes on this rank's stream only after every rank's earlier work on its stream."""
+        import torch.distributed as dist
+        if self.world > 1:
+            dist.all_reduce(self._token, group=self.group)
+
+    def close_frame(self):
+        """After every rank's render of the frame: the root's RGBA8 frame (renderer.read_rgba() on the root) is complete when
+        the root's stream reaches the end of this call."""
+        self._fence()
+        b, e = self.rows
+        self.r.resolve_peers(self.peer_ptrs, b, e, self.out_ptr)
+        self._fence()
+
+    def close_frame_tiles(self, rows_per_tile: int = 16):
+        """Close-out of an image-TILE sharded frame (every rank rendered all samples of capi.row_tiles(rank, world, rows_per_tile)
+        with its own buffer): nothing to sum - each rank resolves its rows straight into the root's frame (4 bytes per pixel
+        over NVLink) between two fences: after the root's reads of the previous frame, and before the root reads this one."""
+        from . import capi
+        self._fence()  # the root's reads of the previous frame (on its stream) come before anybody's stores into it
+        self.r.resolve_rows(capi.row_tiles(self.rank, self.world, rows_per_tile), self.out_ptr)
+        self._fence()
+
+    def release(self):
+        for p in self._opened:
+            self.r.ipc_close(p)
+        self._opened = []

@@ -195,8 +195,9 @@ class Renderer:
         self._ck(self.lib.crt_set_accum_device_buffer(self.ctx, C.c_void_p(ptr)))
 
     def render(self, spp: int, max_depth: int, spp_begin: int = 0, spp_stride: int = 1, seed: int = 1984,
-               variant: int = capi.VARIANT_AUTO, jitter: int = capi.JITTER_RANDOM, flags: int = 0):
-        p = capi.RenderParams(spp_begin, spp, spp_stride, max_depth, seed, variant, jitter, flags, 0)
+               variant: int = capi.VARIANT_AUTO, jitter: int = capi.JITTER_RANDOM, flags: int = 0, row_tiles: int = 0):
+        """row_tiles = capi.row_tiles(rank, world, rows_per_tile): only that row-tile shard of the frame (0 = every row)."""
+        p = capi.RenderParams(spp_begin, spp, spp_stride, max_depth, seed, variant, jitter, flags, row_tiles)
         self._ck(self.lib.crt_render(self.ctx, C.byref(p)))
 
     def synchronize(self):
@@ -216,6 +217,47 @@ class Renderer:
 
     def resolve_device(self, ptr: int):
         self._ck(self.lib.crt_resolve_device(self.ctx, C.c_void_p(ptr)))
+
+    def resolve_rows(self, row_tiles: int, out_rgba_ptr: int):
+        """Resolve the rows of a row-tile shard from this context's buffer into the frame at out_rgba_ptr (may be a peer mapping)."""
+        self._ck(self.lib.crt_resolve_rows(self.ctx, row_tiles, C.c_void_p(out_rgba_ptr)))
+
+    def read_rgba(self, out: np.ndarray | None = None) -> np.ndarray:
+        """The context's own RGBA8 frame as it stands (written by resolve() or by the peers' resolve_peers)."""
+        if out is None:
+            out = np.empty((self.height, self.width), dtype=np.uint32)
+        assert out.dtype == np.uint32 and out.size == self.width * self.height and out.flags.c_contiguous
+        self._ck(self.lib.crt_read_rgba(self.ctx, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def accum_ptr(self) -> int:
+        return int(self.lib.crt_accum_device_ptr(self.ctx) or 0)
+
+    def rgba_ptr(self) -> int:
+        return int(self.lib.crt_rgba_device_ptr(self.ctx) or 0)
+
+    def ipc_export(self, which: int) -> bytes:
+        """64-byte CUDA IPC handle of the context's own accumulation buffer (capi.BUFFER_ACCUM) or RGBA8 frame (BUFFER_RGBA)."""
+        buf = (C.c_uint8 * capi.IPC_HANDLE_BYTES)()
+        self._ck(self.lib.crt_ipc_export(self.ctx, which, buf))
+        return bytes(buf)
+
+    def ipc_open(self, handle: bytes) -> int:
+        """Map a buffer another PROCESS exported; returns the device pointer valid on this context's device."""
+        assert len(handle) == capi.IPC_HANDLE_BYTES
+        buf = (C.c_uint8 * capi.IPC_HANDLE_BYTES).from_buffer_copy(handle)
+        out = C.c_void_p()
+        self._ck(self.lib.crt_ipc_open(self.ctx, buf, C.byref(out)))
+        return int(out.value)
+
+    def ipc_close(self, ptr: int):
+        self._ck(self.lib.crt_ipc_close(self.ctx, C.c_void_p(ptr)))
+
+    def resolve_peers(self, peer_ptrs, row_begin: int, row_end: int, out_rgba_ptr: int, out_sum_ptr: int = 0):
+        """Sum the accumulation buffers `peer_ptrs` over rows [row_begin, row_end), resolve, store into the frame at out_rgba_ptr."""
+        arr = (C.c_void_p * len(peer_ptrs))(*[C.c_void_p(int(p)) for p in peer_ptrs])
+        self._ck(self.lib.crt_resolve_peers(self.ctx, arr, len(peer_ptrs), row_begin, row_end, C.c_void_p(out_rgba_ptr),
+                                            C.c_void_p(out_sum_ptr) if out_sum_ptr else None))
 
     def read_accum(self) -> np.ndarray:
         out = np.empty((self.height, self.width, 4), dtype=np.float32)

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CRT_ABI_VERSION 3
+#define CRT_ABI_VERSION 4
 
 typedef enum crt_status {
     CRT_OK = 0,
@@ -114,8 +114,11 @@ typedef struct crt_render_params {
     int32_t variant;      /* CRT_VARIANT_* */
     int32_t jitter;       /* CRT_JITTER_* */
     uint32_t flags;       /* CRT_FLAG_* */
-    uint32_t reserved_;
+    uint32_t row_tiles;   /* 0 = every row. CRT_ROW_TILES(rank, world, rows_per_tile): render only the rows of the slabs (of
+                           * rows_per_tile rows) number rank, rank + world, ... - image-tile sharding over GPUs: every pixel lives
+                           * on one GPU, so the close-out needs no reduction (crt_resolve_rows into the root's frame) */
 } crt_render_params;
+#define CRT_ROW_TILES(rank, world, rows_per_tile) (((uint32_t)(rows_per_tile) << 16) | ((uint32_t)(world) << 8) | (uint32_t)(rank))
 
 typedef struct crt_counters {
     uint64_t paths;        /* camera paths started */
@@ -202,6 +205,34 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* params);
 crt_status crt_resolve(crt_context* ctx, uint32_t* out_rgba8);
 crt_status crt_resolve_device(crt_context* ctx, void* device_out_rgba8); /* async */
 crt_status crt_read_accum(crt_context* ctx, float* out_float4);          /* width*height*4 floats, synchronises */
+/* Resolve only the rows of a row-tile shard (row_tiles as in crt_render_params; 0 = all rows) from this context's accumulation
+ * buffer into the frame at device_out_rgba8 (pixel 0 of a full frame; may be a peer mapping of another GPU's frame). Async. */
+crt_status crt_resolve_rows(crt_context* ctx, uint32_t row_tiles, void* device_out_rgba8);
+/* Copy the context's own RGBA8 frame (what crt_resolve or a peer's crt_resolve_peers wrote into it) to HOST memory. Synchronises. */
+crt_status crt_read_rgba(crt_context* ctx, uint32_t* out_rgba8);
+void*      crt_rgba_device_ptr(crt_context* ctx);
+
+/* ---- multi-GPU close-out over peer memory (NVLink; one process per GPU). The reference has no multi-GPU path; this replaces
+ * "reduce every rank's accumulation buffer to the root, resolve there" by ONE kernel per rank: for the rows a rank owns it
+ * reads the buffers of all ranks through peer mappings, adds them (int64: exact, the same bits as the NCCL sum), resolves
+ * (Kernel.cu:12-19,151-157) and stores the packed pixels straight into the root's frame. Per pixel 32 bytes per peer travel to
+ * the owner of the row and 4 bytes to the root, instead of 32 bytes per peer into the root.
+ *   crt_ipc_export   a 64-byte CUDA IPC handle of the context's OWN accumulation buffer or RGBA8 frame (send it to the other
+ *                    processes by any means);
+ *   crt_ipc_open     map a buffer exported by ANOTHER process on this context's device; crt_ipc_close / context destruction unmaps;
+ *   crt_resolve_peers  rows [row_begin, row_end): peer_accum[g] are device pointers valid on this device (peer mappings or
+ *                    local buffers, at most 16), device_out_rgba8 points at pixel 0 of the destination frame (may be a peer
+ *                    mapping), device_out_sum (may be NULL) receives the summed rows in the accumulation layout. Asynchronous on
+ *                    the context stream. The CALLER orders it after every rank's render and before the next clear (a
+ *                    stream-ordered collective on the same stream, e.g. a one-element all-reduce, is enough). ---- */
+#define CRT_IPC_HANDLE_BYTES 64
+enum { CRT_BUFFER_ACCUM = 0, CRT_BUFFER_RGBA = 1 };
+crt_status crt_ipc_export(crt_context* ctx, int32_t which, uint8_t out_handle[CRT_IPC_HANDLE_BYTES]);
+crt_status crt_ipc_open(crt_context* ctx, const uint8_t handle[CRT_IPC_HANDLE_BYTES], void** out_device_ptr);
+crt_status crt_ipc_close(crt_context* ctx, void* device_ptr);
+crt_status crt_resolve_peers(crt_context* ctx, const void* const* peer_accum, int32_t n_peers, uint32_t row_begin, uint32_t row_end,
+                             void* device_out_rgba8, void* device_out_sum);
+
 /* Closest-hit hittable index (index into the uploaded list, -1 = miss) of one primary ray per pixel.
  * Always exact math; jitter = CRT_JITTER_*. out is HOST memory, width*height int32. */
 crt_status crt_primary_ids(crt_context* ctx, int32_t jitter, uint64_t seed, int32_t* out_ids);

@@ -33,7 +33,7 @@ def test_binding_table_covers_the_header():
     declared = set(_declared("crt.h"))
     assert declared <= set(capi.SIGNATURES), declared - set(capi.SIGNATURES)
     lib = capi.load()
-    assert lib.crt_abi_version() == 3
+    assert lib.crt_abi_version() == 4
 
 
 def test_struct_layouts():

@@ -39,6 +39,108 @@ def test_sharded_sum_is_bit_identical(world):
     ref_r.close()
 
 
+@pytest.mark.parametrize("world", [1, 2, 5, 16])
+def test_resolve_peers_equals_sum_then_resolve(world):
+    """crt_resolve_peers (sum over the ranks' buffers + resolve, by row slabs) on ONE GPU, the G buffers being plain local
+    pointers: the frame and the summed buffer must be bit-identical to 'add the buffers, then crt_resolve'."""
+    import torch
+    from cudaraytracer_b200.multigpu import row_shard
+    W, H, spp, depth = 200, 37, 9, 50
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    cam = s.default_camera(W, H)
+    ranks = []
+    for rank in range(world):
+        r = Renderer(0)
+        r.upload(s); r.set_camera(cam); r.resize(W, H)
+        b, st, c = sample_shard(rank, world, spp)
+        if c:
+            r.render(spp=c, max_depth=depth, spp_begin=b, spp_stride=st)
+        r.synchronize()
+        ranks.append(r)
+    # the reference result: one context renders all samples, resolves
+    ref_r = Renderer(0)
+    ref_r.upload(s); ref_r.set_camera(cam); ref_r.resize(W, H)
+    ref = torch.zeros((H, W, 4), dtype=torch.int64, device="cuda")
+    ref_r.set_accum_device_buffer(ref.data_ptr())
+    ref_r.render(spp=spp, max_depth=depth)
+    want = ref_r.resolve()
+    # every 'rank' closes its own row slab into rank 0's frame
+    root = ranks[0]
+    ptrs = [r.accum_ptr() for r in ranks]
+    total = torch.full((H, W, 4), -1, dtype=torch.int64, device="cuda")
+    covered = 0
+    for rank, r in enumerate(ranks):
+        b, e = row_shard(rank, world, H)
+        covered += e - b
+        r.resolve_peers(ptrs, b, e, root.rgba_ptr(), total.data_ptr())
+        r.synchronize()
+    assert covered == H
+    got = root.read_rgba()
+    assert np.array_equal(got, want)
+    assert torch.equal(total, ref)
+    # argument checks
+    with pytest.raises(Exception):
+        root.resolve_peers(ptrs, 3, H + 1, root.rgba_ptr())
+    with pytest.raises(Exception):
+        root.resolve_peers(ptrs * 17, 0, H, root.rgba_ptr())
+    with pytest.raises(Exception):
+        root.resolve_peers([ptrs[0] + 8], 0, H, root.rgba_ptr())
+    for r in ranks:
+        r.close()
+    ref_r.close()
+
+
+@pytest.mark.parametrize("world,rows_per_tile,variant", [(1, 16, capi.VARIANT_PIPELINE), (2, 16, capi.VARIANT_PIPELINE),
+                                                        (3, 5, capi.VARIANT_MEGAKERNEL), (8, 16, capi.VARIANT_WAVEFRONT),
+                                                        (7, 1, capi.VARIANT_PIPELINE), (4, 64, capi.VARIANT_AUTO)])
+def test_row_tile_shards_tile_the_full_render(world, rows_per_tile, variant):
+    """Image-tile sharding (crt_render_params::row_tiles): each 'rank' renders ALL samples of its row slabs; the shards touch
+    disjoint rows (the others stay zero), agree with multigpu.tile_shard, and together are bit-identical to the full render -
+    buffers and resolved frame (crt_resolve_rows of every rank into one frame)."""
+    import torch
+    from cudaraytracer_b200.multigpu import tile_shard
+    W, H, spp, depth = 150, 83, 5, 50
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    cam = s.default_camera(W, H)
+    ref_r = Renderer(0)
+    ref_r.upload(s); ref_r.set_camera(cam); ref_r.resize(W, H)
+    ref = torch.zeros((H, W, 4), dtype=torch.int64, device="cuda")
+    ref_r.set_accum_device_buffer(ref.data_ptr())
+    ref_r.render(spp=spp, max_depth=depth)
+    want = ref_r.resolve()
+    frame = torch.zeros((H, W), dtype=torch.int32, device="cuda")
+    r = Renderer(0)
+    r.upload(s); r.set_camera(cam); r.resize(W, H)
+    acc = torch.zeros((H, W, 4), dtype=torch.int64, device="cuda")
+    r.set_accum_device_buffer(acc.data_ptr())
+    total = torch.zeros_like(ref)
+    paths = 0
+    for rank in range(world):
+        acc.zero_()
+        r.reset_counters()
+        rt = capi.row_tiles(rank, world, rows_per_tile)
+        r.render(spp=spp, max_depth=depth, variant=variant, row_tiles=rt)
+        r.resolve_rows(rt, frame.data_ptr())
+        r.synchronize()
+        mine = np.zeros(H, dtype=bool)
+        for y0, y1 in tile_shard(rank, world, H, rows_per_tile):
+            mine[y0:y1] = True
+        touched = (acc[..., 3] != 0).any(dim=1).cpu().numpy()
+        assert np.array_equal(touched, mine)
+        assert torch.equal(acc[torch.from_numpy(mine).cuda()], ref[torch.from_numpy(mine).cuda()])
+        paths += r.counters().paths
+        total += acc
+    assert torch.equal(total, ref)
+    assert paths == W * H * spp
+    assert np.array_equal(frame.cpu().numpy().view(np.uint32), want)
+    with pytest.raises(Exception):
+        r.render(spp=1, max_depth=depth, row_tiles=(16 << 16) | (2 << 8) | 2)  # rank == world
+    with pytest.raises(Exception):
+        r.render(spp=1, max_depth=depth, row_tiles=(0 << 16) | (2 << 8) | 1)  # zero rows per tile
+    r.close()
+    ref_r.close()
+
+
 def test_c_host_example_renders_a_ppm(tmp_path):
     """examples/headless_render.c (plain C over the C ABI): progressive passes, resolve, PPM on disk."""
     import os

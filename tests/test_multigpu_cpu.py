@@ -10,7 +10,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from cudaraytracer_b200.multigpu import reduce_accum, sample_shard, tile_shard
+from cudaraytracer_b200.multigpu import reduce_accum, row_shard, sample_shard, tile_shard
 
 
 def test_sample_shards_partition_the_sample_range():
@@ -37,6 +37,20 @@ def test_tile_shards_cover_every_row_once():
                 for y0, y1 in tile_shard(rank, world, H):
                     rows += list(range(y0, y1))
             assert sorted(rows) == list(range(H))
+
+
+def test_row_shards_are_contiguous_slabs_that_cover_the_frame():
+    for world in (1, 2, 3, 8, 16):
+        for H in (0, 1, 7, 16, 1080, 2160, 4320):
+            prev, sizes = 0, []
+            for rank in range(world):
+                b, e = row_shard(rank, world, H)
+                assert b == prev and b <= e
+                prev = e
+                sizes.append(e - b)
+            assert prev == H and max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        row_shard(3, 3, 10)
 
 
 def _fixed_sample(pixel, sample):
