@@ -409,7 +409,7 @@ def main():
                          "rank; or image-tile sharding (each rank renders all samples of its row slabs and resolves them into the root's frame)")
     ap.add_argument("--tile-rows", type=int, default=16, help="rows per slab of --closeout tiles")
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (debug only)")
-    ap.add_argument("--cpu-spp", type=int, default=32, help="upper bound of the spp of the bounded CPU-baseline sample (about 10 s of host work)")
+    ap.add_argument("--cpu-spp", type=int, default=128, help="upper bound of the spp of the bounded CPU-baseline sample (sized to about 10 s of host work)")
     ap.add_argument("--refkernel-spp", type=int, default=64, help="spp of the bounded reference-CUDA-kernel sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-refkernel", action="store_true")

@@ -123,6 +123,7 @@ SIGNATURES = {
     "crt_resolve_device": (C.c_int, [_P, _P]),
     "crt_read_accum": (C.c_int, [_P, _P]),
     "crt_resolve_rows": (C.c_int, [_P, C.c_uint32, _P]),
+    "crt_row_tiles_rows": (C.c_uint32, [C.c_uint32, C.c_uint32]),
     "crt_read_rgba": (C.c_int, [_P, _P]),
     "crt_rgba_device_ptr": (_P, [_P]),
     "crt_ipc_export": (C.c_int, [_P, C.c_int32, _P]),

@@ -1208,6 +1208,15 @@ static uint32_t crt_row_tiles_local_rows(uint32_t row_tiles, uint32_t rows, uint
 
 extern "C" {
 
+uint32_t crt_row_tiles_rows(uint32_t row_tiles, uint32_t height)
+{
+    if (!row_tiles) return height;
+    uint32_t tr, rank, world;
+    const char* why = nullptr;
+    const uint32_t rows = crt_row_tiles_local_rows(row_tiles, height, &tr, &rank, &world, &why);
+    return why ? 0u : rows;
+}
+
 crt_status crt_render(crt_context* ctx, const crt_render_params* p)
 {
     if (!ctx || !p) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_render: NULL argument");

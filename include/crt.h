@@ -119,6 +119,8 @@ typedef struct crt_render_params {
                            * on one GPU, so the close-out needs no reduction (crt_resolve_rows into the root's frame) */
 } crt_render_params;
 #define CRT_ROW_TILES(rank, world, rows_per_tile) (((uint32_t)(rows_per_tile) << 16) | ((uint32_t)(world) << 8) | (uint32_t)(rank))
+/* Host-only: how many of the `height` image rows the shard `row_tiles` holds (0 for a malformed value; height for 0). */
+uint32_t crt_row_tiles_rows(uint32_t row_tiles, uint32_t height);
 
 typedef struct crt_counters {
     uint64_t paths;        /* camera paths started */
@@ -224,7 +226,9 @@ void*      crt_rgba_device_ptr(crt_context* ctx);
  *                    local buffers, at most 16), device_out_rgba8 points at pixel 0 of the destination frame (may be a peer
  *                    mapping), device_out_sum (may be NULL) receives the summed rows in the accumulation layout. Asynchronous on
  *                    the context stream. The CALLER orders it after every rank's render and before the next clear (a
- *                    stream-ordered collective on the same stream, e.g. a one-element all-reduce, is enough). ---- */
+ *                    stream-ordered collective on the same stream, e.g. a one-element all-reduce, is enough).
+ * crt_framebuffer_resize with a new size frees the exported buffers: peers must close their mappings first and the handles must
+ * be exchanged again afterwards. ---- */
 #define CRT_IPC_HANDLE_BYTES 64
 enum { CRT_BUFFER_ACCUM = 0, CRT_BUFFER_RGBA = 1 };
 crt_status crt_ipc_export(crt_context* ctx, int32_t which, uint8_t out_handle[CRT_IPC_HANDLE_BYTES]);

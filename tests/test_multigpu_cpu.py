@@ -39,6 +39,27 @@ def test_tile_shards_cover_every_row_once():
             assert sorted(rows) == list(range(H))
 
 
+def test_row_tiles_of_the_c_abi_agree_with_tile_shard():
+    """crt_render_params::row_tiles (what the kernels map rows with) and multigpu.tile_shard describe the same slabs."""
+    from cudaraytracer_b200 import capi
+    lib = capi.load()
+    for world in (1, 2, 3, 8, 255):
+        for rpt in (1, 5, 16, 64):
+            for H in (1, 15, 16, 17, 83, 1080, 4320):
+                counts = []
+                for rank in range(world):
+                    want = sum(y1 - y0 for y0, y1 in tile_shard(rank, world, H, rpt))
+                    got = lib.crt_row_tiles_rows(capi.row_tiles(rank, world, rpt), H)
+                    assert got == want, (world, rpt, H, rank)
+                    counts.append(got)
+                assert sum(counts) == H
+    assert lib.crt_row_tiles_rows(0, 123) == 123
+    assert lib.crt_row_tiles_rows((16 << 16) | (2 << 8) | 2, 100) == 0  # rank == world
+    assert lib.crt_row_tiles_rows((0 << 16) | (2 << 8) | 1, 100) == 0   # zero rows per slab
+    with pytest.raises(ValueError):
+        capi.row_tiles(3, 3)
+
+
 def test_row_shards_are_contiguous_slabs_that_cover_the_frame():
     for world in (1, 2, 3, 8, 16):
         for H in (0, 1, 7, 16, 1080, 2160, 4320):
