@@ -82,7 +82,8 @@ struct crt_context
     DevCounters* d_counters = nullptr; // CRT_COUNTER_SHARDS entries
     WfShard* d_shards = nullptr;       // work counters of the pipelined megakernel
     int pipe_thresh = 0, pipe_rounds = 0, // 0 = chosen per scene (render_pipeline)
-         pipe_slots = 0, pipe_check = 4, pipe_ext_low = 256; // CRT_PIPE_THRESH / _ROUNDS / _SLOTS / _CHECK
+         pipe_slots = 0, pipe_check = 4, pipe_ext_low = 256, // CRT_PIPE_THRESH / _ROUNDS / _SLOTS / _CHECK
+         pipe_sched = 0; // CRT_PIPE_SCHED: 1 = the experimental round schedule of pipeline.cuh
     uint64_t launches = 0;
 
     WavefrontState wf;
@@ -219,6 +220,7 @@ crt_status crt_context_create(int device, crt_context** out)
     if ((env = getenv("CRT_PIPE_SLOTS")) && atoi(env) > 0) ctx->pipe_slots = atoi(env);
     if ((env = getenv("CRT_PIPE_CHECK")) && atoi(env) > 0) ctx->pipe_check = atoi(env);
     if ((env = getenv("CRT_PIPE_EXT_LOW")) && atoi(env) >= 0) ctx->pipe_ext_low = atoi(env);
+    if ((env = getenv("CRT_PIPE_SCHED")) && atoi(env) >= 0) ctx->pipe_sched = atoi(env);
     if ((env = getenv("CRT_PIPE_PREFIX_KB")) && atoi(env) >= 0) ctx->pipe_prefix_bytes = 1024L * atoi(env);
     if ((env = getenv("CRT_BVH_BUILDER"))) {
         if (!strcmp(env, "host")) ctx->bvh_builder = CRT_BUILDER_HOST_SAH;
@@ -1093,24 +1095,28 @@ __global__ void k_pipe_init(WfShard* shards, uint32_t work_total)
     shards[i].end = b + per + (i < extra ? 1u : 0u);
 }
 
-template <int NSLOTS, bool ALL> static cudaError_t launch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st)
+template <int NSLOTS, bool ALL, int SCHED = 0> static cudaError_t launch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st)
 {
     static size_t configured[CRT_MAX_DEVICES] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     size_t& configured_smem = configured[dev & (CRT_MAX_DEVICES - 1)];
     if (smem > configured_smem) {
-        cudaError_t e = cudaFuncSetAttribute(k_render_pipe<NSLOTS, ALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(k_render_pipe<NSLOTS, ALL, SCHED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured_smem = smem;
     }
-    k_render_pipe<NSLOTS, ALL><<<grid, PIPE_THREADS, smem, st>>>(W);
+    k_render_pipe<NSLOTS, ALL, SCHED><<<grid, PIPE_THREADS, smem, st>>>(W);
     return cudaGetLastError();
 }
 
 // the two pool sizes the planner picks have kernels with the size compiled in; anything else (CRT_PIPE_SLOTS) runs the generic one
-static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st, bool all)
+static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st, bool all, int sched)
 {
+    if (sched == 1) { // experimental round schedule (pipeline.cuh): only with a compiled-in pool size
+        if (W.n_slots == 1024) return all ? launch_pipe<1024, true, 1>(W, grid, smem, st) : launch_pipe<1024, false, 1>(W, grid, smem, st);
+        if (W.n_slots == 2048) return all ? launch_pipe<2048, true, 1>(W, grid, smem, st) : launch_pipe<2048, false, 1>(W, grid, smem, st);
+    }
 #define CRT_PIPE_CASE(N) case N: return all ? launch_pipe<N, true>(W, grid, smem, st) : launch_pipe<N, false>(W, grid, smem, st)
     switch (W.n_slots) {
         CRT_PIPE_CASE(1024);
@@ -1181,7 +1187,7 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
         W.R.spp_stride = stride;
         k_pipe_init<<<1, WF_SHARDS, 0, ctx->stream>>>(ctx->d_shards, (uint32_t)(P * spp));
         CU(cudaGetLastError());
-        CU(dispatch_pipe(W, ctx->sm_count, smem, ctx->stream, all));
+        CU(dispatch_pipe(W, ctx->sm_count, smem, ctx->stream, all, ctx->pipe_sched));
         const uint32_t npx = A.cover_w * A.cover_h;
         k_wf_add_count<<<(npx + 255) / 256, 256, 0, ctx->stream>>>(A.accum, A.width, A.cover_w, A.cover_h, (long long)spp, A.tile_rows, A.tile_rank, A.tile_world);
         CU(cudaGetLastError());

@@ -229,7 +229,11 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
 // NSLOTS > 0: the pool size is a compile-time constant. The pool sits at the START of dynamic shared memory, so every pool
 // and ring address is `constant + index`: with a run-time N behind the scene tables the compiler re-derived those addresses from
 // kernel parameters at each use (3.7 % of the executed instructions, profiles/r01_j). NSLOTS == 0 takes N from the arguments.
-template <int NSLOTS, bool SMEM_ALL>
+// SCHED: visits of a traversal round. 0 = node, leaf, node, leaf (what runs by default). 1 = node, node, leaf: a lane that
+// reaches a leaf in the first node visit sits the second one out, and ONE leaf visit serves the leaves of both - fewer, fuller
+// leaf visits (they run at 10.7 of 32 lanes, profiles/r01_l_pipe_c2_by_line.txt). Experimental (CRT_PIPE_SCHED=1), not yet
+// measured; every lane walks its own tree in the same order either way, so the image is the same.
+template <int NSLOTS, bool SMEM_ALL, int SCHED = 0>
 __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_constant__ PipeArgs A)
 {
     extern __shared__ float4 smem[];
@@ -326,7 +330,9 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         int rounds_left = A.max_rounds;
         while (true) { // two node visits per vote
             node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
-            if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
+            if (SCHED == 0) {
+                if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
+            }
             node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
             if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
             act = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);

@@ -7,6 +7,8 @@ Bars (BASELINE.json north_star / SURVEY.md §8d):
     measures the oracle-vs-oracle noise floor with two seed bases and requires
     RMSE(new, oracle) <= 1.25 x RMSE(oracle, oracle'), plus an unbiasedness check on block means.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -284,6 +286,25 @@ def test_variants_bit_identical_to_megakernel(renderer, name, kind, hint, W, H, 
     assert cw.paths == cm.paths == W * H * 6 and cw.rays == cm.rays
     assert np.array_equal(mega.view(np.uint32), wave.view(np.uint32)), \
         f"{(mega != wave).any(axis=-1).sum()} of {W * H} pixels differ between the variants"
+
+
+@pytest.mark.skipif(not os.environ.get("CRT_TEST_EXPERIMENTAL"), reason="experimental kernel build (CRT_PIPE_SCHED=1), not the default "
+                    "path: run with CRT_TEST_EXPERIMENTAL=1 when measuring it")
+@pytest.mark.parametrize("kind,hint", [(capi.SCENE_RTIOW, 0), (capi.SCENE_GRID_1M, 60)], ids=["rtiow", "grid3601"])
+def test_experimental_round_schedule_is_bit_identical(monkeypatch, kind, hint):
+    """CRT_PIPE_SCHED=1 (node, node, leaf rounds; pipeline.cuh) changes only the interleaving of the lanes."""
+    s = Scene.generate(kind, 1984, hint)
+    W, H = 161, 91
+    cam = s.default_camera(W, H)
+    out = []
+    for sched in ("0", "1"):
+        monkeypatch.setenv("CRT_PIPE_SCHED", sched)
+        r = Renderer(0)
+        _setup(r, s, cam, W, H)
+        r.render(spp=5, max_depth=50, variant=capi.VARIANT_PIPELINE)
+        out.append(r.read_accum().view(np.uint32).copy())
+        r.close()
+    assert np.array_equal(out[0], out[1])
 
 
 @pytest.mark.parametrize("variant", [capi.VARIANT_WAVEFRONT, capi.VARIANT_PIPELINE], ids=["wavefront", "pipeline"])
