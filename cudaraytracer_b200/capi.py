@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("CRT_LIB_PATH") or os.path.join(_HERE, "libcrt.so")  # override: A/B experiments only
 
 # enums of include/crt.h
-CRT_OK = 0
+CRT_OK, CRT_ERR_INVALID, CRT_ERR_CUDA, CRT_ERR_NOMEM, CRT_ERR_UNSUPPORTED, CRT_ERR_STATE = 0, 1, 2, 3, 4, 5
 SPHERE, XYRECT, XZRECT, YZRECT = 0, 1, 2, 3
 LAMBERTIAN, METAL, DIELECTRIC, DIFFUSELIGHT = 0, 1, 2, 3
 CONSTANT, CHECKER, IMAGE = 0, 1, 2

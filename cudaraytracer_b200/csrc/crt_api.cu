@@ -642,6 +642,9 @@ crt_status crt_scene_edit_hittable(crt_context* ctx, uint64_t index, const crt_h
     if (h->type < CRT_SPHERE || h->type > CRT_YZRECT) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_edit_hittable: unknown type");
     if (h->material < 0 || (uint64_t)h->material >= ctx->host.materials.size())
         return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_edit_hittable: material index out of range");
+    if (h->active && (!std::isfinite(h->cx) || !std::isfinite(h->cy) || !std::isfinite(h->cz) || !std::isfinite(h->a) ||
+                      (h->type != CRT_SPHERE && !std::isfinite(h->b))))
+        return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_edit_hittable: non-finite coordinate or size (deactivate the hittable instead)");
     const crt_hittable old = ctx->host.hittables[index];
     // switching a primitive on/off or changing its kind changes the tree; everything else is a refit
     if ((old.active != 0) != (h->active != 0) || (h->active && old.type != h->type)) ctx->need_rebuild = true;

@@ -335,6 +335,12 @@ static bool check_hittable(const crt_scene_desc* sd, uint64_t i, std::string* er
         *err = "scene: hittable " + std::to_string(i) + " has material index out of range";
         return false;
     }
+    // A NaN or infinite coordinate is never hit by the reference (every comparison of Sphere::Hit fails), but inside a BVH it
+    // poisons the boxes of all its ancestors: refuse it instead of rendering a silently broken tree.
+    if (!std::isfinite(h.cx) || !std::isfinite(h.cy) || !std::isfinite(h.cz) || !std::isfinite(h.a) || (h.type != CRT_SPHERE && !std::isfinite(h.b))) {
+        *err = "scene: hittable " + std::to_string(i) + " has a non-finite coordinate or size (deactivate it instead)";
+        return false;
+    }
     const crt_material& m = sd->materials[h.material];
     if (m.type < CRT_LAMBERTIAN || m.type > CRT_DIFFUSELIGHT) {
         *err = "scene: material " + std::to_string(h.material) + " has unknown type";

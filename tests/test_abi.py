@@ -109,3 +109,56 @@ def test_host_bvh_build_is_deterministic_and_handles_degenerate_input():
     for n in (0, 1, 2, 3):
         s = Scene.from_arrays(same[:n], mat, tex)
         assert capi.load().crt_bvh_build_check(C.byref(s.desc), C.byref(st)) == capi.CRT_OK and st.n_prims == n
+
+
+def test_host_bvh_build_survives_random_and_rejects_malformed_scenes():
+    """Randomised scenes (duplicates, collinear centres, 1e-30 and 1e6 sizes, rects, inactive entries) keep the invariants;
+    malformed ones (bad indices or types, NaN / infinite geometry) are refused with CRT_ERR_INVALID, never crash or build a
+    poisoned tree; an inactive hittable may hold anything."""
+    import random
+    from cudaraytracer_b200 import Scene
+    lib = capi.load()
+    tex = [dict(type=capi.CONSTANT, color=(0.5, 0.5, 0.5))]
+    mat = [dict(type=capi.LAMBERTIAN, texture=0), dict(type=capi.METAL, texture=0), dict(type=capi.DIELECTRIC, texture=0)]
+    rng = random.Random(7)
+
+    def val(scale):
+        k = rng.random()
+        return 0.0 if k < 0.05 else scale * 1e-30 if k < 0.10 else scale * 1e6 if k < 0.15 else rng.uniform(-scale, scale)
+
+    for it in range(120):
+        n = rng.choice([0, 1, 2, 3, 5, 8, 9, 17, 33, 64, 257])
+        mode = rng.choice(["uniform", "line", "dup", "mixed", "huge"])
+        hs = []
+        for i in range(n):
+            t = rng.choice([capi.SPHERE] * 4 + [capi.XYRECT, capi.XZRECT, capi.YZRECT])
+            c = {"line": (float(i), 0.0, 0.0), "dup": (float(i % 3), 1.0, 2.0), "huge": (val(1e5), val(1e5), val(1e5))}.get(
+                mode, (rng.uniform(-10, 10), rng.uniform(-10, 10), rng.uniform(-10, 10)))
+            a = abs(val(2.0)) if mode in ("mixed", "huge") else rng.uniform(0.01, 1.0)
+            hs.append(dict(type=t, cx=c[0], cy=c[1], cz=c[2], a=-a if rng.random() < 0.1 else a, b=abs(val(3.0)),
+                           material=rng.randrange(3), active=int(rng.random() > 0.1)))
+        st = capi.BvhStats()
+        s = Scene.from_arrays(hs, mat, tex)
+        assert lib.crt_bvh_build_check(C.byref(s.desc), C.byref(st)) == capi.CRT_OK, (it, lib.crt_last_error_string(None))
+        assert st.n_prims == sum(h["active"] for h in hs) and st.max_depth < 64
+
+    base = dict(type=capi.SPHERE, cx=0.0, cy=0.0, cz=0.0, a=1.0, b=0.0, material=0, active=1)
+    others = [dict(base, cx=float(i + 3)) for i in range(5)]
+    nan, inf = float("nan"), float("inf")
+    bad = [dict(base, cx=nan), dict(base, cy=inf), dict(base, cz=-inf), dict(base, a=nan), dict(base, a=inf),
+           dict(base, type=capi.XZRECT, b=nan), dict(base, material=5), dict(base, material=-1), dict(base, type=17)]
+    for h in bad:
+        for rest in ([], others):
+            s = Scene.from_arrays([h] + rest, mat, tex)
+            assert lib.crt_bvh_build_check(C.byref(s.desc), C.byref(capi.BvhStats())) == capi.CRT_ERR_INVALID, h
+            assert b"hittable 0" in lib.crt_last_error_string(None)
+    st = capi.BvhStats()
+    s = Scene.from_arrays([dict(base, cx=nan, a=inf, material=99, active=0)] + others, mat, tex)  # inactive: not looked at
+    assert lib.crt_bvh_build_check(C.byref(s.desc), C.byref(st)) == capi.CRT_OK and st.n_prims == 5
+    s = Scene.from_arrays([dict(base, a=-0.5)], mat, tex)  # negative radius = the hollow-sphere idiom: its box uses |r|
+    assert lib.crt_bvh_build_check(C.byref(s.desc), C.byref(st)) == capi.CRT_OK and st.n_prims == 1
+    for m, t in (([dict(type=capi.LAMBERTIAN, texture=3)], tex), ([dict(type=9, texture=0)], tex),
+                 ([dict(type=capi.LAMBERTIAN, texture=0)], [dict(type=capi.IMAGE, image=2)])):
+        s = Scene.from_arrays([base], m, t)
+        assert lib.crt_bvh_build_check(C.byref(s.desc), C.byref(capi.BvhStats())) == capi.CRT_ERR_INVALID
+
