@@ -165,7 +165,10 @@ crt_status crt_synchronize(crt_context* ctx);
 crt_status crt_set_bvh_builder(crt_context* ctx, int32_t builder);
 /* CRT_ERR_INVALID (with the offending index in the message) for an ACTIVE hittable with an unknown type, a material /
  * texture / image index out of range, or a NaN / infinite coordinate or size: the reference would never hit such a primitive,
- * a BVH over it would be poisoned. Inactive hittables are not looked at. A negative sphere radius is legal (|r| bounds it). */
+ * a BVH over it would be poisoned. Inactive hittables are not looked at. A negative sphere radius is legal here: |r| bounds
+ * it and the normal flips (the hollow-sphere idiom). The reference gives such a sphere an inverted box (Hittable.cuh:112-116),
+ * which AABB::Hit rejects (AABB.cuh:44-45), so there it is visible only through whatever sibling box happens to cover it -
+ * tree-dependent behaviour that no other tree can reproduce; none of the reference's scenes or GUI ranges produce one. */
 crt_status crt_scene_upload(crt_context* ctx, const crt_scene_desc* scene);
 /* Walk the reference's own pointer graph: `world` is the Hittable of type BVHNODE that
  * LaunchKernel receives (Kernel.cu:178-181). Host-readable (managed or host) memory. */
