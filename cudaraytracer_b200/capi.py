@@ -126,6 +126,7 @@ SIGNATURES = {
     "crt_row_tiles_rows": (C.c_uint32, [C.c_uint32, C.c_uint32]),
     "crt_read_rgba": (C.c_int, [_P, _P]),
     "crt_rgba_device_ptr": (_P, [_P]),
+    "crt_peer_enable": (C.c_int, [_P, C.c_int32]),
     "crt_ipc_export": (C.c_int, [_P, C.c_int32, _P]),
     "crt_ipc_open": (C.c_int, [_P, _P, C.POINTER(_P)]),
     "crt_ipc_close": (C.c_int, [_P, _P]),

@@ -1399,6 +1399,20 @@ crt_status crt_ipc_close(crt_context* ctx, void* device_ptr)
     return crt_set_error(ctx, CRT_ERR_INVALID, "crt_ipc_close: not a pointer returned by crt_ipc_open on this context");
 }
 
+crt_status crt_peer_enable(crt_context* ctx, int32_t peer_device)
+{
+    if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_peer_enable: ctx is NULL");
+    if (peer_device == ctx->device) return CRT_OK;
+    CU(cudaSetDevice(ctx->device));
+    int can = 0;
+    CU(cudaDeviceCanAccessPeer(&can, ctx->device, peer_device));
+    if (!can) return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, "crt_peer_enable: this device cannot address the memory of peer_device");
+    const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return CRT_OK; } // idempotent
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "cudaDeviceEnablePeerAccess");
+    return CRT_OK;
+}
+
 crt_status crt_resolve_peers(crt_context* ctx, const void* const* peer_accum, int32_t n_peers, uint32_t row_begin, uint32_t row_end,
                              void* device_out_rgba8, void* device_out_sum)
 {

@@ -237,6 +237,10 @@ void*      crt_rgba_device_ptr(crt_context* ctx);
  * be exchanged again afterwards. ---- */
 #define CRT_IPC_HANDLE_BYTES 64
 enum { CRT_BUFFER_ACCUM = 0, CRT_BUFFER_RGBA = 1 };
+/* All GPUs in ONE process (one context per device, e.g. one host thread per GPU; examples/multigpu_render.cpp): no IPC is
+ * needed - let this context's device address peer_device's memory, then pass crt_accum_device_ptr / crt_rgba_device_ptr of
+ * the context on peer_device to crt_resolve_peers / crt_resolve_rows here. Idempotent. CRT_ERR_UNSUPPORTED without a P2P path. */
+crt_status crt_peer_enable(crt_context* ctx, int32_t peer_device);
 crt_status crt_ipc_export(crt_context* ctx, int32_t which, uint8_t out_handle[CRT_IPC_HANDLE_BYTES]);
 crt_status crt_ipc_open(crt_context* ctx, const uint8_t handle[CRT_IPC_HANDLE_BYTES], void** out_device_ptr);
 crt_status crt_ipc_close(crt_context* ctx, void* device_ptr);

@@ -83,6 +83,21 @@ def test_c_host_example_builds_and_fails_loudly_without_a_gpu(tmp_path):
         assert r.returncode != 0 and "no CUDA device" in r.stderr
 
 
+def test_native_multigpu_host_example_builds_and_fails_loudly_without_a_gpu(tmp_path):
+    """examples/multigpu_render.cpp: one thread and one context per GPU over the C ABI. Without a device every thread must get
+    the library's loud error and the process must end (no thread left waiting at a barrier)."""
+    import subprocess
+    import torch
+    exe = os.path.join(ROOT, "examples", "multigpu_render")
+    assert os.path.exists(exe), "built by make -C cudaraytracer_b200/csrc (target examples)"
+    if torch.cuda.is_available():
+        pytest.skip("with a GPU this is tests/test_gpu_multigpu.py::test_native_multigpu_host_example")
+    for mode in ("tiles", "spp"):
+        r = subprocess.run([exe, "3", mode, "1", "64", "36", "2", "8", str(tmp_path / "f.png")], capture_output=True, text=True, timeout=60)
+        assert r.returncode == 1 and "no CUDA device" in r.stderr
+    assert subprocess.run([exe, "99"], capture_output=True, text=True, timeout=60).returncode == 2
+
+
 @pytest.mark.parametrize("kind,hint,n", [(capi.SCENE_RTIOW, 0, None), (capi.SCENE_REFERENCE_DEFAULT, 0, 17), (capi.SCENE_TEXTURED, 64, None),
                                          (capi.SCENE_STRESS_10K, 0, 10001), (capi.SCENE_GRID_1M, 300, 90001)])
 def test_host_bvh_build_invariants(kind, hint, n):

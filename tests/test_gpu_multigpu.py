@@ -181,6 +181,25 @@ def test_ipc_export_open_close_across_processes():
     r.close()
 
 
+@pytest.mark.skipif(not os.environ.get("CRT_TEST_EXPERIMENTAL"), reason="examples/multigpu_render.cpp has not run on a B200 yet "
+                    "(its entry points have, one by one); CRT_TEST_EXPERIMENTAL=1 runs it")
+def test_native_multigpu_host_example(tmp_path):
+    """examples/multigpu_render.cpp on every GPU of the box, tile- and spp-sharded: the PNG must be byte-identical to the
+    one-GPU frame (one GPU: the two modes and the peer close-out with a single buffer)."""
+    import subprocess
+    import torch
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "examples", "multigpu_render")
+    G = torch.cuda.device_count()
+    files = []
+    for g, mode in [(1, "tiles"), (1, "spp"), (G, "tiles"), (G, "spp")]:
+        out = str(tmp_path / f"f_{g}_{mode}.png")
+        r = subprocess.run([exe, str(g), mode, "1", "200", "113", "6", "50", out], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        files.append(open(out, "rb").read())
+    assert files[0].startswith(b"\x89PNG") and all(f == files[0] for f in files[1:])
+
+
 def test_c_host_example_renders_a_ppm(tmp_path):
     """examples/headless_render.c (plain C over the C ABI): progressive passes, resolve, PPM on disk."""
     import os
