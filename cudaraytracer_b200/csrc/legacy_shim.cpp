@@ -28,10 +28,19 @@ struct Legacy
 Legacy g;
 std::mutex g_mu;
 
+// Change detector of the flattened scene, run on every LaunchKernel call: eight bytes per multiply (a byte-wise FNV is one
+// dependent multiply per byte, ~1 GB/s - 6 ms per frame on a 60 k-sphere scene, more than the frame itself at 1 spp).
 uint64_t fnv(uint64_t h, const void* p, size_t n)
 {
     const unsigned char* b = (const unsigned char*)p;
-    for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 0x100000001B3ull; }
+    size_t i = 0;
+    for (; i + 8 <= n; i += 8) {
+        uint64_t w;
+        memcpy(&w, b + i, 8);
+        h = (h ^ w) * 0x9E3779B97F4A7C15ull;
+        h ^= h >> 29;
+    }
+    for (; i < n; i++) { h ^= b[i]; h *= 0x100000001B3ull; }
     return h;
 }
 
