@@ -1116,10 +1116,13 @@ template <int NSLOTS, bool ALL, int SCHED = 0> static cudaError_t launch_pipe(co
 // the two pool sizes the planner picks have kernels with the size compiled in; anything else (CRT_PIPE_SLOTS) runs the generic one
 static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st, bool all, int sched)
 {
-    if (sched == 1) { // experimental round schedule (pipeline.cuh): only with a compiled-in pool size
+    // experimental builds (pipeline.cuh, CRT_PIPE_SCHED): only with a compiled-in pool size; bit 1 needs the scene in shared memory
+    if (sched == 1 || (sched == 3 && !all)) {
         if (W.n_slots == 1024) return all ? launch_pipe<1024, true, 1>(W, grid, smem, st) : launch_pipe<1024, false, 1>(W, grid, smem, st);
         if (W.n_slots == 2048) return all ? launch_pipe<2048, true, 1>(W, grid, smem, st) : launch_pipe<2048, false, 1>(W, grid, smem, st);
     }
+    if ((sched == 2 || sched == 3) && all && W.n_slots == 2048)
+        return sched == 2 ? launch_pipe<2048, true, 2>(W, grid, smem, st) : launch_pipe<2048, true, 3>(W, grid, smem, st);
 #define CRT_PIPE_CASE(N) case N: return all ? launch_pipe<N, true>(W, grid, smem, st) : launch_pipe<N, false>(W, grid, smem, st)
     switch (W.n_slots) {
         CRT_PIPE_CASE(1024);

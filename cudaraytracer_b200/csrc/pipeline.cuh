@@ -233,6 +233,9 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
 // reaches a leaf in the first node visit sits the second one out, and ONE leaf visit serves the leaves of both - fewer, fuller
 // leaf visits (they run at 10.7 of 32 lanes, profiles/r01_l_pipe_c2_by_line.txt). Experimental (CRT_PIPE_SCHED=1), not yet
 // measured; every lane walks its own tree in the same order either way, so the image is the same.
+//        2 (SMEM_ALL only) = 0 with the staged nodes' child references as byte offsets (trace.cuh stage_scene OFFS) and the
+//        descend / push / pop decision of a visit written without branches: 57 instructions per visit, all predicated (no
+//        convergence barrier), against 55 + ~5 of pop path behind two branches. 3 = 1 + 2.
 template <int NSLOTS, bool SMEM_ALL, int SCHED = 0>
 __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_constant__ PipeArgs A)
 {
@@ -247,7 +250,8 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
     P.px = reinterpret_cast<uint2*>(smem + 3 * P.n);
     P.ring = reinterpret_cast<unsigned short*>(smem + 3 * P.n + P.n / 2);
     // 70 bytes per slot: N is a multiple of 64, so the scene tables that follow stay 16-byte aligned
-    const SceneView S = stage_scene<true>(A.R.scene, smem + (3 * P.n + P.n / 2) + (PQ_COUNT * P.n) / 8);
+    constexpr bool OFFS = SMEM_ALL && (SCHED & 2) != 0;
+    const SceneView S = stage_scene<true, OFFS>(A.R.scene, smem + (3 * P.n + P.n / 2) + (PQ_COUNT * P.n) / 8);
     for (int i = threadIdx.x; i < PQ_COUNT * P.n; i += PIPE_THREADS) P.ring[i] = (unsigned short)(i >= PQ_GEN * P.n ? i - PQ_GEN * P.n : PIPE_EMPTY);
     if (threadIdx.x <= PQ_COUNT) { ctl.head[threadIdx.x] = 0u; ctl.tail[threadIdx.x] = threadIdx.x == PQ_GEN ? (unsigned int)P.n : 0u; }
     if (threadIdx.x == 0) ctl.live = P.n; // every slot starts in the GEN queue
@@ -329,11 +333,11 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         const int leave_below = refill_short ? 1 : A.thresh; // EXT ran dry: leaving early would only spin
         int rounds_left = A.max_rounds;
         while (true) { // two node visits per vote
-            node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
-            if (SCHED == 0) {
+            node_step_all<SMEM_ALL, OFFS>(S, r, t_min, h.t, cur, sp, stack);
+            if ((SCHED & 1) == 0) {
                 if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
             }
-            node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
+            node_step_all<SMEM_ALL, OFFS>(S, r, t_min, h.t, cur, sp, stack);
             if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
             act = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
             if (__popc(act) < leave_below || --rounds_left <= 0) break;
