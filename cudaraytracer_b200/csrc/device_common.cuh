@@ -154,8 +154,13 @@ __device__ __forceinline__ float dot3(float3 a, float3 b) { return fmaf(a.z, b.z
 __device__ __forceinline__ float3 madd3(float s, float3 b, float3 a) { return f3(fmaf(s, b.x, a.x), fmaf(s, b.y, a.y), fmaf(s, b.z, a.z)); }
 
 // Approximate single-instruction forms for the throughput path (MUFU.RCP / MUFU.SQRT; ~1-2 ulp).
+#ifdef CRT_HOST_SIM // tests/sim/trace_sim.cpp compiles the traversal for the HOST (g++) to check its logic without a GPU
+__device__ __forceinline__ float fast_rcp(float x) { return 1.0f / x; }
+__device__ __forceinline__ float fast_sqrt(float x) { return sqrtf(x); }
+#else
 __device__ __forceinline__ float fast_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ float fast_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+#endif
 __device__ __forceinline__ float fast_div(float a, float b) { return __fdividef(a, b); }
 
 // IEEE, never-contracted versions used by the exact path (bit-for-bit the host oracle's arithmetic).

@@ -29,9 +29,14 @@ struct SceneView
 // 32 bytes through the read-only path in one instruction (PTX 8.8 ld.global.nc.v8, 32-byte aligned address).
 __device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b)
 {
+#ifdef CRT_HOST_SIM
+    a = p[0];
+    b = p[1];
+#else
     asm("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
         : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
         : "l"(p));
+#endif
 }
 
 // Two shared-memory layouts of the node table, both chosen so that lanes at different nodes spread over all eight 16-byte

@@ -1,0 +1,192 @@
+// trace_sim.cpp — TEST INFRASTRUCTURE: cudaraytracer_b200/csrc/trace.cuh (the BVH traversal of every kernel) compiled for the
+// HOST with g++, so that its logic can be checked without a GPU: the closest hit of the traversal — in each of its forms: the
+// megakernel's node_step loop, the pipelined kernel's node_step_all rounds, and the experimental byte-offset / branch-free
+// node visit with either round schedule — must be the closest hit of a brute-force loop over all primitives, bit for bit,
+// on the trees crt_pack_scene builds. Only the approximate reciprocal / square root differ from the device (IEEE here), which
+// no comparison in this file depends on: every form runs the same arithmetic.
+//
+//   trace_sim <scene kind 1..5> <size hint> <rays> <seed>      exit code 0 = all forms agree
+#define CRT_HOST_SIM 1
+#include <cuda_runtime.h> // vector types only
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#undef __device__
+#undef __host__
+#undef __forceinline__
+#undef __global__
+#define __device__
+#define __host__
+#define __forceinline__ inline
+#define __global__
+
+// the few device intrinsics the headers use, with their host meaning
+static inline int __float_as_int(float f) { int i; memcpy(&i, &f, 4); return i; }
+static inline float __int_as_float(int i) { float f; memcpy(&f, &i, 4); return f; }
+static inline unsigned __float_as_uint(float f) { unsigned i; memcpy(&i, &f, 4); return i; }
+static inline float __uint_as_float(unsigned i) { float f; memcpy(&f, &i, 4); return f; }
+template <class T> static inline T __ldg(const T* p) { return *p; }
+static inline float __fmul_rn(float a, float b) { volatile float r = a * b; return r; }
+static inline float __fadd_rn(float a, float b) { volatile float r = a + b; return r; }
+static inline float __fsub_rn(float a, float b) { volatile float r = a - b; return r; }
+static inline float __fdiv_rn(float a, float b) { volatile float r = a / b; return r; }
+static inline float __fsqrt_rn(float a) { return sqrtf(a); }
+static inline float __fdividef(float a, float b) { return a / b; }
+static inline long long __float2ll_rn(float x) { return llrintf(x); }
+static inline unsigned __umulhi(unsigned a, unsigned b) { return (unsigned)(((unsigned long long)a * b) >> 32); }
+using std::max;
+using std::min;
+static struct { unsigned x, y, z; } threadIdx = {0, 0, 0}, blockDim = {1, 1, 1};
+
+#include "crt_internal.h"
+#include "trace.cuh"
+
+namespace {
+
+uint64_t g_state;
+double rnd() // splitmix64 -> [0, 1)
+{
+    uint64_t z = (g_state += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return (double)(z >> 11) * (1.0 / 9007199254740992.0);
+}
+
+Hit brute_force(const SceneView& S, int n_prims, const std::vector<int>& codes, const TravRay& r, float t_min)
+{
+    Hit h;
+    h.t = 3.402823466e+38f;
+    h.leaf = -1;
+    for (int i = 0; i < n_prims; i++) {
+        float t;
+        if (leaf_test<false, true>(S, codes[i], r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) { h.t = t; h.leaf = codes[i]; }
+    }
+    return h;
+}
+
+// one lane of k_render_pipe's traversal: rounds of node / leaf visits (pipeline.cuh), SCHED bit 0 = node, node, leaf
+template <bool OFFS, int SCHED> Hit pipe_lane(const SceneView& S, const TravRay& r, float t_min, long& visits)
+{
+    Hit h;
+    h.t = 3.402823466e+38f;
+    h.leaf = -1;
+    int stack[CRT_STACK_SIZE], sp = 0;
+    int cur = trav_begin<false, true>(S, r, t_min, h);
+    while (cur != CRT_TRAV_DONE) {
+        node_step_all<true, OFFS>(S, r, t_min, h.t, cur, sp, stack);
+        if ((SCHED & 1) == 0) {
+            if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, true>(S, r, t_min, h, cur, sp, stack);
+        }
+        node_step_all<true, OFFS>(S, r, t_min, h.t, cur, sp, stack);
+        if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, true>(S, r, t_min, h, cur, sp, stack);
+        if (++visits > 100000000L) { fprintf(stderr, "traversal does not terminate\n"); exit(3); }
+        if (sp < 0 || sp > CRT_STACK_SIZE) { fprintf(stderr, "stack pointer out of range: %d\n", sp); exit(3); }
+    }
+    return h;
+}
+
+} // namespace
+
+int main(int argc, char** argv)
+{
+    const int kind = argc > 1 ? atoi(argv[1]) : CRT_SCENE_RTIOW;
+    const uint64_t hint = argc > 2 ? (uint64_t)atoll(argv[2]) : 0;
+    const int n_rays = argc > 3 ? atoi(argv[3]) : 20000;
+    g_state = argc > 4 ? (uint64_t)atoll(argv[4]) : 1;
+
+    crt_scene_builder* sb = nullptr;
+    if (crt_scene_generate(kind, 1984, hint, &sb) != CRT_OK) { fprintf(stderr, "scene: %s\n", crt_last_error_string(nullptr)); return 2; }
+    CrtPackedScene P;
+    std::string err;
+    if (!crt_pack_scene(crt_scene_builder_desc(sb), &P, &err)) { fprintf(stderr, "pack: %s\n", err.c_str()); return 2; }
+    const int nn = (int)P.nodes.size(), np = (int)P.stats.n_prims;
+
+    DevScene D;
+    memset(&D, 0, sizeof(D));
+    D.nodes = reinterpret_cast<const float4*>(P.nodes.data());
+    D.prims = reinterpret_cast<const float4*>(P.prims.data());
+    D.prim_k = P.prim_k.data();
+    D.mats = reinterpret_cast<const float4*>(P.mats.data());
+    D.prim_id = P.prim_id.data();
+    D.n_nodes = nn; D.n_prims = np;
+    int32_t entry = 0, codes[CRT_MAX_TOP] = {0, 0, 0, 0};
+    D.n_top = crt_peel_top(P.nodes.data(), P.nodes.size(), (uint64_t)np, CRT_MAX_TOP, &entry, codes);
+    D.entry = entry;
+    for (int k = 0; k < CRT_MAX_TOP; k++) D.top_code[k] = k < D.n_top ? codes[k] : 0;
+
+    // leaf codes of every primitive (for the brute-force loop), read off the tree
+    std::vector<int> leaf_code((size_t)std::max(np, 1), 0);
+    int found = 0;
+    for (const CrtPackedNode& n : P.nodes)
+        for (int c = 0; c < 2; c++)
+            if (n.child[c] < 0 && np > 0) {
+                const int code = ~n.child[c];
+                const int slot = code & CRT_LEAF_INDEX_MASK;
+                if (slot < np && (np >= 2 || c == 0)) { leaf_code[(size_t)slot] = code; found++; }
+            }
+    if (found != np) { fprintf(stderr, "tree names %d leaves, scene has %d primitives\n", found, np); return 2; }
+
+    // the stagings: everything behind 'global' pointers, the megakernel's word-major shared-memory table, the padded (80-byte)
+    // table of the one-CTA-per-SM kernels, and that table with byte-offset child references
+    D.smem_nodes = D.smem_prims = D.smem_mats = 0;
+    std::vector<float4> smem0(16), smem1((size_t)nn * CRT_SMEM_NODE_F4 + (size_t)np * 3 + 16), smem2(smem1.size());
+    const SceneView Sg = stage_scene<false>(D, smem0.data());
+    D.smem_nodes = nn; D.smem_prims = np; D.smem_mats = np;
+    std::vector<float4> smem3(smem1.size());
+    const SceneView Sw = stage_scene<false>(D, smem3.data()); // word-major table: what the megakernel stages
+    const SceneView Sp = stage_scene<true, false>(D, smem1.data());
+    const SceneView So = stage_scene<true, true>(D, smem2.data());
+
+    // rays: from a camera-like point towards the scene, from random points inside the scene box in random directions, and
+    // axis-parallel ones (zero direction components take the clamped-reciprocal path of trav_setup)
+    float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
+    for (int i = 0; i < np; i++)
+        for (int a = 0; a < 3; a++) {
+            const float c = P.prims[4 * (size_t)i + a];
+            if (fabsf(c) < 200.f) { lo[a] = std::min(lo[a], c); hi[a] = std::max(hi[a], c); }
+        }
+    for (int a = 0; a < 3; a++) if (!(lo[a] <= hi[a])) { lo[a] = -1.f; hi[a] = 1.f; }
+    long mism = 0, hits = 0, visits = 0;
+    const float t_min = 0.001f;
+    for (int i = 0; i < n_rays; i++) {
+        float3 o, d;
+        const int mode = i % 3;
+        if (mode == 0) {
+            o = make_float3(13.f + (float)rnd(), 2.f + (float)rnd(), 3.f + (float)rnd());
+            d = make_float3((float)(lo[0] + (hi[0] - lo[0]) * rnd()) - o.x, (float)(lo[1] + (hi[1] - lo[1]) * rnd()) - o.y,
+                            (float)(lo[2] + (hi[2] - lo[2]) * rnd()) - o.z);
+        }
+        else {
+            o = make_float3((float)(lo[0] + (hi[0] - lo[0]) * rnd()), (float)(lo[1] + (hi[1] - lo[1]) * rnd()) + 0.5f,
+                            (float)(lo[2] + (hi[2] - lo[2]) * rnd()));
+            d = make_float3((float)(2 * rnd() - 1), (float)(2 * rnd() - 1), (float)(2 * rnd() - 1));
+            if (mode == 2) { const int z = (int)(rnd() * 3); (z == 0 ? d.x : z == 1 ? d.y : d.z) = 0.f; }
+        }
+        const TravRay r = trav_setup<false>(o, d);
+        const Hit want = brute_force(Sp, np, leaf_code, r, t_min);
+        unsigned nb = 0, npr = 0;
+        Hit got[6];
+        got[0] = closest_hit<false, false, false>(Sg, o, d, t_min, 3.402823466e+38f, nb, npr); // megakernel form, global tables
+        got[1] = closest_hit<false, false, true>(Sw, o, d, t_min, 3.402823466e+38f, nb, npr);  // ... tables in 'shared memory'
+        got[2] = pipe_lane<false, 0>(Sp, r, t_min, visits);
+        got[3] = pipe_lane<false, 1>(Sp, r, t_min, visits);
+        got[4] = pipe_lane<true, 2>(So, r, t_min, visits);
+        got[5] = pipe_lane<true, 3>(So, r, t_min, visits);
+        hits += want.leaf >= 0;
+        for (int k = 0; k < 6; k++)
+            if (got[k].leaf != want.leaf || memcmp(&got[k].t, &want.t, 4) != 0) {
+                if (mism++ < 5)
+                    fprintf(stderr, "ray %d form %d: leaf %d t %.9g, brute force: leaf %d t %.9g\n", i, k, got[k].leaf, got[k].t, want.leaf, want.t);
+            }
+    }
+    printf("scene %d (%d primitives, %d nodes, %d peeled): %d rays, %ld hits, %ld mismatches\n", kind, np, nn, D.n_top, n_rays, hits, mism);
+    crt_scene_builder_free(sb);
+    return mism ? 1 : 0;
+}

@@ -1,0 +1,35 @@
+"""The BVH traversal of the kernels (cudaraytracer_b200/csrc/trace.cuh) compiled for the HOST (tests/sim/trace_sim.cpp, g++ with
+-DCRT_HOST_SIM) and run against a brute-force closest hit on the trees the library's own builder packs. No GPU: this checks the
+LOGIC of every traversal form - the megakernel's node_step loop on global and on word-major shared tables, the pipelined
+kernel's node_step_all rounds, and the experimental builds (CRT_PIPE_SCHED bits: node-node-leaf rounds, byte-offset child
+references with the branch-free visit) - bit for bit; the device arithmetic itself is what the -m gpu parity tests pin."""
+import os
+import subprocess
+
+import pytest
+
+from cudaraytracer_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def trace_sim(tmp_path_factory):
+    exe = str(tmp_path_factory.mktemp("sim") / "trace_sim")
+    libdir = os.path.dirname(capi.LIB_PATH)
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    cmd = ["g++", "-std=c++17", "-O1", "-ffp-contract=off", "-Wno-attributes", "-Wno-unknown-pragmas",
+           "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "cudaraytracer_b200", "csrc"), "-I", os.path.join(cuda, "include"),
+           os.path.join(ROOT, "tests", "sim", "trace_sim.cpp"), "-o", exe, "-L", libdir, "-lcrt", f"-Wl,-rpath,{libdir}"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return exe
+
+
+@pytest.mark.parametrize("kind,hint,rays", [(capi.SCENE_RTIOW, 0, 6000), (capi.SCENE_REFERENCE_DEFAULT, 0, 6000), (capi.SCENE_TEXTURED, 0, 4000),
+                                           (capi.SCENE_STRESS_10K, 0, 3000), (capi.SCENE_GRID_1M, 40, 3000), (capi.SCENE_GRID_1M, 1, 2000),
+                                           (capi.SCENE_GRID_1M, 2, 2000)])
+def test_every_traversal_form_finds_the_brute_force_closest_hit(trace_sim, kind, hint, rays):
+    r = subprocess.run([trace_sim, str(kind), str(hint), str(rays), str(kind * 100 + hint)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert " 0 mismatches" in r.stdout
