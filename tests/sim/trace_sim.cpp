@@ -72,20 +72,25 @@ Hit brute_force(const SceneView& S, int n_prims, const std::vector<int>& codes, 
 }
 
 // one lane of k_render_pipe's traversal: rounds of node / leaf visits (pipeline.cuh), SCHED bit 0 = node, node, leaf
+long g_node_visits = 0, g_leaf_visits = 0; // of the default form (statistics of the tree, printed at the end)
+
 template <bool OFFS, int SCHED> Hit pipe_lane(const SceneView& S, const TravRay& r, float t_min, long& visits)
 {
+    constexpr bool COUNT = !OFFS && SCHED == 0;
     Hit h;
     h.t = 3.402823466e+38f;
     h.leaf = -1;
     int stack[CRT_STACK_SIZE], sp = 0;
     int cur = trav_begin<false, true>(S, r, t_min, h);
     while (cur != CRT_TRAV_DONE) {
+        if (COUNT && cur >= 0) g_node_visits++;
         node_step_all<true, OFFS>(S, r, t_min, h.t, cur, sp, stack);
         if ((SCHED & 1) == 0) {
-            if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, true>(S, r, t_min, h, cur, sp, stack);
+            if (cur < 0 && cur != CRT_TRAV_DONE) { g_leaf_visits += COUNT; leaf_step<false, true>(S, r, t_min, h, cur, sp, stack); }
         }
+        if (COUNT && cur >= 0) g_node_visits++;
         node_step_all<true, OFFS>(S, r, t_min, h.t, cur, sp, stack);
-        if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, true>(S, r, t_min, h, cur, sp, stack);
+        if (cur < 0 && cur != CRT_TRAV_DONE) { g_leaf_visits += COUNT; leaf_step<false, true>(S, r, t_min, h, cur, sp, stack); }
         if (++visits > 100000000L) { fprintf(stderr, "traversal does not terminate\n"); exit(3); }
         if (sp < 0 || sp > CRT_STACK_SIZE) { fprintf(stderr, "stack pointer out of range: %d\n", sp); exit(3); }
     }
@@ -187,6 +192,8 @@ int main(int argc, char** argv)
             }
     }
     printf("scene %d (%d primitives, %d nodes, %d peeled): %d rays, %ld hits, %ld mismatches\n", kind, np, nn, D.n_top, n_rays, hits, mism);
+    printf("tree: SAH cost %.3f, depth %d; per ray %.3f node visits, %.3f leaf visits (+ %d peeled tests)\n", P.stats.sah_cost, (int)P.stats.max_depth,
+           (double)g_node_visits / n_rays, (double)g_leaf_visits / n_rays, D.n_top);
     crt_scene_builder_free(sb);
     return mism ? 1 : 0;
 }
