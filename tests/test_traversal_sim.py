@@ -33,3 +33,13 @@ def test_every_traversal_form_finds_the_brute_force_closest_hit(trace_sim, kind,
     r = subprocess.run([trace_sim, str(kind), str(hint), str(rays), str(kind * 100 + hint)], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
     assert " 0 mismatches" in r.stdout
+
+
+@pytest.mark.parametrize("kind,hint", [(capi.SCENE_RTIOW, 0), (capi.SCENE_TEXTURED, 0), (capi.SCENE_STRESS_10K, 0), (capi.SCENE_GRID_1M, 3)])
+def test_rotated_trees_are_still_trees(trace_sim, kind, hint):
+    """CRT_BVH_ROTATE (experimental post-pass of the host builder: tree rotations) must leave a tree every traversal form
+    agrees on with brute force; tests/sim/path_sim measures what it does to the box / primitive tests per ray."""
+    env = dict(os.environ, CRT_BVH_ROTATE="4")
+    r = subprocess.run([trace_sim, str(kind), str(hint), "3000", "11"], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and " 0 mismatches" in r.stdout, r.stdout + r.stderr
+
