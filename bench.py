@@ -332,16 +332,19 @@ def run_gpu_arm(args):
         b_ray = {"mega": 64.0 / rpp / spp, "pipeline": 24.0 / rpp, "wavefront": 24.0 / rpp + 160.0}[resolved]
         hbm_gbs = kc.rays * b_ray / (k_ms / 1e3) / 1e9
         traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at this config, from the committed ncu capture
+        issue = None    # what actually bounds the kernel: issue-slot and lane utilisation of the same capture
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-                traffic = json.load(f).get(f"{args.workload}:{resolved}")
+                tj = json.load(f)
+            traffic = tj.get(f"{args.workload}:{resolved}")
+            issue = tj.get(f"{args.workload}:{resolved}_issue")
         except Exception:
             pass
         roofline = {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
                     "traffic": traffic, "kernel": kernel_name, "kernel_ms": k_ms, "kernel_share_of_step": k_ms / ms_per_step,
                     "bound_note": "no dense contraction and ~0.1 B/ray of DRAM traffic: neither tensor nor HBM bound; the kernel is "
                                   "FP32/ALU issue bound (SURVEY.md 8d), the HBM fraction is given beside it",
-                    "flop_per_ray": f_ray, "box_tests_per_ray": n_box, "prim_tests_per_ray": n_sph,
+                    "issue": issue, "flop_per_ray": f_ray, "box_tests_per_ray": n_box, "prim_tests_per_ray": n_sph,
                     "peak_source": f"148 SMs x 128 lanes x 2 x {sm_mhz:.0f} MHz (SM clock sampled during the timed region)",
                     "hbm": {"achieved": hbm_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s", "frac": hbm_gbs / peaks.get("hbm_gbs", 6650.0),
                             "bytes_per_ray": b_ray, "peak_source": peaks_src}}
