@@ -83,7 +83,7 @@ struct crt_context
     WfShard* d_shards = nullptr;       // work counters of the pipelined megakernel
     int pipe_thresh = 0, pipe_rounds = 0, // 0 = chosen per scene (render_pipeline)
          pipe_slots = 0, pipe_check = 4, pipe_ext_low = 256, // CRT_PIPE_THRESH / _ROUNDS / _SLOTS / _CHECK
-         pipe_sched = 0; // CRT_PIPE_SCHED: 1 = the experimental round schedule of pipeline.cuh
+         pipe_sched = 0; // CRT_PIPE_SCHED: bits selecting the experimental builds of pipeline.cuh (0 = the default kernel)
     uint64_t launches = 0;
 
     WavefrontState wf;
@@ -1116,13 +1116,17 @@ template <int NSLOTS, bool ALL, int SCHED = 0> static cudaError_t launch_pipe(co
 // the two pool sizes the planner picks have kernels with the size compiled in; anything else (CRT_PIPE_SLOTS) runs the generic one
 static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st, bool all, int sched)
 {
-    // experimental builds (pipeline.cuh, CRT_PIPE_SCHED): only with a compiled-in pool size; bit 1 needs the scene in shared memory
-    if (sched == 1 || (sched == 3 && !all)) {
-        if (W.n_slots == 1024) return all ? launch_pipe<1024, true, 1>(W, grid, smem, st) : launch_pipe<1024, false, 1>(W, grid, smem, st);
-        if (W.n_slots == 2048) return all ? launch_pipe<2048, true, 1>(W, grid, smem, st) : launch_pipe<2048, false, 1>(W, grid, smem, st);
-    }
-    if ((sched == 2 || sched == 3) && all && W.n_slots == 2048)
-        return sched == 2 ? launch_pipe<2048, true, 2>(W, grid, smem, st) : launch_pipe<2048, true, 3>(W, grid, smem, st);
+    // experimental builds (pipeline.cuh, CRT_PIPE_SCHED): only with a compiled-in pool size; bit 1 (byte offsets) needs the whole
+    // scene in shared memory and is built for the 2048-slot pool only; bit 2 (three node visits per round) overrides bit 0
+    if (W.n_slots != 1024 && W.n_slots != 2048) sched = 0;
+    if (!all || W.n_slots != 2048) sched &= ~2;
+    if (sched & 4) sched &= ~1;
+    sched &= 7;
+#define CRT_PIPE_EXP(N, ALL, S) if (W.n_slots == N && all == ALL && sched == S) return launch_pipe<N, ALL, S>(W, grid, smem, st)
+    CRT_PIPE_EXP(1024, true, 1); CRT_PIPE_EXP(1024, false, 1); CRT_PIPE_EXP(2048, true, 1); CRT_PIPE_EXP(2048, false, 1);
+    CRT_PIPE_EXP(1024, true, 4); CRT_PIPE_EXP(1024, false, 4); CRT_PIPE_EXP(2048, true, 4); CRT_PIPE_EXP(2048, false, 4);
+    CRT_PIPE_EXP(2048, true, 2); CRT_PIPE_EXP(2048, true, 3); CRT_PIPE_EXP(2048, true, 6);
+#undef CRT_PIPE_EXP
 #define CRT_PIPE_CASE(N) case N: return all ? launch_pipe<N, true>(W, grid, smem, st) : launch_pipe<N, false>(W, grid, smem, st)
     switch (W.n_slots) {
         CRT_PIPE_CASE(1024);

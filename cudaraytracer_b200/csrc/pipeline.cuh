@@ -236,6 +236,9 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
 //        2 (SMEM_ALL only) = 0 with the staged nodes' child references as byte offsets (trace.cuh stage_scene OFFS) and the
 //        descend / push / pop decision of a visit written without branches: 57 instructions per visit, all predicated (no
 //        convergence barrier), against 55 + ~5 of pop path behind two branches. 3 = 1 + 2.
+//        4 = node, node, node, leaf (6 = with 2): a ray makes 9.2 node visits and one leaf visit, and the lane model of
+//        tools/sched_model.py, fed with the real visit sequences, puts three node visits per leaf visit at the optimum
+//        (-12 % instructions in the rounds, against -5 % for two).
 template <int NSLOTS, bool SMEM_ALL, int SCHED = 0>
 __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_constant__ PipeArgs A)
 {
@@ -334,10 +337,11 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         int rounds_left = A.max_rounds;
         while (true) { // two node visits per vote
             node_step_all<SMEM_ALL, OFFS>(S, r, t_min, h.t, cur, sp, stack);
-            if ((SCHED & 1) == 0) {
+            if ((SCHED & 5) == 0) {
                 if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
             }
             node_step_all<SMEM_ALL, OFFS>(S, r, t_min, h.t, cur, sp, stack);
+            if (SCHED & 4) node_step_all<SMEM_ALL, OFFS>(S, r, t_min, h.t, cur, sp, stack);
             if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
             act = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
             if (__popc(act) < leave_below || --rounds_left <= 0) break;

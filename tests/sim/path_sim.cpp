@@ -8,6 +8,7 @@
 // nothing below depends on that.
 //
 //   path_sim <scene kind> <size hint> <width> <height> <spp> <max depth> [out.f32: width*height*3 mean radiance] [threads]
+//            [events file: the node / leaf visit sequence of every ray, for tools/sched_model.py]
 #define CRT_HOST_SIM 1
 #include <cuda_runtime.h> // vector types only
 
@@ -64,6 +65,9 @@ int main(int argc, char** argv)
     const uint32_t spp = argc > 5 ? (uint32_t)atoi(argv[5]) : 8, depth = argc > 6 ? (uint32_t)atoi(argv[6]) : 50;
     const char* out = argc > 7 ? argv[7] : "";
     unsigned nt = argc > 8 ? (unsigned)atoi(argv[8]) : std::max(1u, std::thread::hardware_concurrency());
+    // optional: the visit sequence of every ray ('N' / 'L' bytes, 0-terminated) for tools/sched_model.py; forces one thread
+    FILE* ev = argc > 9 ? fopen(argv[9], "wb") : nullptr;
+    if (ev) nt = 1;
 
     crt_scene_builder* sb = nullptr;
     if (crt_scene_generate(kind, 1984, hint, &sb) != CRT_OK) { fprintf(stderr, "scene: %s\n", crt_last_error_string(nullptr)); return 2; }
@@ -143,7 +147,21 @@ int main(int argc, char** argv)
                     while (true) {
                         unsigned nb = 0, npr = 0;
                         rays++;
-                        const Hit h = closest_hit<false, true, true>(S, o, d, 0.001f, 3.402823466e+38f, nb, npr);
+                        Hit h;
+                        if (!ev) h = closest_hit<false, true, true>(S, o, d, 0.001f, 3.402823466e+38f, nb, npr);
+                        else { // the same walk, written out: one byte per visit ('N' inner node, 'L' leaf), 0 ends the ray
+                            h.t = 3.402823466e+38f;
+                            h.leaf = -1;
+                            const TravRay r = trav_setup<false>(o, d);
+                            int stack[CRT_STACK_SIZE], sp = 0;
+                            int cur = trav_begin<false, true>(S, r, 0.001f, h);
+                            npr += (unsigned)S.n_top;
+                            while (cur != CRT_TRAV_DONE) {
+                                if (cur >= 0) { node_step<false, true>(S, r, 0.001f, h.t, cur, sp, stack); nb += 2; fputc('N', ev); }
+                                else { leaf_step<false, true>(S, r, 0.001f, h, cur, sp, stack); npr++; fputc('L', ev); }
+                            }
+                            fputc(0, ev);
+                        }
                         box += nb; prim += npr;
                         if (!scatter_step<true>(A, S, h, pixel, s, bounce, o, d, thr, add)) break;
                     }
@@ -166,6 +184,7 @@ int main(int argc, char** argv)
            "\"rays_per_path\": %.6f, \"box_tests_per_ray\": %.6f, \"prim_tests_per_ray\": %.6f}\n",
            kind, np, nn, D.n_top, W, H, spp, t_paths.load(), t_rays.load(), rays / (double)t_paths.load(), (double)t_box.load() / rays,
            (double)t_prim.load() / rays);
+    if (ev) fclose(ev);
     if (out[0]) {
         FILE* f = fopen(out, "wb");
         if (!f || fwrite(mean.data(), sizeof(float), mean.size(), f) != mean.size()) { fprintf(stderr, "cannot write %s\n", out); return 2; }

@@ -71,7 +71,8 @@ Hit brute_force(const SceneView& S, int n_prims, const std::vector<int>& codes, 
     return h;
 }
 
-// one lane of k_render_pipe's traversal: rounds of node / leaf visits (pipeline.cuh), SCHED bit 0 = node, node, leaf
+// one lane of k_render_pipe's traversal: rounds of node / leaf visits (pipeline.cuh), SCHED bit 0 = node, node, leaf,
+// bit 2 = node, node, node, leaf
 long g_node_visits = 0, g_leaf_visits = 0; // of the default form (statistics of the tree, printed at the end)
 
 template <bool OFFS, int SCHED> Hit pipe_lane(const SceneView& S, const TravRay& r, float t_min, long& visits)
@@ -85,11 +86,12 @@ template <bool OFFS, int SCHED> Hit pipe_lane(const SceneView& S, const TravRay&
     while (cur != CRT_TRAV_DONE) {
         if (COUNT && cur >= 0) g_node_visits++;
         node_step_all<true, OFFS>(S, r, t_min, h.t, cur, sp, stack);
-        if ((SCHED & 1) == 0) {
+        if ((SCHED & 5) == 0) {
             if (cur < 0 && cur != CRT_TRAV_DONE) { g_leaf_visits += COUNT; leaf_step<false, true>(S, r, t_min, h, cur, sp, stack); }
         }
         if (COUNT && cur >= 0) g_node_visits++;
         node_step_all<true, OFFS>(S, r, t_min, h.t, cur, sp, stack);
+        if (SCHED & 4) node_step_all<true, OFFS>(S, r, t_min, h.t, cur, sp, stack);
         if (cur < 0 && cur != CRT_TRAV_DONE) { g_leaf_visits += COUNT; leaf_step<false, true>(S, r, t_min, h, cur, sp, stack); }
         if (++visits > 100000000L) { fprintf(stderr, "traversal does not terminate\n"); exit(3); }
         if (sp < 0 || sp > CRT_STACK_SIZE) { fprintf(stderr, "stack pointer out of range: %d\n", sp); exit(3); }
@@ -177,15 +179,17 @@ int main(int argc, char** argv)
         const TravRay r = trav_setup<false>(o, d);
         const Hit want = brute_force(Sp, np, leaf_code, r, t_min);
         unsigned nb = 0, npr = 0;
-        Hit got[6];
+        Hit got[8];
         got[0] = closest_hit<false, false, false>(Sg, o, d, t_min, 3.402823466e+38f, nb, npr); // megakernel form, global tables
         got[1] = closest_hit<false, false, true>(Sw, o, d, t_min, 3.402823466e+38f, nb, npr);  // ... tables in 'shared memory'
         got[2] = pipe_lane<false, 0>(Sp, r, t_min, visits);
         got[3] = pipe_lane<false, 1>(Sp, r, t_min, visits);
         got[4] = pipe_lane<true, 2>(So, r, t_min, visits);
         got[5] = pipe_lane<true, 3>(So, r, t_min, visits);
+        got[6] = pipe_lane<false, 4>(Sp, r, t_min, visits);
+        got[7] = pipe_lane<true, 6>(So, r, t_min, visits);
         hits += want.leaf >= 0;
-        for (int k = 0; k < 6; k++)
+        for (int k = 0; k < 8; k++)
             if (got[k].leaf != want.leaf || memcmp(&got[k].t, &want.t, 4) != 0) {
                 if (mism++ < 5)
                     fprintf(stderr, "ray %d form %d: leaf %d t %.9g, brute force: leaf %d t %.9g\n", i, k, got[k].leaf, got[k].t, want.leaf, want.t);

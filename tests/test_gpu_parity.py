@@ -288,17 +288,18 @@ def test_variants_bit_identical_to_megakernel(renderer, name, kind, hint, W, H, 
         f"{(mega != wave).any(axis=-1).sum()} of {W * H} pixels differ between the variants"
 
 
-@pytest.mark.skipif(not os.environ.get("CRT_TEST_EXPERIMENTAL"), reason="experimental kernel builds (CRT_PIPE_SCHED=1..3), not the default "
+@pytest.mark.skipif(not os.environ.get("CRT_TEST_EXPERIMENTAL"), reason="experimental kernel builds (CRT_PIPE_SCHED=1..6), not the default "
                     "path: run with CRT_TEST_EXPERIMENTAL=1 when measuring it")
 @pytest.mark.parametrize("kind,hint", [(capi.SCENE_RTIOW, 0), (capi.SCENE_GRID_1M, 60)], ids=["rtiow", "grid3601"])
 def test_experimental_round_schedule_is_bit_identical(monkeypatch, kind, hint):
-    """CRT_PIPE_SCHED=1 (node, node, leaf rounds), 2 (byte-offset child references, branch-free node visit) and 3 (both) of
-    pipeline.cuh change the interleaving of the lanes and the naming of the nodes, never the result."""
+    """CRT_PIPE_SCHED=1 (node, node, leaf rounds), 2 (byte-offset child references, branch-free node visit), 3 (both), 4 (node,
+    node, node, leaf) and 6 (4 + 2) of pipeline.cuh change the interleaving of the lanes and the naming of the nodes, never the
+    result."""
     s = Scene.generate(kind, 1984, hint)
     W, H = 161, 91
     cam = s.default_camera(W, H)
     out = []
-    for sched in ("0", "1", "2", "3"):
+    for sched in ("0", "1", "2", "3", "4", "6"):
         monkeypatch.setenv("CRT_PIPE_SCHED", sched)
         r = Renderer(0)
         _setup(r, s, cam, W, H)
