@@ -8,7 +8,8 @@
 // nothing below depends on that.
 //
 //   path_sim <scene kind> <size hint> <width> <height> <spp> <max depth> [out.f32: width*height*3 mean radiance] [threads]
-//            [events file: the node / leaf visit sequence of every ray, for tools/sched_model.py]
+//            [events file: the node / leaf visit sequence of every ray, for tools/sched_model.py | ""]
+//            [ids file: primary-hit hittable index per pixel with the EXACT arithmetic (what crt_primary_ids computes)]
 #define CRT_HOST_SIM 1
 #include <cuda_runtime.h> // vector types only
 
@@ -66,7 +67,7 @@ int main(int argc, char** argv)
     const char* out = argc > 7 ? argv[7] : "";
     unsigned nt = argc > 8 ? (unsigned)atoi(argv[8]) : std::max(1u, std::thread::hardware_concurrency());
     // optional: the visit sequence of every ray ('N' / 'L' bytes, 0-terminated) for tools/sched_model.py; forces one thread
-    FILE* ev = argc > 9 ? fopen(argv[9], "wb") : nullptr;
+    FILE* ev = argc > 9 && argv[9][0] ? fopen(argv[9], "wb") : nullptr;
     if (ev) nt = 1;
 
     crt_scene_builder* sb = nullptr;
@@ -185,6 +186,20 @@ int main(int argc, char** argv)
            kind, np, nn, D.n_top, W, H, spp, t_paths.load(), t_rays.load(), rays / (double)t_paths.load(), (double)t_box.load() / rays,
            (double)t_prim.load() / rays);
     if (ev) fclose(ev);
+    if (argc > 10) { // k_primary_ids on the host: exact arithmetic, jitter (0.5, 0.5) -> hittable index per pixel (int32)
+        std::vector<int32_t> ids((size_t)W * H);
+        for (uint32_t y = 0; y < H; y++)
+            for (uint32_t x = 0; x < W; x++) {
+                float3 o, d;
+                camera_ray<true>(A.cam, W, H, (int)x, (int)y, 0.5f, 0.5f, o, d);
+                unsigned nb = 0, npr = 0;
+                const Hit h = closest_hit<true, false, true>(S, o, d, 0.001f, 3.402823466e+38f, nb, npr);
+                ids[(size_t)y * W + x] = h.leaf < 0 ? -1 : D.prim_id[h.leaf & CRT_LEAF_INDEX_MASK];
+            }
+        FILE* f = fopen(argv[10], "wb");
+        if (!f || fwrite(ids.data(), 4, ids.size(), f) != ids.size()) { fprintf(stderr, "cannot write %s\n", argv[10]); return 2; }
+        fclose(f);
+    }
     if (out[0]) {
         FILE* f = fopen(out, "wb");
         if (!f || fwrite(mean.data(), sizeof(float), mean.size(), f) != mean.size()) { fprintf(stderr, "cannot write %s\n", out); return 2; }

@@ -97,3 +97,21 @@ def test_traversal_counters_match_what_the_b200_reported(path_sim):
                          (st["box_tests_per_ray"], gpu["roofline"]["box_tests_per_ray"]),
                          (st["prim_tests_per_ray"], gpu["roofline"]["prim_tests_per_ray"])):
         assert abs(mine - theirs) <= 0.005 * theirs, (st, theirs)
+
+
+@pytest.mark.parametrize("name,kind,hint,W,H", [("rtiow", capi.SCENE_RTIOW, 0, 400, 225), ("default", capi.SCENE_REFERENCE_DEFAULT, 0, 321, 181),
+                                               ("textured", capi.SCENE_TEXTURED, 0, 320, 180), ("stress", capi.SCENE_STRESS_10K, 0, 320, 180),
+                                               ("grid3601", capi.SCENE_GRID_1M, 60, 257, 145)])
+def test_exact_primary_hit_ids_of_the_device_code_equal_the_oracles(path_sim, tmp_path, name, kind, hint, W, H):
+    """The EXACT-arithmetic path of the device code (camera_ray<true>, closest_hit<true>: what crt_primary_ids runs) on the
+    host, where its explicitly rounded operations are IEEE like the GPU's: hittable index per pixel bit-exact vs the oracle."""
+    ids_file = str(tmp_path / "ids.i32")
+    r = subprocess.run([path_sim, str(kind), str(hint), str(W), str(H), "1", "2", "", "0", "", ids_file], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr
+    ids = np.fromfile(ids_file, dtype=np.int32).reshape(H, W)
+    s = Scene.generate(kind, 1984, hint)
+    cam = s.default_camera(W, H)
+    ref = O.oracle_render(s, cam, W, H, 0, 50, want_ids=True, want_rgba=False, want_mean=False)["ids"]
+    assert np.array_equal(ids, ref), f"{int((ids != ref).sum())} of {W * H} pixels differ"
+    assert (ids >= 0).any()
+
