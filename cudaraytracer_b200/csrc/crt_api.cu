@@ -1119,13 +1119,15 @@ static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaS
     // experimental builds (pipeline.cuh, CRT_PIPE_SCHED): only with a compiled-in pool size; bit 1 (byte offsets) needs the whole
     // scene in shared memory and is built for the 2048-slot pool only; bit 2 (three node visits per round) overrides bit 0
     if (W.n_slots != 1024 && W.n_slots != 2048) sched = 0;
-    if (!all || W.n_slots != 2048) sched &= ~2;
+    if (!all || W.n_slots != 2048) sched &= ~(2 | 8);
+    if (sched & 8) sched &= ~2;
     if (sched & 4) sched &= ~1;
-    sched &= 7;
+    sched &= 15;
 #define CRT_PIPE_EXP(N, ALL, S) if (W.n_slots == N && all == ALL && sched == S) return launch_pipe<N, ALL, S>(W, grid, smem, st)
     CRT_PIPE_EXP(1024, true, 1); CRT_PIPE_EXP(1024, false, 1); CRT_PIPE_EXP(2048, true, 1); CRT_PIPE_EXP(2048, false, 1);
     CRT_PIPE_EXP(1024, true, 4); CRT_PIPE_EXP(1024, false, 4); CRT_PIPE_EXP(2048, true, 4); CRT_PIPE_EXP(2048, false, 4);
     CRT_PIPE_EXP(2048, true, 2); CRT_PIPE_EXP(2048, true, 3); CRT_PIPE_EXP(2048, true, 6);
+    CRT_PIPE_EXP(2048, true, 8); CRT_PIPE_EXP(2048, true, 9); CRT_PIPE_EXP(2048, true, 12);
 #undef CRT_PIPE_EXP
 #define CRT_PIPE_CASE(N) case N: return all ? launch_pipe<N, true>(W, grid, smem, st) : launch_pipe<N, false>(W, grid, smem, st)
     switch (W.n_slots) {

@@ -253,8 +253,9 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
     P.px = reinterpret_cast<uint2*>(smem + 3 * P.n);
     P.ring = reinterpret_cast<unsigned short*>(smem + 3 * P.n + P.n / 2);
     // 70 bytes per slot: N is a multiple of 64, so the scene tables that follow stay 16-byte aligned
-    constexpr bool OFFS = SMEM_ALL && (SCHED & 2) != 0;
-    const SceneView S = stage_scene<true, OFFS>(A.R.scene, smem + (3 * P.n + P.n / 2) + (PQ_COUNT * P.n) / 8);
+    constexpr bool PAIR = SMEM_ALL && (SCHED & 8) != 0;
+    constexpr bool OFFS = SMEM_ALL && (SCHED & 10) != 0;
+    const SceneView S = stage_scene<true, OFFS, PAIR>(A.R.scene, smem + (3 * P.n + P.n / 2) + (PQ_COUNT * P.n) / 8);
     for (int i = threadIdx.x; i < PQ_COUNT * P.n; i += PIPE_THREADS) P.ring[i] = (unsigned short)(i >= PQ_GEN * P.n ? i - PQ_GEN * P.n : PIPE_EMPTY);
     if (threadIdx.x <= PQ_COUNT) { ctl.head[threadIdx.x] = 0u; ctl.tail[threadIdx.x] = threadIdx.x == PQ_GEN ? (unsigned int)P.n : 0u; }
     if (threadIdx.x == 0) ctl.live = P.n; // every slot starts in the GEN queue
@@ -268,6 +269,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
     h.t = 0.f;
     h.leaf = -1;
     int stack[CRT_STACK_SIZE];
+    if (PAIR) stack[0] = CRT_TRAV_DONE; // sentinel: a pop of the empty stack yields "finished" (node_visit_pair)
     unsigned n_rays = 0, n_paths = 0;
     unsigned int shard_cursor = (blockIdx.x * PIPE_WARPS + warp) & (WF_SHARDS - 1);
     bool exhausted = false;
@@ -323,7 +325,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
                 h.t = 3.402823466e+38f;
                 h.leaf = -1;
                 cur = trav_begin<false, SMEM_ALL>(S, r, t_min, h);
-                sp = 0;
+                sp = PAIR ? 1 : 0;
             }
             refill_short = n < __popc(m);
         }
@@ -336,6 +338,16 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         const int leave_below = refill_short ? 1 : A.thresh; // EXT ran dry: leaving early would only spin
         int rounds_left = A.max_rounds;
         while (true) { // two node visits per vote
+            if (PAIR) {
+                node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
+                if ((SCHED & 5) == 0) {
+                    if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL, true>(S, r, t_min, h, cur, sp, stack);
+                }
+                node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
+                if (SCHED & 4) node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
+                if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL, true>(S, r, t_min, h, cur, sp, stack);
+            }
+            else {
             node_step_all<SMEM_ALL, OFFS>(S, r, t_min, h.t, cur, sp, stack);
             if ((SCHED & 5) == 0) {
                 if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
@@ -343,6 +355,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
             node_step_all<SMEM_ALL, OFFS>(S, r, t_min, h.t, cur, sp, stack);
             if (SCHED & 4) node_step_all<SMEM_ALL, OFFS>(S, r, t_min, h.t, cur, sp, stack);
             if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
+            }
             act = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
             if (__popc(act) < leave_below || --rounds_left <= 0) break;
         }

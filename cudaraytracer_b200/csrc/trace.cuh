@@ -98,7 +98,10 @@ template <bool SMEM_ALL> __device__ __forceinline__ void load_mat(const SceneVie
 // Stages the first smem_* entries of each table into dynamic shared memory. Call from every thread, then __syncthreads().
 // OFFS (experimental, needs PAD and the whole tree in shared memory): inner-child references of the staged nodes, and the
 // entry node, become BYTE OFFSETS into the staged table (index * 80), so a visit needs no address arithmetic at all.
-template <bool PAD, bool OFFS = false> __device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem)
+// PAIR (needs OFFS): the twelve box words of a staged node are interleaved child-wise, {c0.x, c1.x, c0.y, c1.y | c0.z, c1.z,
+// h0.x, h1.x | h0.y, h1.y, h0.z, h1.z}, so that each 64-bit register pair of the three 128-bit loads holds the same quantity of
+// BOTH children and one packed FFMA2 (fma.rn.f32x2, new on sm_100) does the work of two FFMA (node_visit_pair below).
+template <bool PAD, bool OFFS = false, bool PAIR = false> __device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem)
 {
     SceneView S;
     S.g_nodes = D.nodes; S.g_prims = D.prims; S.g_prim_k = D.prim_k; S.g_mats = D.mats; S.images = D.images;
@@ -109,6 +112,19 @@ template <bool PAD, bool OFFS = false> __device__ __forceinline__ SceneView stag
     float4* sp = sn + (PAD ? CRT_SMEM_NODE_F4 : 4) * (size_t)D.smem_nodes;
     float4* sm = sp + D.smem_prims;
     const int tid = threadIdx.x, nt = blockDim.x;
+    if (PAIR) {
+        const float* src = reinterpret_cast<const float*>(D.nodes);
+        float* dst = reinterpret_cast<float*>(sn);
+        for (int i = tid; i < 16 * D.smem_nodes; i += nt) {
+            const int node = i >> 4, k = i & 15;
+            float v = __ldg(src + i);
+            int at = k;
+            if (k < 12) at = 2 * (k % 6) + k / 6; // child c, quantity j (centre xyz, half xyz) -> word 2 j + c
+            else if (k < 14) { const int c = __float_as_int(v); v = __int_as_float(c >= 0 ? c * (16 * CRT_SMEM_NODE_F4) : c); }
+            dst[4 * CRT_SMEM_NODE_F4 * node + at] = v;
+        }
+    }
+    else
     for (int i = tid; i < 4 * D.smem_nodes; i += nt) {
         float4 v = __ldg(D.nodes + i);
         if (OFFS && (i & 3) == 3) { // {child 0, child 1, -, -}: inner children (>= 0) are renamed, leaf codes (< 0) stay
@@ -258,6 +274,62 @@ __device__ __forceinline__ void slab2(const TravRay& r, float4 w0, float4 w1, fl
     tf1 = fminf(fminf(fmaf(w2.y, r.aid.x, mx1), fmaf(w2.z, r.aid.y, my1)), fminf(fmaf(w2.w, r.aid.z, mz1), t_hit));
 }
 
+// d = a * {s, s} + c on both halves of a register pair: one FFMA2 (fma.rn.f32x2). Each half is the IEEE fused multiply-add
+// fmaf() computes, so the paired visit produces the bits of slab2().
+__device__ __forceinline__ float2 fma2s(float2 a, float s, float2 c)
+{
+#ifdef CRT_HOST_SIM
+    return make_float2(fmaf(a.x, s, c.x), fmaf(a.y, s, c.y));
+#else
+    float2 d;
+    asm("{.reg .b64 ra, rb, rc, rd; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%4}; mov.b64 rc, {%5,%6}; fma.rn.f32x2 rd, ra, rb, rc; mov.b64 {%0,%1}, rd;}"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(s), "f"(c.x), "f"(c.y));
+    return d;
+#endif
+}
+// d = a * {s, s} + {t, t}
+__device__ __forceinline__ float2 fma2ss(float2 a, float s, float t)
+{
+#ifdef CRT_HOST_SIM
+    return make_float2(fmaf(a.x, s, t), fmaf(a.y, s, t));
+#else
+    float2 d;
+    asm("{.reg .b64 ra, rb, rc, rd; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%4}; mov.b64 rc, {%5,%5}; fma.rn.f32x2 rd, ra, rb, rc; mov.b64 {%0,%1}, rd;}"
+        : "=f"(d.x), "=f"(d.y) : "f"(a.x), "f"(a.y), "f"(s), "f"(t));
+    return d;
+#endif
+}
+
+// The inner-node visit of the kernels that hold the WHOLE tree in shared memory in the PAIR layout (stage_scene<true, true, true>),
+// executed by every lane of the warp like node_step_all. `cur` >= 0 is the byte offset of a staged node; the stack holds a
+// CRT_TRAV_DONE sentinel below the first entry, so a pop needs no emptiness test (sp >= 1 while a ray is in flight).
+// Per visit: 1 VIMNMX + 4 LDS + 9 FFMA2 + 8 min/max + 3 FSETP + the select / push / pop, no branch: ~40 instructions against
+// the 55 of node_step_all (profiles/r01_l_pipe_c2_spp128.txt).
+__device__ __forceinline__ void node_visit_pair(const SceneView& S, const TravRay& r, float t_min, float t_hit, int& cur, int& sp, int* stack)
+{
+    const bool at = cur >= 0;
+    const float4* p = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(S.s_nodes) + max(cur, 0));
+    const float4 w0 = p[0], w1 = p[1], w2 = p[2];
+    const int2 ch = *reinterpret_cast<const int2*>(p + 3);
+    const float2 mx = fma2ss(make_float2(w0.x, w0.y), r.id.x, -r.ood.x);
+    const float2 my = fma2ss(make_float2(w0.z, w0.w), r.id.y, -r.ood.y);
+    const float2 mz = fma2ss(make_float2(w1.x, w1.y), r.id.z, -r.ood.z);
+    const float2 nx = fma2s(make_float2(-w1.z, -w1.w), r.aid.x, mx), fx = fma2s(make_float2(w1.z, w1.w), r.aid.x, mx);
+    const float2 ny = fma2s(make_float2(-w2.x, -w2.y), r.aid.y, my), fy = fma2s(make_float2(w2.x, w2.y), r.aid.y, my);
+    const float2 nz = fma2s(make_float2(-w2.z, -w2.w), r.aid.z, mz), fz = fma2s(make_float2(w2.z, w2.w), r.aid.z, mz);
+    const float tn0 = fmaxf(fmaxf(nx.x, ny.x), fmaxf(nz.x, t_min)), tf0 = fminf(fminf(fx.x, fy.x), fminf(fz.x, t_hit));
+    const float tn1 = fmaxf(fmaxf(nx.y, ny.y), fmaxf(nz.y, t_min)), tf1 = fminf(fminf(fx.y, fy.y), fminf(fz.y, t_hit));
+    const bool h0 = at && tn0 <= tf0, h1 = at && tn1 <= tf1;
+    const bool second_first = h1 && (tn1 < tn0 || !h0); // child 1 is the nearer hit child, or the only one
+    const int first = second_first ? ch.y : ch.x, other = second_first ? ch.x : ch.y;
+    const bool push = h0 && h1, pop = at && !(h0 || h1);
+    if (push) stack[sp] = other;
+    int next = first;
+    if (pop) next = stack[sp - 1];
+    sp += (push ? 1 : 0) - (pop ? 1 : 0);
+    if (at) cur = next;
+}
+
 // One inner-node visit: slab-test both child boxes against (t_min, t_hit), descend into the nearer hit child and push the
 // other. `cur` >= 0 on entry; on exit it is the next node (>= 0), a leaf (~code, < 0) or CRT_TRAV_DONE.
 template <bool EXACT, bool SMEM_ALL, bool PAD = false>
@@ -322,7 +394,8 @@ __device__ __forceinline__ void node_step_all(const SceneView& S, const TravRay&
 }
 
 // One leaf visit: test the primitive, shrink the hit distance, pop. `cur` < 0 and != CRT_TRAV_DONE on entry.
-template <bool EXACT, bool SMEM_ALL>
+// SENT: the stack has a CRT_TRAV_DONE sentinel at its bottom (node_visit_pair), so the pop is unconditional.
+template <bool EXACT, bool SMEM_ALL, bool SENT = false>
 __device__ __forceinline__ void leaf_step(const SceneView& S, const TravRay& r, float t_min, Hit& h, int& cur, int& sp, const int* stack)
 {
     const int code = ~cur;
@@ -331,7 +404,8 @@ __device__ __forceinline__ void leaf_step(const SceneView& S, const TravRay& r, 
         h.t = t;
         h.leaf = code;
     }
-    cur = sp ? stack[--sp] : CRT_TRAV_DONE;
+    if (SENT) cur = stack[--sp];
+    else cur = sp ? stack[--sp] : CRT_TRAV_DONE;
 }
 
 // Start of a closest-hit query: the primitives peeled off the top of the tree (DevScene::top_code) are tested here, without
