@@ -1127,7 +1127,7 @@ static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaS
     CRT_PIPE_EXP(1024, true, 1); CRT_PIPE_EXP(1024, false, 1); CRT_PIPE_EXP(2048, true, 1); CRT_PIPE_EXP(2048, false, 1);
     CRT_PIPE_EXP(1024, true, 4); CRT_PIPE_EXP(1024, false, 4); CRT_PIPE_EXP(2048, true, 4); CRT_PIPE_EXP(2048, false, 4);
     CRT_PIPE_EXP(2048, true, 2); CRT_PIPE_EXP(2048, true, 3); CRT_PIPE_EXP(2048, true, 6);
-    CRT_PIPE_EXP(2048, true, 8); CRT_PIPE_EXP(2048, true, 9); CRT_PIPE_EXP(2048, true, 12);
+    CRT_PIPE_EXP(2048, true, 8); CRT_PIPE_EXP(2048, true, 12);
 #undef CRT_PIPE_EXP
 #define CRT_PIPE_CASE(N) case N: return all ? launch_pipe<N, true>(W, grid, smem, st) : launch_pipe<N, false>(W, grid, smem, st)
     switch (W.n_slots) {
@@ -1145,8 +1145,8 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
     if (P == 0 || A.spp_count == 0) return CRT_OK;
     // shared memory: [scene prefix][pool of N slots: 56 B of path state + 7 16-bit ring entries]
     const long per_slot = 3 * 16 + 8 + 2 * PQ_COUNT;
-    const long node_b = 16 * CRT_SMEM_NODE_F4;
     const long budget = (ctx->smem_budget_override >= 0 ? std::min<long>(ctx->smem_budget_override, ctx->smem_optin) : (long)ctx->smem_optin) - 1024;
+    const long node_b = 16 * CRT_SMEM_NODE_F4;
     const long full = (long)A.scene.n_nodes * node_b + (long)A.scene.n_prims * 48;
     int n_slots = ctx->pipe_slots > 0 ? ctx->pipe_slots : (full + 2048 * per_slot <= budget ? 2048 : 1024);
     while (n_slots & (n_slots - 1)) n_slots &= n_slots - 1; // power of two
@@ -1262,6 +1262,7 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
     A.spp_begin = p->spp_begin; A.spp_count = p->spp_count; A.spp_stride = p->spp_stride ? p->spp_stride : 1;
     A.max_depth = p->max_depth;
     A.seed_lo = (uint32_t)p->seed; A.seed_hi = (uint32_t)(p->seed >> 32);
+    crt_philox_round_keys(A.seed_lo, A.seed_hi, A.philox_keys);
     A.jitter = p->jitter;
     const bool exact = (p->flags & CRT_FLAG_EXACT_MATH) != 0, count = (p->flags & CRT_FLAG_COUNT_TESTS) != 0;
 

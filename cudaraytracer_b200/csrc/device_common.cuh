@@ -81,6 +81,9 @@ struct RenderArgs
     uint32_t cover_w, cover_h;    // pixels actually rendered (== width/height unless CRT_FLAG_TRUNCATED_GRID)
     uint32_t spp_begin, spp_count, spp_stride, max_depth;
     uint32_t seed_lo, seed_hi;
+    // the ten Philox round keys of this seed, {k0 + r W0, k1 + r W1}: filled on the host (crt_philox_round_keys) so that the
+    // device reads each of them as a constant-bank operand instead of adding a 32-bit immediate per round and word
+    uint32_t philox_keys[20];
     int jitter;
     // row-tile sharding (crt_render_params::row_tiles): this launch renders only the rows of slabs tile_rank, tile_rank +
     // tile_world, ... (slabs of tile_rows rows); cover_h then counts the LOCAL rows. tile_world <= 1: the whole frame.
@@ -125,6 +128,23 @@ __host__ __device__ __forceinline__ uint4 crt_philox4x32_10(uint4 c, uint32_t k0
         c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
         k0 += CRT_PHILOX_W0;
         k1 += CRT_PHILOX_W1;
+    }
+    return c;
+}
+
+__host__ __device__ __forceinline__ void crt_philox_round_keys(uint32_t k0, uint32_t k1, uint32_t* keys)
+{
+    for (int r = 0; r < 10; r++) { keys[2 * r] = k0 + (uint32_t)r * CRT_PHILOX_W0; keys[2 * r + 1] = k1 + (uint32_t)r * CRT_PHILOX_W1; }
+}
+// the same function with the round keys precomputed
+__host__ __device__ __forceinline__ uint4 crt_philox4x32_10k(uint4 c, const uint32_t* keys)
+{
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        uint32_t hi0, lo0, hi1, lo1;
+        crt_mulhilo(CRT_PHILOX_M0, c.x, hi0, lo0);
+        crt_mulhilo(CRT_PHILOX_M1, c.z, hi1, lo1);
+        c = make_uint4(hi1 ^ c.y ^ keys[2 * r], lo1, hi0 ^ c.w ^ keys[2 * r + 1], lo0);
     }
     return c;
 }

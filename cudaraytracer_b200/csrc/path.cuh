@@ -10,7 +10,7 @@
 template <bool EXACT>
 __device__ __forceinline__ void gen_primary(const RenderArgs& A, int x, int y, uint32_t pixel, uint32_t sample, float3& o, float3& d)
 {
-    uint4 r = crt_philox4x32_10(make_uint4(pixel, sample, 0u, CRT_STREAM_CAMERA), A.seed_lo, A.seed_hi);
+    uint4 r = crt_philox4x32_10k(make_uint4(pixel, sample, 0u, CRT_STREAM_CAMERA), A.philox_keys);
     float j1 = 0.5f, j2 = 0.5f;
     if (A.jitter == CRT_JITTER_RANDOM) { j1 = crt_uniform(r.x); j2 = crt_uniform(r.y); }
     camera_ray<EXACT>(A.cam, A.width, A.height, x, y, j1, j2, o, d);
@@ -27,7 +27,7 @@ __device__ __forceinline__ bool scatter_step(const RenderArgs& A, const SceneVie
         add = thr * background(A.cam, d);
         return false;
     }
-    uint4 r = crt_philox4x32_10(make_uint4(pixel, sample, bounce, CRT_STREAM_SCATTER), A.seed_lo, A.seed_hi);
+    uint4 r = crt_philox4x32_10k(make_uint4(pixel, sample, bounce, CRT_STREAM_SCATTER), A.philox_keys);
     float4 xi = make_float4(crt_uniform(r.x), crt_uniform(r.y), crt_uniform(r.z), crt_uniform(r.w));
     bool alive = shade_hit<SMEM_ALL>(S, h, o, d, thr, add, xi);
     bounce++;

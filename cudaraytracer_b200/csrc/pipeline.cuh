@@ -45,6 +45,7 @@ struct PipeCtl
     unsigned int head[PQ_COUNT + 1];
     unsigned int tail[PQ_COUNT + 1];
     int live; // slots not yet retired; the CTA exits at 0
+    unsigned int n_rays, n_paths; // this CTA's ray / path counts: one shared atomic per batch instead of two registers per thread
 };
 
 struct PipePool
@@ -166,8 +167,7 @@ template <bool SMEM_ALL> __device__ __forceinline__ uint32_t pipe_mat_bits(const
 // One batch of queue q (n <= 32 slots, lane < n holds `slot`): generate, or shade one bounce.
 template <bool SMEM_ALL>
 __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S, const PipePool& P, PipeCtl* ctl, int q, int n, int slot,
-                                           unsigned lane, unsigned lt, unsigned int& shard_cursor, bool& exhausted, unsigned& n_rays,
-                                           unsigned& n_paths)
+                                           unsigned lane, unsigned lt, unsigned int& shard_cursor, bool& exhausted)
 {
     const bool mine = (int)lane < n;
     if (q == PQ_GEN) {
@@ -187,17 +187,20 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
                 P.b[slot] = make_float4(d.y, d.z, 0.f, 0.f);
                 P.c[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(0u));
                 P.px[slot] = make_uint2(pixel, sample);
-                n_paths++;
                 started = true;
             }
             done += g;
         }
-        if (lane == 0 && done < n) atomicSub(&ctl->live, n - done); // no work left: these slots retire
+        if (lane == 0) {
+            if (done > 0) atomicAdd(&ctl->n_paths, (unsigned)done);
+            if (done < n) atomicSub(&ctl->live, n - done); // no work left: these slots retire
+        }
         pipe_release();
         pipe_push(P, ctl, PQ_EXT, started, slot, lt);
         return;
     }
     bool alive = false, ended = false;
+    if (lane == 0) atomicAdd(&ctl->n_rays, (unsigned)n);
     if (mine) {
         const float4 a0 = P.a[slot], b0 = P.b[slot], c0 = P.c[slot];
         const uint2 ps = P.px[slot];
@@ -206,7 +209,6 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
         Hit h;
         h.t = b0.z;
         h.leaf = __float_as_int(b0.w);
-        n_rays++;
         alive = scatter_step<SMEM_ALL>(A.R, S, h, ps.x, ps.y, bounce, o, d, thr, add);
         if (alive) {
             P.a[slot] = make_float4(o.x, o.y, o.z, d.x);
@@ -258,7 +260,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
     const SceneView S = stage_scene<true, OFFS, PAIR>(A.R.scene, smem + (3 * P.n + P.n / 2) + (PQ_COUNT * P.n) / 8);
     for (int i = threadIdx.x; i < PQ_COUNT * P.n; i += PIPE_THREADS) P.ring[i] = (unsigned short)(i >= PQ_GEN * P.n ? i - PQ_GEN * P.n : PIPE_EMPTY);
     if (threadIdx.x <= PQ_COUNT) { ctl.head[threadIdx.x] = 0u; ctl.tail[threadIdx.x] = threadIdx.x == PQ_GEN ? (unsigned int)P.n : 0u; }
-    if (threadIdx.x == 0) ctl.live = P.n; // every slot starts in the GEN queue
+    if (threadIdx.x == 0) { ctl.live = P.n; ctl.n_rays = 0u; ctl.n_paths = 0u; } // every slot starts in the GEN queue
     __syncthreads();
 
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, lt = (1u << lane) - 1u;
@@ -270,18 +272,18 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
     h.leaf = -1;
     int stack[CRT_STACK_SIZE];
     if (PAIR) stack[0] = CRT_TRAV_DONE; // sentinel: a pop of the empty stack yields "finished" (node_visit_pair)
-    unsigned n_rays = 0, n_paths = 0;
     unsigned int shard_cursor = (blockIdx.x * PIPE_WARPS + warp) & (WF_SHARDS - 1);
     bool exhausted = false;
 
     bool refill_short = true;
     int ext_left = 0;
-    for (unsigned it = 0; *(volatile int*)&ctl.live > 0; it++) {
+    constexpr bool LEAN = PAIR; // every iteration looks at the queues (the cadence made no difference: profiles/r02_c_sweep.txt)
+    for (unsigned it = 0; *(volatile int*)&ctl.live > 0; it += LEAN ? 0u : 1u) {
         const unsigned act0 = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
         bool worked = false;
         // ---- shade / generate duty: lanes 1..6 each look at one queue. With 32 warps looking, every A.check_every-th
         //      iteration of a warp is enough to keep the class queues short; a warp that could not refill looks at once ----
-        if (refill_short || ext_left < A.ext_low || (it & (unsigned)A.check_mask) == 0u) {
+        if (LEAN || refill_short || ext_left < A.ext_low || (it & (unsigned)A.check_mask) == 0u) {
             int sz = 0;
             if (lane < PQ_COUNT) sz = (int)(*(volatile unsigned int*)&ctl.tail[lane] - *(volatile unsigned int*)&ctl.head[lane]);
             const unsigned full_q = __ballot_sync(0xffffffffu, lane >= 1u && sz >= 32);
@@ -301,7 +303,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
                 int s2 = -1;
                 const int n = pipe_pop(P, &ctl, q, 32, (int)lane, true, s2);
                 if (n > 0) {
-                    pipe_batch<SMEM_ALL>(A, S, P, &ctl, q, n, s2, lane, lt, shard_cursor, exhausted, n_rays, n_paths);
+                    pipe_batch<SMEM_ALL>(A, S, P, &ctl, q, n, s2, lane, lt, shard_cursor, exhausted);
                     worked = true;
                     // Lanes in mid-traversal kept only {slot, cur, sp, t, leaf} across the batch: rebuild the per-ray constants.
                     const int si = max(slot, 0);
@@ -317,7 +319,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         if (m != 0u) {
             int s2 = -1;
             const int rank = __popc(m & lt);
-            const int n = pipe_pop(P, &ctl, PQ_EXT, __popc(m), rank, idle, s2, &ext_left);
+            const int n = pipe_pop(P, &ctl, PQ_EXT, __popc(m), rank, idle, s2, LEAN ? nullptr : &ext_left);
             if (idle && rank < n) {
                 slot = s2;
                 const float4 a0 = P.a[slot], b0 = P.b[slot];
@@ -337,6 +339,16 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         // ---- traverse: until fewer than THRESH lanes are busy (a refill is due) or it is time to look at the queues ----
         const int leave_below = refill_short ? 1 : A.thresh; // EXT ran dry: leaving early would only spin
         int rounds_left = A.max_rounds;
+        if (LEAN) {
+            for (; rounds_left > 0; rounds_left--) {
+                node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
+                node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
+                node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
+                if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL, true>(S, r, t_min, h, cur, sp, stack);
+                if (__popc(__ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE)) < leave_below) break;
+            }
+        }
+        else
         while (true) { // two node visits per vote
             if (PAIR) {
                 node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
@@ -370,6 +382,11 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
             if (fin) slot = -1;
         }
     }
-    // ray / path counters: block-aggregated into one of the counter shards
-    flush_counters(A.stat, n_paths, n_rays, 0u, 0u, false);
+    // ray / path counters of the CTA into one of the counter shards
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        DevCounters* c = A.stat + (blockIdx.x & (CRT_COUNTER_SHARDS - 1));
+        atomicAdd(&c->paths, (unsigned long long)ctl.n_paths);
+        atomicAdd(&c->rays, (unsigned long long)ctl.n_rays);
+    }
 }

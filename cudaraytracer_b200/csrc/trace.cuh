@@ -95,6 +95,8 @@ template <bool SMEM_ALL> __device__ __forceinline__ void load_mat(const SceneVie
     }
 }
 
+#define CRT_TRAV_DONE ((int)0x80000000)
+
 // Stages the first smem_* entries of each table into dynamic shared memory. Call from every thread, then __syncthreads().
 // OFFS (experimental, needs PAD and the whole tree in shared memory): inner-child references of the staged nodes, and the
 // entry node, become BYTE OFFSETS into the staged table (index * 80), so a visit needs no address arithmetic at all.
@@ -140,8 +142,6 @@ template <bool PAD, bool OFFS = false, bool PAIR = false> __device__ __forceinli
     S.s_nodes = sn; S.s_prims = sp; S.s_mats = sm;
     return S;
 }
-
-#define CRT_TRAV_DONE ((int)0x80000000)
 
 struct Hit
 {

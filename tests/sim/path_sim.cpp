@@ -129,6 +129,7 @@ int main(int argc, char** argv)
     A.width = W; A.height = H; A.cover_w = W; A.cover_h = H;
     A.spp_begin = 0; A.spp_count = spp; A.spp_stride = 1; A.max_depth = depth;
     A.seed_lo = 1984u; A.seed_hi = 0u;
+    crt_philox_round_keys(A.seed_lo, A.seed_hi, A.philox_keys);
     A.jitter = CRT_JITTER_RANDOM;
 
     std::vector<float> mean((size_t)W * H * 3, 0.f);

@@ -299,7 +299,7 @@ def test_experimental_round_schedule_is_bit_identical(monkeypatch, kind, hint):
     W, H = 161, 91
     cam = s.default_camera(W, H)
     out = []
-    for sched in ("0", "1", "2", "3", "4", "6", "8", "9", "12"):
+    for sched in ("0", "4", "8", "12"):
         monkeypatch.setenv("CRT_PIPE_SCHED", sched)
         r = Renderer(0)
         _setup(r, s, cam, W, H)

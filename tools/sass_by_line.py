@@ -76,6 +76,16 @@ print("-- by kernel-body line (outermost frame): share of instructions, avg acti
 ts = sum(samples)
 for loc, e in outer.most_common(top):
     print(f"  {loc[0]}:{loc[1]:<5d} {100.0*e/total:6.2f}%  {outer_thr[loc]/max(e,1):5.1f} thr  {100.0*outer_smp[loc]/ts:6.2f}% smp")
+if len(sys.argv) > 4:  # breakdown of one kernel-body line by the second frame (the function called there) and by innermost line
+    want = int(sys.argv[4])
+    sub = collections.Counter(); sub_thr = collections.Counter()
+    for loc, e, t in zip(inst_loc, execs, thr):
+        if loc and loc[-1][1] == want:
+            key = (loc[-2] if len(loc) > 1 else loc[-1], loc[0])
+            sub[key] += e; sub_thr[key] += t
+    print(f"-- inside kernel-body line {want}: (frame below it, innermost line): share of ALL instructions, avg threads")
+    for key, e in sub.most_common(top):
+        print(f"  {key[0][0]}:{key[0][1]:<5d} {key[1][0]}:{key[1][1]:<5d} {100.0*e/total:6.2f}%  {sub_thr[key]/max(e,1):5.1f} thr")
 print("-- by innermost line")
 for loc, e in inner.most_common(top):
     print(f"  {loc[0]}:{loc[1]:<5d} {100.0*e/total:6.2f}%")
