@@ -572,7 +572,20 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
 }
 
 // Builds the BVH of `sd` with the builder the context is set to and makes it the scene in use.
+static crt_status build_and_upload_tree(crt_context* ctx, const crt_scene_desc* sd, bool keep_images, const char* who);
 static crt_status build_and_upload(crt_context* ctx, const crt_scene_desc* sd, bool keep_images, const char* who)
+{
+    crt_status st = build_and_upload_tree(ctx, sd, keep_images, who);
+    if (st != CRT_OK) return st;
+    // scenes without rectangles run leaf visits without the type dispatch (trace.cuh leaf_step SPH)
+    int only = 1;
+    for (uint64_t i = 0; i < sd->n_hittables && only; i++)
+        if (sd->hittables[i].active && sd->hittables[i].type != CRT_SPHERE) only = 0;
+    ctx->scene.spheres_only = only;
+    return CRT_OK;
+}
+
+static crt_status build_and_upload_tree(crt_context* ctx, const crt_scene_desc* sd, bool keep_images, const char* who)
 {
     uint64_t n_active_bound = sd ? sd->n_hittables : 0;
     const bool gpu = ctx->bvh_builder == CRT_BUILDER_GPU_LBVH || ctx->bvh_builder == CRT_BUILDER_GPU_PLOC ||
@@ -681,6 +694,14 @@ crt_status crt_scene_commit(crt_context* ctx, int force_rebuild, int* out_rebuil
     }
     // refit path: scatter the edited records, then recompute every box bottom-up on the GPU
     auto t0 = std::chrono::steady_clock::now();
+    // The rebuild path validates through crt_pack_scene. Here the records are packed directly, and a hittable may have been
+    // re-pointed at a material that no active hittable used at upload, so nothing has looked at its texture chain yet: check
+    // before anything is touched (on failure the edits stay pending; fix the material and commit again).
+    for (uint64_t idx : ctx->dirty_list) {
+        const crt_hittable& h = ctx->host.hittables[idx];
+        std::string merr;
+        if (h.active && !crt_check_material(&d, h.material, &merr)) return crt_set_error(ctx, CRT_ERR_INVALID, ("crt_scene_commit: " + merr).c_str());
+    }
     std::vector<EditRec> recs;
     recs.reserve(ctx->dirty_list.size());
     float extent = 0.f;
@@ -1122,12 +1143,13 @@ static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaS
     if (!all || W.n_slots != 2048) sched &= ~(2 | 8);
     if (sched & 8) sched &= ~2;
     if (sched & 4) sched &= ~1;
-    sched &= 15;
+    if ((sched & 8) && W.R.scene.spheres_only) sched |= 16;
+    sched &= 31;
 #define CRT_PIPE_EXP(N, ALL, S) if (W.n_slots == N && all == ALL && sched == S) return launch_pipe<N, ALL, S>(W, grid, smem, st)
     CRT_PIPE_EXP(1024, true, 1); CRT_PIPE_EXP(1024, false, 1); CRT_PIPE_EXP(2048, true, 1); CRT_PIPE_EXP(2048, false, 1);
     CRT_PIPE_EXP(1024, true, 4); CRT_PIPE_EXP(1024, false, 4); CRT_PIPE_EXP(2048, true, 4); CRT_PIPE_EXP(2048, false, 4);
     CRT_PIPE_EXP(2048, true, 2); CRT_PIPE_EXP(2048, true, 3); CRT_PIPE_EXP(2048, true, 6);
-    CRT_PIPE_EXP(2048, true, 8); CRT_PIPE_EXP(2048, true, 12);
+    CRT_PIPE_EXP(2048, true, 8); CRT_PIPE_EXP(2048, true, 12); CRT_PIPE_EXP(2048, true, 28);
 #undef CRT_PIPE_EXP
 #define CRT_PIPE_CASE(N) case N: return all ? launch_pipe<N, true>(W, grid, smem, st) : launch_pipe<N, false>(W, grid, smem, st)
     switch (W.n_slots) {

@@ -68,6 +68,7 @@ bool crt_pack_scene(const crt_scene_desc* scene, CrtPackedScene* out, std::strin
 // One primitive / one material record in the packed layout (also used by the edit path).
 bool crt_prepare_gpu_build(const crt_scene_desc* scene, std::vector<uint32_t>* active, float cmin[3], float cmax[3], float blo[3],
                            float bhi[3], float* abs_pad, std::string* err);
+bool crt_check_material(const crt_scene_desc* scene, int64_t index, std::string* err);
 void crt_pack_prim(const crt_hittable& h, float prim[4], float* k);
 void crt_pack_material(const crt_scene_desc* scene, const crt_material& m, float record[8]);
 

@@ -30,6 +30,7 @@ struct DevScene
     // starts, and the traversal starts at `entry`, the first node below the chain.
     int entry, n_top;
     int top_code[CRT_MAX_TOP];
+    int spheres_only; // no active rectangle: leaf visits skip the primitive-type dispatch
 };
 
 struct DevCamera

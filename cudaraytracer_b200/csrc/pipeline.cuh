@@ -277,6 +277,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
 
     bool refill_short = true;
     int ext_left = 0;
+    constexpr bool SPH = PAIR && (SCHED & 16) != 0; // the scene holds only spheres (DevScene::spheres_only, chosen by the host)
     constexpr bool LEAN = PAIR; // every iteration looks at the queues (the cadence made no difference: profiles/r02_c_sweep.txt)
     for (unsigned it = 0; *(volatile int*)&ctl.live > 0; it += LEAN ? 0u : 1u) {
         const unsigned act0 = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
@@ -344,7 +345,10 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
                 node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
                 node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
                 node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
-                if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL, true>(S, r, t_min, h, cur, sp, stack);
+                if (cur < 0 && cur != CRT_TRAV_DONE) {
+                    if (SPH) leaf_step_sphere(S, r, t_min, h, cur, sp, stack);
+                    else leaf_step<false, SMEM_ALL, true>(S, r, t_min, h, cur, sp, stack);
+                }
                 if (__popc(__ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE)) < leave_below) break;
             }
         }

@@ -323,6 +323,37 @@ int crt_peel_top(const CrtPackedNode* nodes, size_t n_nodes, uint64_t n_prims, i
     return n_top;
 }
 
+// Validation of one material and of the texture / image it references. Shared by the build paths (through check_hittable)
+// and by the refit path of crt_scene_commit, which packs the material records of edited hittables without a rebuild.
+bool crt_check_material(const crt_scene_desc* sd, int64_t index, std::string* err)
+{
+    if (index < 0 || (uint64_t)index >= sd->n_materials) {
+        *err = "scene: material index " + std::to_string(index) + " out of range";
+        return false;
+    }
+    const crt_material& m = sd->materials[index];
+    if (m.type < CRT_LAMBERTIAN || m.type > CRT_DIFFUSELIGHT) {
+        *err = "scene: material " + std::to_string(index) + " has unknown type";
+        return false;
+    }
+    if (m.type != CRT_DIELECTRIC) {
+        if (m.texture < 0 || (uint64_t)m.texture >= sd->n_textures) {
+            *err = "scene: material " + std::to_string(index) + " has texture index out of range";
+            return false;
+        }
+        const crt_texture& t = sd->textures[m.texture];
+        if (t.type < CRT_CONSTANT || t.type > CRT_IMAGE) {
+            *err = "scene: texture " + std::to_string(m.texture) + " has unknown type";
+            return false;
+        }
+        if (t.type == CRT_IMAGE && t.image >= 0 && (uint64_t)t.image >= sd->n_images) {
+            *err = "scene: texture " + std::to_string(m.texture) + " has image index out of range";
+            return false;
+        }
+    }
+    return true;
+}
+
 // Validation of one ACTIVE hittable and of everything it references (shared by the host and the GPU build paths).
 static bool check_hittable(const crt_scene_desc* sd, uint64_t i, std::string* err)
 {
@@ -341,26 +372,7 @@ static bool check_hittable(const crt_scene_desc* sd, uint64_t i, std::string* er
         *err = "scene: hittable " + std::to_string(i) + " has a non-finite coordinate or size (deactivate it instead)";
         return false;
     }
-    const crt_material& m = sd->materials[h.material];
-    if (m.type < CRT_LAMBERTIAN || m.type > CRT_DIFFUSELIGHT) {
-        *err = "scene: material " + std::to_string(h.material) + " has unknown type";
-        return false;
-    }
-    if (m.type != CRT_DIELECTRIC) {
-        if (m.texture < 0 || (uint64_t)m.texture >= sd->n_textures) {
-            *err = "scene: material " + std::to_string(h.material) + " has texture index out of range";
-            return false;
-        }
-        const crt_texture& t = sd->textures[m.texture];
-        if (t.type < CRT_CONSTANT || t.type > CRT_IMAGE) {
-            *err = "scene: texture " + std::to_string(m.texture) + " has unknown type";
-            return false;
-        }
-        if (t.type == CRT_IMAGE && t.image >= 0 && (uint64_t)t.image >= sd->n_images) {
-            *err = "scene: texture " + std::to_string(m.texture) + " has image index out of range";
-            return false;
-        }
-    }
+    if (!crt_check_material(sd, h.material, err)) return false;
     return true;
 }
 

@@ -408,6 +408,27 @@ __device__ __forceinline__ void leaf_step(const SceneView& S, const TravRay& r, 
     else cur = sp ? stack[--sp] : CRT_TRAV_DONE;
 }
 
+// The leaf visit of a scene that holds only spheres, in shared memory, with the sentinel stack: no type dispatch, no branch
+// (the two roots are tried by selects). The arithmetic is sphere_test<false>'s, operation for operation.
+__device__ __forceinline__ void leaf_step_sphere(const SceneView& S, const TravRay& r, float t_min, Hit& h, int& cur, int& sp, const int* stack)
+{
+    const int code = ~cur;
+    const float4 sph = S.s_prims[code & CRT_LEAF_INDEX_MASK];
+    const float3 oc = r.o - f3(sph.x, sph.y, sph.z);
+    const float b = dot3(oc, r.d);
+    const float c = fmaf(-sph.w, sph.w, dot3(oc, oc));
+    const float disc = fmaf(-r.a, c, b * b);
+    const float sq = fast_sqrt(fmaxf(disc, 0.f)); // only used where disc > 0, where it is fast_sqrt(disc)
+    const float t1 = (-b - sq) * r.inv_a, t2 = (-b + sq) * r.inv_a;
+    const bool ok1 = t1 < h.t && t1 > t_min, ok2 = t2 < h.t && t2 > t_min;
+    const bool hit = disc > 0.f && (ok1 || ok2);
+    if (hit) {
+        h.t = ok1 ? t1 : t2;
+        h.leaf = code;
+    }
+    cur = stack[--sp];
+}
+
 // Start of a closest-hit query: the primitives peeled off the top of the tree (DevScene::top_code) are tested here, without
 // their boxes, and the descent starts below them. Returns the node to start at.
 template <bool EXACT, bool SMEM_ALL>
