@@ -82,8 +82,7 @@ struct crt_context
     DevCounters* d_counters = nullptr; // CRT_COUNTER_SHARDS entries
     WfShard* d_shards = nullptr;       // work counters of the pipelined megakernel
     int pipe_thresh = 0, pipe_rounds = 0, // 0 = chosen per scene (render_pipeline)
-         pipe_slots = 0, pipe_check = 4, pipe_ext_low = 256, // CRT_PIPE_THRESH / _ROUNDS / _SLOTS / _CHECK
-         pipe_sched = 0; // CRT_PIPE_SCHED: bits selecting the experimental builds of pipeline.cuh (0 = the default kernel)
+         pipe_slots = 0; // CRT_PIPE_THRESH / _ROUNDS / _SLOTS
     uint64_t launches = 0;
 
     WavefrontState wf;
@@ -218,9 +217,6 @@ crt_status crt_context_create(int device, crt_context** out)
     if ((env = getenv("CRT_PIPE_THRESH")) && atoi(env) > 0) ctx->pipe_thresh = atoi(env);
     if ((env = getenv("CRT_PIPE_ROUNDS")) && atoi(env) > 0) ctx->pipe_rounds = atoi(env);
     if ((env = getenv("CRT_PIPE_SLOTS")) && atoi(env) > 0) ctx->pipe_slots = atoi(env);
-    if ((env = getenv("CRT_PIPE_CHECK")) && atoi(env) > 0) ctx->pipe_check = atoi(env);
-    if ((env = getenv("CRT_PIPE_EXT_LOW")) && atoi(env) >= 0) ctx->pipe_ext_low = atoi(env);
-    if ((env = getenv("CRT_PIPE_SCHED")) && atoi(env) >= 0) ctx->pipe_sched = atoi(env);
     if ((env = getenv("CRT_PIPE_PREFIX_KB")) && atoi(env) >= 0) ctx->pipe_prefix_bytes = 1024L * atoi(env);
     if ((env = getenv("CRT_BVH_BUILDER"))) {
         if (!strcmp(env, "host")) ctx->bvh_builder = CRT_BUILDER_HOST_SAH;
@@ -1119,39 +1115,26 @@ __global__ void k_pipe_init(WfShard* shards, uint32_t work_total)
     shards[i].end = b + per + (i < extra ? 1u : 0u);
 }
 
-template <int NSLOTS, bool ALL, int SCHED = 0> static cudaError_t launch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st)
+template <int NSLOTS, bool ALL, bool SPH> static cudaError_t launch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st)
 {
     static size_t configured[CRT_MAX_DEVICES] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     size_t& configured_smem = configured[dev & (CRT_MAX_DEVICES - 1)];
     if (smem > configured_smem) {
-        cudaError_t e = cudaFuncSetAttribute(k_render_pipe<NSLOTS, ALL, SCHED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(k_render_pipe<NSLOTS, ALL, SPH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured_smem = smem;
     }
-    k_render_pipe<NSLOTS, ALL, SCHED><<<grid, PIPE_THREADS, smem, st>>>(W);
+    k_render_pipe<NSLOTS, ALL, SPH><<<grid, PIPE_THREADS, smem, st>>>(W);
     return cudaGetLastError();
 }
 
 // the two pool sizes the planner picks have kernels with the size compiled in; anything else (CRT_PIPE_SLOTS) runs the generic one
-static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st, bool all, int sched)
+static cudaError_t dispatch_pipe(const PipeArgs& W, int grid, size_t smem, cudaStream_t st, bool all)
 {
-    // experimental builds (pipeline.cuh, CRT_PIPE_SCHED): only with a compiled-in pool size; bit 1 (byte offsets) needs the whole
-    // scene in shared memory and is built for the 2048-slot pool only; bit 2 (three node visits per round) overrides bit 0
-    if (W.n_slots != 1024 && W.n_slots != 2048) sched = 0;
-    if (!all || W.n_slots != 2048) sched &= ~(2 | 8);
-    if (sched & 8) sched &= ~2;
-    if (sched & 4) sched &= ~1;
-    if ((sched & 8) && W.R.scene.spheres_only) sched |= 16;
-    sched &= 31;
-#define CRT_PIPE_EXP(N, ALL, S) if (W.n_slots == N && all == ALL && sched == S) return launch_pipe<N, ALL, S>(W, grid, smem, st)
-    CRT_PIPE_EXP(1024, true, 1); CRT_PIPE_EXP(1024, false, 1); CRT_PIPE_EXP(2048, true, 1); CRT_PIPE_EXP(2048, false, 1);
-    CRT_PIPE_EXP(1024, true, 4); CRT_PIPE_EXP(1024, false, 4); CRT_PIPE_EXP(2048, true, 4); CRT_PIPE_EXP(2048, false, 4);
-    CRT_PIPE_EXP(2048, true, 2); CRT_PIPE_EXP(2048, true, 3); CRT_PIPE_EXP(2048, true, 6);
-    CRT_PIPE_EXP(2048, true, 8); CRT_PIPE_EXP(2048, true, 12); CRT_PIPE_EXP(2048, true, 28);
-#undef CRT_PIPE_EXP
-#define CRT_PIPE_CASE(N) case N: return all ? launch_pipe<N, true>(W, grid, smem, st) : launch_pipe<N, false>(W, grid, smem, st)
+    const bool sph = all && W.R.scene.spheres_only; // leaf visits without the type dispatch need the staged primitive table
+#define CRT_PIPE_CASE(N) case N: return !all ? launch_pipe<N, false, false>(W, grid, smem, st) : sph ? launch_pipe<N, true, true>(W, grid, smem, st) : launch_pipe<N, true, false>(W, grid, smem, st)
     switch (W.n_slots) {
         CRT_PIPE_CASE(1024);
         CRT_PIPE_CASE(2048);
@@ -1205,12 +1188,6 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
     // best at 12-14). Scene mostly behind L1: it is latency-bound, idle lanes cost nothing and every refill costs instructions,
     // so a warp runs its batch of rays to completion (THRESH 1: +9 % on the 1 M-sphere scene, +7 % on the 10 k glass/metal one).
     W.max_rounds = ctx->pipe_rounds > 0 ? ctx->pipe_rounds : (all ? 16 : 64);
-    {
-        int ce = std::max(ctx->pipe_check, 1); // rounded down to a power of two: the kernel tests it with a mask
-        while (ce & (ce - 1)) ce &= ce - 1;
-        W.check_mask = ce - 1;
-    }
-    W.ext_low = ctx->pipe_ext_low;
     const uint32_t stride = A.spp_stride ? A.spp_stride : 1u;
     const uint32_t spp_per_pass = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(A.spp_count, 0xF0000000ull / P));
     for (uint32_t done = 0; done < A.spp_count; done += spp_per_pass) {
@@ -1221,7 +1198,7 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
         W.R.spp_stride = stride;
         k_pipe_init<<<1, WF_SHARDS, 0, ctx->stream>>>(ctx->d_shards, (uint32_t)(P * spp));
         CU(cudaGetLastError());
-        CU(dispatch_pipe(W, ctx->sm_count, smem, ctx->stream, all, ctx->pipe_sched));
+        CU(dispatch_pipe(W, ctx->sm_count, smem, ctx->stream, all));
         const uint32_t npx = A.cover_w * A.cover_h;
         k_wf_add_count<<<(npx + 255) / 256, 256, 0, ctx->stream>>>(A.accum, A.width, A.cover_w, A.cover_h, (long long)spp, A.tile_rows, A.tile_rank, A.tile_world);
         CU(cudaGetLastError());

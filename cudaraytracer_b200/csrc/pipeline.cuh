@@ -34,8 +34,6 @@ struct PipeArgs
     int n_slots;             // N, a power of two
     int thresh;              // traversal leaves its loop when fewer lanes than this are busy (a refill is due)
     int max_rounds;          // traversal rounds between two refills at most
-    int check_mask;          // a warp looks for shade/generate work when (iteration & check_mask) == 0 (every 2^k-th) ...
-    int ext_low;             // ... and whenever the EXT queue held fewer rays than this at its last refill
 };
 
 // Control words of the queues (static shared memory). head/tail count reservations and never wrap in practice
@@ -94,8 +92,7 @@ __device__ __forceinline__ void pipe_release() { asm volatile("" ::: "memory"); 
 
 // Warp-level pop of up to `want` entries of queue q (never more than are reserved by producers). Returns the count n and
 // gives lanes with rank < n their slot id. One CAS per call; a lost race returns 0 and the caller simply tries again later.
-__device__ __forceinline__ int pipe_pop(const PipePool& P, PipeCtl* ctl, int q, int want, int rank, bool take, int& slot,
-                                        int* left = nullptr)
+__device__ __forceinline__ int pipe_pop(const PipePool& P, PipeCtl* ctl, int q, int want, int rank, bool take, int& slot)
 {
     unsigned int h = 0;
     int n = 0, avail = 0;
@@ -108,7 +105,6 @@ __device__ __forceinline__ int pipe_pop(const PipePool& P, PipeCtl* ctl, int q, 
     }
     h = __shfl_sync(0xffffffffu, h, 0);
     n = __shfl_sync(0xffffffffu, n, 0);
-    if (left) *left = __shfl_sync(0xffffffffu, avail, 0) - n; // entries the queue still held when this warp looked
     if (take && rank < n) {
         volatile unsigned short* e = pipe_entry(P, q, h + (unsigned int)rank);
         unsigned int v;
@@ -231,17 +227,12 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
 // NSLOTS > 0: the pool size is a compile-time constant. The pool sits at the START of dynamic shared memory, so every pool
 // and ring address is `constant + index`: with a run-time N behind the scene tables the compiler re-derived those addresses from
 // kernel parameters at each use (3.7 % of the executed instructions, profiles/r01_j). NSLOTS == 0 takes N from the arguments.
-// SCHED: visits of a traversal round. 0 = node, leaf, node, leaf (what runs by default). 1 = node, node, leaf: a lane that
-// reaches a leaf in the first node visit sits the second one out, and ONE leaf visit serves the leaves of both - fewer, fuller
-// leaf visits (they run at 10.7 of 32 lanes, profiles/r01_l_pipe_c2_by_line.txt). Experimental (CRT_PIPE_SCHED=1), not yet
-// measured; every lane walks its own tree in the same order either way, so the image is the same.
-//        2 (SMEM_ALL only) = 0 with the staged nodes' child references as byte offsets (trace.cuh stage_scene OFFS) and the
-//        descend / push / pop decision of a visit written without branches: 57 instructions per visit, all predicated (no
-//        convergence barrier), against 55 + ~5 of pop path behind two branches. 3 = 1 + 2.
-//        4 = node, node, node, leaf (6 = with 2): a ray makes 9.2 node visits and one leaf visit, and the lane model of
-//        tools/sched_model.py, fed with the real visit sequences, puts three node visits per leaf visit at the optimum
-//        (-12 % instructions in the rounds, against -5 % for two).
-template <int NSLOTS, bool SMEM_ALL, int SCHED = 0>
+// A traversal round is node, node, node, leaf: a lane that reaches a leaf sits the remaining node visits of the round out, and
+// ONE leaf visit serves them all (measured against node, leaf, node, leaf: +7 % on C2, +4 % on the 1 M-sphere scene; two or
+// four node visits per leaf visit are slower, profiles/r02_a_*).
+// SMEM_ALL (the whole scene is staged): the nodes take the PAIR layout and node_visit_pair (FFMA2, branch-free, sentinel stack).
+// SPH: the scene holds only spheres (DevScene::spheres_only, chosen by the host): leaf visits without the type dispatch.
+template <int NSLOTS, bool SMEM_ALL, bool SPH = false>
 __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_constant__ PipeArgs A)
 {
     extern __shared__ float4 smem[];
@@ -255,9 +246,8 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
     P.px = reinterpret_cast<uint2*>(smem + 3 * P.n);
     P.ring = reinterpret_cast<unsigned short*>(smem + 3 * P.n + P.n / 2);
     // 70 bytes per slot: N is a multiple of 64, so the scene tables that follow stay 16-byte aligned
-    constexpr bool PAIR = SMEM_ALL && (SCHED & 8) != 0;
-    constexpr bool OFFS = SMEM_ALL && (SCHED & 10) != 0;
-    const SceneView S = stage_scene<true, OFFS, PAIR>(A.R.scene, smem + (3 * P.n + P.n / 2) + (PQ_COUNT * P.n) / 8);
+    constexpr bool PAIR = SMEM_ALL;
+    const SceneView S = stage_scene<true, PAIR>(A.R.scene, smem + (3 * P.n + P.n / 2) + (PQ_COUNT * P.n) / 8);
     for (int i = threadIdx.x; i < PQ_COUNT * P.n; i += PIPE_THREADS) P.ring[i] = (unsigned short)(i >= PQ_GEN * P.n ? i - PQ_GEN * P.n : PIPE_EMPTY);
     if (threadIdx.x <= PQ_COUNT) { ctl.head[threadIdx.x] = 0u; ctl.tail[threadIdx.x] = threadIdx.x == PQ_GEN ? (unsigned int)P.n : 0u; }
     if (threadIdx.x == 0) { ctl.live = P.n; ctl.n_rays = 0u; ctl.n_paths = 0u; } // every slot starts in the GEN queue
@@ -276,15 +266,12 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
     bool exhausted = false;
 
     bool refill_short = true;
-    int ext_left = 0;
-    constexpr bool SPH = PAIR && (SCHED & 16) != 0; // the scene holds only spheres (DevScene::spheres_only, chosen by the host)
-    constexpr bool LEAN = PAIR; // every iteration looks at the queues (the cadence made no difference: profiles/r02_c_sweep.txt)
-    for (unsigned it = 0; *(volatile int*)&ctl.live > 0; it += LEAN ? 0u : 1u) {
+    while (*(volatile int*)&ctl.live > 0) {
         const unsigned act0 = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
         bool worked = false;
-        // ---- shade / generate duty: lanes 1..6 each look at one queue. With 32 warps looking, every A.check_every-th
-        //      iteration of a warp is enough to keep the class queues short; a warp that could not refill looks at once ----
-        if (LEAN || refill_short || ext_left < A.ext_low || (it & (unsigned)A.check_mask) == 0u) {
+        // ---- shade / generate duty: lanes 1..6 each look at one queue, every iteration (looking only every 2nd..16th one, or
+        //      only when the EXT queue ran low, made no difference: profiles/r02_c_sweep.txt) ----
+        {
             int sz = 0;
             if (lane < PQ_COUNT) sz = (int)(*(volatile unsigned int*)&ctl.tail[lane] - *(volatile unsigned int*)&ctl.head[lane]);
             const unsigned full_q = __ballot_sync(0xffffffffu, lane >= 1u && sz >= 32);
@@ -320,7 +307,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         if (m != 0u) {
             int s2 = -1;
             const int rank = __popc(m & lt);
-            const int n = pipe_pop(P, &ctl, PQ_EXT, __popc(m), rank, idle, s2, LEAN ? nullptr : &ext_left);
+            const int n = pipe_pop(P, &ctl, PQ_EXT, __popc(m), rank, idle, s2);
             if (idle && rank < n) {
                 slot = s2;
                 const float4 a0 = P.a[slot], b0 = P.b[slot];
@@ -332,16 +319,14 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
             }
             refill_short = n < __popc(m);
         }
-        unsigned act = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
-        if (act == 0u) {
+        if (__ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE) == 0u) {
             if (!worked) __nanosleep(100);
             continue;
         }
-        // ---- traverse: until fewer than THRESH lanes are busy (a refill is due) or it is time to look at the queues ----
+        // ---- traverse: until fewer than THRESH lanes are busy (a refill is due) ----
         const int leave_below = refill_short ? 1 : A.thresh; // EXT ran dry: leaving early would only spin
-        int rounds_left = A.max_rounds;
-        if (LEAN) {
-            for (; rounds_left > 0; rounds_left--) {
+        for (int rounds_left = A.max_rounds; rounds_left > 0; rounds_left--) {
+            if (PAIR) {
                 node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
                 node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
                 node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
@@ -349,31 +334,14 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
                     if (SPH) leaf_step_sphere(S, r, t_min, h, cur, sp, stack);
                     else leaf_step<false, SMEM_ALL, true>(S, r, t_min, h, cur, sp, stack);
                 }
-                if (__popc(__ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE)) < leave_below) break;
-            }
-        }
-        else
-        while (true) { // two node visits per vote
-            if (PAIR) {
-                node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
-                if ((SCHED & 5) == 0) {
-                    if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL, true>(S, r, t_min, h, cur, sp, stack);
-                }
-                node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
-                if (SCHED & 4) node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
-                if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL, true>(S, r, t_min, h, cur, sp, stack);
             }
             else {
-            node_step_all<SMEM_ALL, OFFS>(S, r, t_min, h.t, cur, sp, stack);
-            if ((SCHED & 5) == 0) {
+                node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
+                node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
+                node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
                 if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
             }
-            node_step_all<SMEM_ALL, OFFS>(S, r, t_min, h.t, cur, sp, stack);
-            if (SCHED & 4) node_step_all<SMEM_ALL, OFFS>(S, r, t_min, h.t, cur, sp, stack);
-            if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
-            }
-            act = __ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE);
-            if (__popc(act) < leave_below || --rounds_left <= 0) break;
+            if (__popc(__ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE)) < leave_below) break;
         }
             // ---- finished lanes: store the hit, push the slot into the queue of what it hit ----
         const bool fin = cur == CRT_TRAV_DONE && slot >= 0;

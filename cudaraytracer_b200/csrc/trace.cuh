@@ -98,12 +98,11 @@ template <bool SMEM_ALL> __device__ __forceinline__ void load_mat(const SceneVie
 #define CRT_TRAV_DONE ((int)0x80000000)
 
 // Stages the first smem_* entries of each table into dynamic shared memory. Call from every thread, then __syncthreads().
-// OFFS (experimental, needs PAD and the whole tree in shared memory): inner-child references of the staged nodes, and the
-// entry node, become BYTE OFFSETS into the staged table (index * 80), so a visit needs no address arithmetic at all.
-// PAIR (needs OFFS): the twelve box words of a staged node are interleaved child-wise, {c0.x, c1.x, c0.y, c1.y | c0.z, c1.z,
+// PAIR (needs PAD and the whole tree in shared memory): inner-child references of the staged nodes, and the entry node, become
+// BYTE OFFSETS into the staged table (index * 80), so a visit needs no address arithmetic; the twelve box words of a staged node are interleaved child-wise, {c0.x, c1.x, c0.y, c1.y | c0.z, c1.z,
 // h0.x, h1.x | h0.y, h1.y, h0.z, h1.z}, so that each 64-bit register pair of the three 128-bit loads holds the same quantity of
 // BOTH children and one packed FFMA2 (fma.rn.f32x2, new on sm_100) does the work of two FFMA (node_visit_pair below).
-template <bool PAD, bool OFFS = false, bool PAIR = false> __device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem)
+template <bool PAD, bool PAIR = false> __device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem)
 {
     SceneView S;
     S.g_nodes = D.nodes; S.g_prims = D.prims; S.g_prim_k = D.prim_k; S.g_mats = D.mats; S.images = D.images;
@@ -128,15 +127,10 @@ template <bool PAD, bool OFFS = false, bool PAIR = false> __device__ __forceinli
     }
     else
     for (int i = tid; i < 4 * D.smem_nodes; i += nt) {
-        float4 v = __ldg(D.nodes + i);
-        if (OFFS && (i & 3) == 3) { // {child 0, child 1, -, -}: inner children (>= 0) are renamed, leaf codes (< 0) stay
-            const int c0 = __float_as_int(v.x), c1 = __float_as_int(v.y);
-            v.x = __int_as_float(c0 >= 0 ? c0 * (16 * CRT_SMEM_NODE_F4) : c0);
-            v.y = __int_as_float(c1 >= 0 ? c1 * (16 * CRT_SMEM_NODE_F4) : c1);
-        }
+        const float4 v = __ldg(D.nodes + i);
         sn[PAD ? CRT_SMEM_NODE_F4 * (i >> 2) + (i & 3) : (i & 3) * D.smem_nodes + (i >> 2)] = v;
     }
-    if (OFFS && S.entry >= 0) S.entry *= 16 * CRT_SMEM_NODE_F4;
+    if (PAIR && S.entry >= 0) S.entry *= 16 * CRT_SMEM_NODE_F4;
     for (int i = tid; i < D.smem_prims; i += nt) sp[i] = __ldg(D.prims + i);
     for (int i = tid; i < 2 * D.smem_mats; i += nt) sm[i] = __ldg(D.mats + i);
     S.s_nodes = sn; S.s_prims = sp; S.s_mats = sm;
@@ -356,18 +350,12 @@ __device__ __forceinline__ void node_step(const SceneView& S, const TravRay& r, 
 // The same visit executed by EVERY lane of the warp (fast path): lanes that are not at an inner node run it on node 0 and
 // discard the result. Inactive lanes cost a SIMT machine the same issue slots either way, and without the branch around the
 // body the loop loses its convergence-barrier bookkeeping (profiles/r01_c: 20 uniform instructions per round before this).
-template <bool SMEM_ALL, bool OFFS = false>
+template <bool SMEM_ALL>
 __device__ __forceinline__ void node_step_all(const SceneView& S, const TravRay& r, float t_min, float t_hit, int& cur, int& sp, int* stack)
 {
     const bool at = cur >= 0;
     float4 w0, w1, w2;
     int2 ch;
-    if (OFFS) { // cur is a byte offset into the staged table (stage_scene<true, true>)
-        const float4* p = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(S.s_nodes) + max(cur, 0));
-        w0 = p[0]; w1 = p[1]; w2 = p[2];
-        ch = *reinterpret_cast<const int2*>(p + 3);
-    }
-    else
     load_node<SMEM_ALL, true>(S, at ? cur : 0, w0, w1, w2, ch);
     float tn0, tf0, tn1, tf1;
     slab2(r, w0, w1, w2, t_min, t_hit, tn0, tf0, tn1, tf1);
@@ -375,17 +363,6 @@ __device__ __forceinline__ void node_step_all(const SceneView& S, const TravRay&
     const bool swap = tn1 < tn0;
     const int first = (h0 && !(h1 && swap)) ? ch.x : ch.y; // the nearer hit child (or the only one)
     const int second = swap ? ch.x : ch.y;
-    if (OFFS) { // the same decision written without nested branches: one predicated store, one predicated load
-        const bool any = h0 || h1;
-        const bool push = at && h0 && h1, pop = at && !any && sp > 0;
-        if (push) stack[sp] = second;
-        sp += push ? 1 : 0;
-        int next = any ? first : CRT_TRAV_DONE;
-        if (pop) next = stack[sp - 1];
-        sp -= pop ? 1 : 0;
-        cur = at ? next : cur;
-        return;
-    }
     if (at) {
         if (h0 && h1) stack[sp++] = second;
         if (h0 || h1) cur = first;

@@ -1,7 +1,8 @@
 // trace_sim.cpp — TEST INFRASTRUCTURE: cudaraytracer_b200/csrc/trace.cuh (the BVH traversal of every kernel) compiled for the
 // HOST with g++, so that its logic can be checked without a GPU: the closest hit of the traversal — in each of its forms: the
-// megakernel's node_step loop, the pipelined kernel's node_step_all rounds, and the experimental byte-offset / branch-free
-// node visit with either round schedule — must be the closest hit of a brute-force loop over all primitives, bit for bit,
+// megakernel's node_step loop, the pipelined kernel's node, node, node, leaf rounds with node_step_all (80-byte staged or global
+// nodes) and with node_visit_pair (child-interleaved nodes, FFMA2 emulated by two fmaf, sentinel stack; generic and
+// sphere-only leaf visits) — must be the closest hit of a brute-force loop over all primitives, bit for bit,
 // on the trees crt_pack_scene builds. Only the approximate reciprocal / square root differ from the device (IEEE here), which
 // no comparison in this file depends on: every form runs the same arithmetic.
 //
@@ -71,28 +72,43 @@ Hit brute_force(const SceneView& S, int n_prims, const std::vector<int>& codes, 
     return h;
 }
 
-// one lane of k_render_pipe's traversal: rounds of node / leaf visits (pipeline.cuh), SCHED bit 0 = node, node, leaf,
-// bit 2 = node, node, node, leaf
-long g_node_visits = 0, g_leaf_visits = 0; // of the default form (statistics of the tree, printed at the end)
+// one lane of k_render_pipe's traversal: rounds of three node visits and one leaf visit (pipeline.cuh)
+long g_node_visits = 0, g_leaf_visits = 0; // statistics of the tree, printed at the end
 
-template <bool OFFS, int SCHED> Hit pipe_lane(const SceneView& S, const TravRay& r, float t_min, long& visits)
+template <bool SMEM_ALL> Hit pipe_lane(const SceneView& S, const TravRay& r, float t_min, long& visits)
 {
-    constexpr bool COUNT = !OFFS && SCHED == 0;
     Hit h;
     h.t = 3.402823466e+38f;
     h.leaf = -1;
     int stack[CRT_STACK_SIZE], sp = 0;
+    int cur = trav_begin<false, SMEM_ALL>(S, r, t_min, h);
+    while (cur != CRT_TRAV_DONE) {
+        for (int k = 0; k < 3; k++) {
+            if (cur >= 0) g_node_visits++;
+            node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
+        }
+        if (cur < 0 && cur != CRT_TRAV_DONE) { g_leaf_visits++; leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack); }
+        if (++visits > 100000000L) { fprintf(stderr, "traversal does not terminate\n"); exit(3); }
+        if (sp < 0 || sp > CRT_STACK_SIZE) { fprintf(stderr, "stack pointer out of range: %d\n", sp); exit(3); }
+    }
+    return h;
+}
+
+// the same lane on the PAIR staging: node_visit_pair, sentinel stack, generic or sphere-only leaf visit
+template <bool SPH> Hit pair_lane(const SceneView& S, const TravRay& r, float t_min, long& visits)
+{
+    Hit h;
+    h.t = 3.402823466e+38f;
+    h.leaf = -1;
+    int stack[CRT_STACK_SIZE], sp = 1;
+    stack[0] = CRT_TRAV_DONE;
     int cur = trav_begin<false, true>(S, r, t_min, h);
     while (cur != CRT_TRAV_DONE) {
-        if (COUNT && cur >= 0) g_node_visits++;
-        node_step_all<true, OFFS>(S, r, t_min, h.t, cur, sp, stack);
-        if ((SCHED & 5) == 0) {
-            if (cur < 0 && cur != CRT_TRAV_DONE) { g_leaf_visits += COUNT; leaf_step<false, true>(S, r, t_min, h, cur, sp, stack); }
+        for (int k = 0; k < 3; k++) node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
+        if (cur < 0 && cur != CRT_TRAV_DONE) {
+            if (SPH) leaf_step_sphere(S, r, t_min, h, cur, sp, stack);
+            else leaf_step<false, true, true>(S, r, t_min, h, cur, sp, stack);
         }
-        if (COUNT && cur >= 0) g_node_visits++;
-        node_step_all<true, OFFS>(S, r, t_min, h.t, cur, sp, stack);
-        if (SCHED & 4) node_step_all<true, OFFS>(S, r, t_min, h.t, cur, sp, stack);
-        if (cur < 0 && cur != CRT_TRAV_DONE) { g_leaf_visits += COUNT; leaf_step<false, true>(S, r, t_min, h, cur, sp, stack); }
         if (++visits > 100000000L) { fprintf(stderr, "traversal does not terminate\n"); exit(3); }
         if (sp < 0 || sp > CRT_STACK_SIZE) { fprintf(stderr, "stack pointer out of range: %d\n", sp); exit(3); }
     }
@@ -141,7 +157,7 @@ int main(int argc, char** argv)
     if (found != np) { fprintf(stderr, "tree names %d leaves, scene has %d primitives\n", found, np); return 2; }
 
     // the stagings: everything behind 'global' pointers, the megakernel's word-major shared-memory table, the padded (80-byte)
-    // table of the one-CTA-per-SM kernels, and that table with byte-offset child references
+    // table of the one-CTA-per-SM kernels, and that table child-interleaved with byte-offset child references (PAIR)
     D.smem_nodes = D.smem_prims = D.smem_mats = 0;
     std::vector<float4> smem0(16), smem1((size_t)nn * CRT_SMEM_NODE_F4 + (size_t)np * 3 + 16), smem2(smem1.size());
     const SceneView Sg = stage_scene<false>(D, smem0.data());
@@ -150,6 +166,8 @@ int main(int argc, char** argv)
     const SceneView Sw = stage_scene<false>(D, smem3.data()); // word-major table: what the megakernel stages
     const SceneView Sp = stage_scene<true, false>(D, smem1.data());
     const SceneView So = stage_scene<true, true>(D, smem2.data());
+    bool spheres_only = true;
+    for (int c : leaf_code) if (((c >> CRT_LEAF_TYPE_SHIFT) & 3) != CRT_SPHERE) spheres_only = false;
 
     // rays: from a camera-like point towards the scene, from random points inside the scene box in random directions, and
     // axis-parallel ones (zero direction components take the clamped-reciprocal path of trav_setup)
@@ -179,17 +197,15 @@ int main(int argc, char** argv)
         const TravRay r = trav_setup<false>(o, d);
         const Hit want = brute_force(Sp, np, leaf_code, r, t_min);
         unsigned nb = 0, npr = 0;
-        Hit got[8];
+        Hit got[6];
         got[0] = closest_hit<false, false, false>(Sg, o, d, t_min, 3.402823466e+38f, nb, npr); // megakernel form, global tables
         got[1] = closest_hit<false, false, true>(Sw, o, d, t_min, 3.402823466e+38f, nb, npr);  // ... tables in 'shared memory'
-        got[2] = pipe_lane<false, 0>(Sp, r, t_min, visits);
-        got[3] = pipe_lane<false, 1>(Sp, r, t_min, visits);
-        got[4] = pipe_lane<true, 2>(So, r, t_min, visits);
-        got[5] = pipe_lane<true, 3>(So, r, t_min, visits);
-        got[6] = pipe_lane<false, 4>(Sp, r, t_min, visits);
-        got[7] = pipe_lane<true, 6>(So, r, t_min, visits);
+        got[2] = pipe_lane<true>(Sp, r, t_min, visits);
+        got[3] = pipe_lane<false>(Sg, r, t_min, visits); // nodes behind the 'global' pointers (scenes that do not fit)
+        got[4] = pair_lane<false>(So, r, t_min, visits);
+        got[5] = spheres_only ? pair_lane<true>(So, r, t_min, visits) : got[4];
         hits += want.leaf >= 0;
-        for (int k = 0; k < 8; k++)
+        for (int k = 0; k < 6; k++)
             if (got[k].leaf != want.leaf || memcmp(&got[k].t, &want.t, 4) != 0) {
                 if (mism++ < 5)
                     fprintf(stderr, "ray %d form %d: leaf %d t %.9g, brute force: leaf %d t %.9g\n", i, k, got[k].leaf, got[k].t, want.leaf, want.t);
@@ -197,7 +213,7 @@ int main(int argc, char** argv)
     }
     printf("scene %d (%d primitives, %d nodes, %d peeled): %d rays, %ld hits, %ld mismatches\n", kind, np, nn, D.n_top, n_rays, hits, mism);
     printf("tree: SAH cost %.3f, depth %d; per ray %.3f node visits, %.3f leaf visits (+ %d peeled tests)\n", P.stats.sah_cost, (int)P.stats.max_depth,
-           (double)g_node_visits / n_rays, (double)g_leaf_visits / n_rays, D.n_top);
+           (double)g_node_visits / (2.0 * n_rays), (double)g_leaf_visits / (2.0 * n_rays), D.n_top);
     crt_scene_builder_free(sb);
     return mism ? 1 : 0;
 }

@@ -288,28 +288,6 @@ def test_variants_bit_identical_to_megakernel(renderer, name, kind, hint, W, H, 
         f"{(mega != wave).any(axis=-1).sum()} of {W * H} pixels differ between the variants"
 
 
-@pytest.mark.skipif(not os.environ.get("CRT_TEST_EXPERIMENTAL"), reason="experimental kernel builds (CRT_PIPE_SCHED=1..6), not the default "
-                    "path: run with CRT_TEST_EXPERIMENTAL=1 when measuring it")
-@pytest.mark.parametrize("kind,hint", [(capi.SCENE_RTIOW, 0), (capi.SCENE_GRID_1M, 60)], ids=["rtiow", "grid3601"])
-def test_experimental_round_schedule_is_bit_identical(monkeypatch, kind, hint):
-    """CRT_PIPE_SCHED=1 (node, node, leaf rounds), 2 (byte-offset child references, branch-free node visit), 3 (both), 4 (node,
-    node, node, leaf) and 6 (4 + 2) of pipeline.cuh change the interleaving of the lanes and the naming of the nodes, never the
-    result."""
-    s = Scene.generate(kind, 1984, hint)
-    W, H = 161, 91
-    cam = s.default_camera(W, H)
-    out = []
-    for sched in ("0", "4", "8", "12"):
-        monkeypatch.setenv("CRT_PIPE_SCHED", sched)
-        r = Renderer(0)
-        _setup(r, s, cam, W, H)
-        r.render(spp=5, max_depth=50, variant=capi.VARIANT_PIPELINE)
-        out.append(r.read_accum().view(np.uint32).copy())
-        r.close()
-    for o in out[1:]:
-        assert np.array_equal(out[0], o)
-
-
 @pytest.mark.parametrize("variant", [capi.VARIANT_WAVEFRONT, capi.VARIANT_PIPELINE], ids=["wavefront", "pipeline"])
 def test_small_pool_progressive_and_sharded(monkeypatch, variant):
     """A pool much smaller than the work (regeneration + drain), progressive calls, and spp sharding: all bit-identical."""

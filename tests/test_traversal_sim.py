@@ -1,8 +1,8 @@
 """The BVH traversal of the kernels (cudaraytracer_b200/csrc/trace.cuh) compiled for the HOST (tests/sim/trace_sim.cpp, g++ with
 -DCRT_HOST_SIM) and run against a brute-force closest hit on the trees the library's own builder packs. No GPU: this checks the
 LOGIC of every traversal form - the megakernel's node_step loop on global and on word-major shared tables, the pipelined
-kernel's node_step_all rounds, and the experimental builds (CRT_PIPE_SCHED bits: node-node-leaf rounds, byte-offset child
-references with the branch-free visit) - bit for bit; the device arithmetic itself is what the -m gpu parity tests pin."""
+kernel's node, node, node, leaf rounds with node_step_all (staged or 'global' nodes) and with node_visit_pair (child-interleaved
+staged nodes, FFMA2 emulated with fmaf, sentinel stack, generic and sphere-only leaf visits) - bit for bit; the device arithmetic itself is what the -m gpu parity tests pin."""
 import os
 import subprocess
 
