@@ -90,7 +90,7 @@ class Counters(C.Structure):
 class BvhStats(C.Structure):
     _fields_ = [("n_prims", C.c_uint64), ("n_nodes", C.c_uint64), ("max_depth", C.c_uint64), ("smem_nodes", C.c_uint64),
                 ("sah_cost", C.c_double), ("build_ms", C.c_double), ("node_bytes", C.c_uint64), ("prim_bytes", C.c_uint64),
-                ("h2d_bytes", C.c_uint64), ("builder", C.c_uint64)]
+                ("h2d_bytes", C.c_uint64), ("builder", C.c_uint64), ("cache_hits", C.c_uint64)]
 
 
 assert C.sizeof(Hittable) == 32 and C.sizeof(Material) == 16 and C.sizeof(Texture) == 48 and C.sizeof(InputStruct) == 72
@@ -105,6 +105,7 @@ SIGNATURES = {
     "crt_set_stream": (C.c_int, [_P, _P]),
     "crt_synchronize": (C.c_int, [_P]),
     "crt_set_bvh_builder": (C.c_int, [_P, C.c_int32]),
+    "crt_set_scene_cache": (C.c_int, [_P, C.c_int32]),
     "crt_scene_upload": (C.c_int, [_P, C.POINTER(SceneDesc)]),
     "crt_scene_from_reference": (C.c_int, [_P, _P]),
     "crt_bvh_get_stats": (C.c_int, [_P, C.POINTER(BvhStats)]),
@@ -160,6 +161,25 @@ SIGNATURES = {
 }
 
 _lib = None
+_scenegen = None
+SCENEGEN_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libcrt_scenegen.so")
+SCENEGEN_SYMBOLS = ("crt_scene_generate", "crt_scene_builder_desc", "crt_scene_builder_camera", "crt_scene_builder_free",
+                    "crt_camera_look", "crt_last_error_string", "crt_load_image", "crt_free")
+
+
+def load_scenegen() -> C.CDLL:
+    """The HOST-ONLY library (scene generators + image decoder, no CUDA): for processes that must not map libcrt.so, i.e. the
+    CPU arm of bench.py that times the reference's own code."""
+    global _scenegen
+    if _scenegen is None:
+        if not os.path.exists(SCENEGEN_PATH):
+            raise RuntimeError(f"{SCENEGEN_PATH} is missing: build it with `make -C cudaraytracer_b200/csrc`")
+        lib = C.CDLL(SCENEGEN_PATH)
+        for name in SCENEGEN_SYMBOLS:
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = SIGNATURES[name]
+        _scenegen = lib
+    return _scenegen
 
 
 def load() -> C.CDLL:

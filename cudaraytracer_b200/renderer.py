@@ -32,14 +32,20 @@ class Scene:
     def __init__(self):
         self._builder = None
         self._keep = []
+        self._lib = None
         self.desc = None
 
     @classmethod
-    def generate(cls, kind: int, seed: int = 1984, size_hint: int = 0) -> "Scene":
-        lib = capi.load()
+    def generate(cls, kind: int, seed: int = 1984, size_hint: int = 0, host_only: bool = False) -> "Scene":
+        """host_only: use libcrt_scenegen.so (no CUDA, the product library stays unmapped) instead of libcrt.so."""
+        lib = capi.load_scenegen() if host_only else capi.load()
         s = cls()
+        s._lib = lib
         b = C.c_void_p()
-        _check(lib.crt_scene_generate(kind, seed, size_hint, C.byref(b)))
+        st = lib.crt_scene_generate(kind, seed, size_hint, C.byref(b))
+        if st != capi.CRT_OK:
+            msg = lib.crt_last_error_string(None)
+            raise CrtError(f"crt status {st}: {msg.decode() if msg else '?'}")
         s._builder = b
         s.desc = lib.crt_scene_builder_desc(b).contents
         return s
@@ -76,7 +82,8 @@ class Scene:
         if self._builder is None:
             raise CrtError("default_camera: only generated scenes carry a camera")
         cam = capi.InputStruct()
-        _check(capi.load().crt_scene_builder_camera(self._builder, width, height, C.byref(cam)))
+        if self._lib.crt_scene_builder_camera(self._builder, width, height, C.byref(cam)) != capi.CRT_OK:
+            raise CrtError("crt_scene_builder_camera failed")
         return cam
 
     @property
@@ -101,7 +108,7 @@ class Scene:
     def __del__(self):
         if self._builder is not None:
             try:
-                capi.load().crt_scene_builder_free(self._builder)
+                self._lib.crt_scene_builder_free(self._builder)
             except Exception:
                 pass
             self._builder = None
@@ -156,6 +163,11 @@ class Renderer:
     def set_bvh_builder(self, builder: int):
         """capi.BUILDER_AUTO / BUILDER_HOST_SAH (threaded SAH on the host) / BUILDER_GPU_LBVH (Morton LBVH on the device)."""
         self._ck(self.lib.crt_set_bvh_builder(self.ctx, builder))
+
+    def set_scene_cache(self, enabled: bool):
+        """crt_scene_upload of a description whose content hash equals the scene already on the device returns at once (default
+        on); off = every upload validates, builds and copies."""
+        self._ck(self.lib.crt_set_scene_cache(self.ctx, int(bool(enabled))))
 
     def upload(self, scene: Scene):
         self._ck(self.lib.crt_scene_upload(self.ctx, C.byref(scene.desc)))

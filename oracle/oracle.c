@@ -512,6 +512,28 @@ static v3 color(const oscene* S, ray r, int max_depth, xorwow* rng, const crt_in
 static unsigned long long g_seed_base = 1984;
 void oracle_set_seed_base(uint64_t seed) { g_seed_base = seed; }
 
+/* Pixel subset for checks at full benchmark resolution (bench.py `parity`, tests of the 4K / 8K workloads): only pixels with
+ * x % sx == 0 and y % sy == 0 are computed, with exactly the rays they have in the full frame; the others keep what the
+ * caller put into the output arrays. 1, 1 (the default) is the whole frame. */
+static uint32_t g_stride_x = 1, g_stride_y = 1;
+void oracle_set_pixel_stride(uint32_t sx, uint32_t sy)
+{
+    g_stride_x = sx ? sx : 1;
+    g_stride_y = sy ? sy : 1;
+}
+
+/* Thin-lens extension of the NEW path (crt_set_lens; north_star asks for defocus, the reference renders a pinhole and only
+ * carries an unused RandomInUnitDisk, Math.cuh:276-285). Restated here so that the lens has a checker: lens point uniform on
+ * the disk of radius aperture / 2 spanned by (right, up) - the polar map of two uniforms has the distribution of the
+ * reference's rejection sampler -, aimed at the point where the pinhole ray meets the plane at focus_dist along forward.
+ * aperture == 0 (the default) draws nothing and is the reference camera bit for bit. */
+static float g_lens_radius = 0.0f, g_focus_dist = 1.0f;
+void oracle_set_lens(float aperture, float focus_dist)
+{
+    g_lens_radius = aperture > 0.0f ? 0.5f * aperture : 0.0f;
+    g_focus_dist = focus_dist > 0.0f ? focus_dist : 1.0f;
+}
+
 typedef struct
 {
     const oscene* S;
@@ -580,6 +602,15 @@ static void pixel(job* J, int x, int y, uint64_t* rays)
         float j1 = J->jitter_center ? 0.5f : xorwow_uniform(&rng);
         float j2 = J->jitter_center ? 0.5f : xorwow_uniform(&rng);
         ray r = camera_ray(in, rightV, width, height, x, y, j1, j2);
+        if (g_lens_radius > 0.0f) {
+            float l1 = xorwow_uniform(&rng), l2 = xorwow_uniform(&rng);
+            float rad = g_lens_radius * sqrtf(l1), phi = 2.0f * 3.141592654f * l2;
+            v3 off = vadd(smul(rad * cosf(phi), rightV), smul(rad * sinf(phi), upV));
+            float tf = g_focus_dist / dot(r.dir, forwardV);
+            v3 focus = vadd(r.orig, smul(tf, r.dir));
+            r.orig = vadd(r.orig, off);
+            r.dir = normalize(vsub(focus, r.orig));
+        }
         col = vadd(col, color(J->S, r, (int)J->max_depth, &rng, in, rays));
     }
     col = sdiv(col, (float)(J->spp));
@@ -605,7 +636,9 @@ static void* worker(void* arg)
         pthread_mutex_unlock(&J->mu);
         if (y >= J->height)
             break;
-        for (uint32_t x = 0; x < J->width; x++)
+        if (y % g_stride_y)
+            continue;
+        for (uint32_t x = 0; x < J->width; x += g_stride_x)
             pixel(J, (int)x, (int)y, &rays);
     }
     pthread_mutex_lock(&J->mu);

@@ -31,6 +31,13 @@ int oracle_render(const crt_scene_desc* scene, const crt_input_struct* cam, uint
 /* Seed base of RenderInit (Kernel.cu:175 uses 1984). Only for noise-floor measurements between two oracle runs. */
 void oracle_set_seed_base(uint64_t seed);
 
+/* Only pixels with x % sx == 0 and y % sy == 0 are computed (same rays as in the full frame); the rest of the output arrays is
+ * left alone. For checks at full benchmark resolution. 1, 1 restores the whole frame. */
+void oracle_set_pixel_stride(uint32_t sx, uint32_t sy);
+
+/* Thin lens of the new path (crt_set_lens): aperture = lens diameter, 0 = the reference's pinhole (default). */
+void oracle_set_lens(float aperture, float focus_dist);
+
 /* Kernel.cu:151-157 + 12-19 applied to an accumulation buffer (float4 per pixel: rgb sum, sample count). */
 void oracle_resolve(const float* accum_float4, uint32_t n_pixels, uint32_t* out_rgba8);
 

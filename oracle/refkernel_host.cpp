@@ -45,6 +45,9 @@ extern "C" void LaunchRenderInit(dim3 grid, dim3 block, unsigned int window_widt
 // oracle/refkernel_ids.cu
 extern "C" int refkernel_ids_launch(Hittable* world, const char* slab, size_t list_bytes, size_t record_bytes, size_t n,
                                     InputStruct inputs, unsigned width, unsigned height, int* d_out);
+// the same translation unit compiled with IEEE arithmetic (-fmad=false, no -use_fast_math)
+extern "C" int refkernel_ids_launch_ieee(Hittable* world, const char* slab, size_t list_bytes, size_t record_bytes, size_t n,
+                                         InputStruct inputs, unsigned width, unsigned height, int* d_out);
 
 namespace {
 
@@ -101,8 +104,18 @@ int refkernel_render(const crt_scene_desc* scene, const crt_input_struct* cam, u
     return rc;
 }
 
-// Primary-hit hittable indices (xi = 0.5) computed by the reference's own device BVHNode::Hit.
+// Primary-hit hittable indices (xi = 0.5) computed by the reference's own device BVHNode::Hit; ieee = 0: the reference's release
+// flags (fast math), 1: IEEE arithmetic.
+static int primary_ids(const crt_scene_desc* scene, const crt_input_struct* cam, uint32_t width, uint32_t height, int32_t* out_ids, int ieee);
 int refkernel_primary_ids(const crt_scene_desc* scene, const crt_input_struct* cam, uint32_t width, uint32_t height, int32_t* out_ids)
+{
+    return primary_ids(scene, cam, width, height, out_ids, 0);
+}
+int refkernel_primary_ids_ieee(const crt_scene_desc* scene, const crt_input_struct* cam, uint32_t width, uint32_t height, int32_t* out_ids)
+{
+    return primary_ids(scene, cam, width, height, out_ids, 1);
+}
+static int primary_ids(const crt_scene_desc* scene, const crt_input_struct* cam, uint32_t width, uint32_t height, int32_t* out_ids, int ieee)
 {
     Log::Init();
     RefScene rs;
@@ -113,7 +126,7 @@ int refkernel_primary_ids(const crt_scene_desc* scene, const crt_input_struct* c
     const size_t npx = (size_t)width * height;
     int rc = 0;
     if (cudaMalloc(&d_out, npx * 4) != cudaSuccess) rc = 2;
-    if (!rc) rc = refkernel_ids_launch(rs.world, rs.slab, rs.list_bytes, rs.record_bytes, rs.n, in, width, height, d_out);
+    if (!rc) rc = (ieee ? refkernel_ids_launch_ieee : refkernel_ids_launch)(rs.world, rs.slab, rs.list_bytes, rs.record_bytes, rs.n, in, width, height, d_out);
     if (!rc && cudaMemcpy(out_ids, d_out, npx * 4, cudaMemcpyDeviceToHost) != cudaSuccess) rc = 4;
     cudaFree(d_out);
     FreeScene(rs);

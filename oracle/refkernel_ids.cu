@@ -2,7 +2,13 @@
 // A tiny kernel of OURS that calls the REFERENCE'S device BVHNode::Hit (Hittable.cuh:387-439) for one
 // xi = 0.5 primary ray per pixel and maps rec.mat_ptr back to the hittable-list index (each record of the
 // slab owns its Material, so the pointer identifies the hittable). Ray generation restates Kernel.cu:130-146.
-// Compiled with the reference's release flags, so this is the fast-math GPU flavour of the reference.
+// Compiled twice (oracle/Makefile): with the reference's release flags (-use_fast_math: the GPU flavour the reference ships,
+// entry refkernel_ids_launch) and with IEEE arithmetic (-fmad=false, no fast math: entry refkernel_ids_launch_ieee), the
+// flavour whose IDs the new path must reproduce BIT FOR BIT (SURVEY.md §7 hard parts (iii), north_star).
+#ifndef REFIDS_KERNEL
+#define REFIDS_KERNEL RefPrimaryIds
+#define REFIDS_LAUNCH refkernel_ids_launch
+#endif
 #include <cuda_runtime.h>
 #include <device_launch_parameters.h>
 #include <float.h>
@@ -11,7 +17,7 @@
 #include "Hittables/Material.cuh"
 #include "Utils/SharedStructs.h"
 
-__global__ void RefPrimaryIds(Hittable* world, const char* slab, size_t list_bytes, size_t record_bytes, size_t n, InputStruct inputs,
+__global__ void REFIDS_KERNEL(Hittable* world, const char* slab, size_t list_bytes, size_t record_bytes, size_t n, InputStruct inputs,
                               unsigned width, unsigned height, int* out)
 {
     int x = blockIdx.x * blockDim.x + threadIdx.x;
@@ -39,10 +45,10 @@ __global__ void RefPrimaryIds(Hittable* world, const char* slab, size_t list_byt
     out[y * width + x] = id;
 }
 
-extern "C" int refkernel_ids_launch(Hittable* world, const char* slab, size_t list_bytes, size_t record_bytes, size_t n,
+extern "C" int REFIDS_LAUNCH(Hittable* world, const char* slab, size_t list_bytes, size_t record_bytes, size_t n,
                                     InputStruct inputs, unsigned width, unsigned height, int* d_out)
 {
     dim3 block(16, 16, 1), grid((width + 15) / 16, (height + 15) / 16, 1);
-    RefPrimaryIds<<<grid, block>>>(world, slab, list_bytes, record_bytes, n, inputs, width, height, d_out);
+    REFIDS_KERNEL<<<grid, block>>>(world, slab, list_bytes, record_bytes, n, inputs, width, height, d_out);
     return cudaDeviceSynchronize() == cudaSuccess ? 0 : 3;
 }

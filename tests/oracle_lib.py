@@ -35,6 +35,9 @@ def oracle():
         lib.oracle_aabb_hit.restype = C.c_int
         lib.oracle_aabb_hit.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float]
         lib.oracle_philox4x32_10.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.oracle_set_pixel_stride.argtypes = [C.c_uint32, C.c_uint32]
+        lib.oracle_set_lens.argtypes = [C.c_float, C.c_float]
+        lib.oracle_set_seed_base.argtypes = [C.c_uint64]
         _oracle = lib
     return _oracle
 
@@ -79,8 +82,17 @@ def _render(which, scene, cam, width, height, spp, max_depth, jitter_center=Fals
     return {"rgba": rgba, "mean": mean, "ids": ids, "rays": int(rays.value)}
 
 
-def oracle_render(scene, cam, width, height, spp, max_depth, **kw):
-    return _render("oracle", scene, cam, width, height, spp, max_depth, **kw)
+def oracle_render(scene, cam, width, height, spp, max_depth, stride=(1, 1), lens=None, **kw):
+    """stride = (sx, sy): only pixels with x % sx == 0 and y % sy == 0 (their full-frame rays); the other entries of the
+    outputs keep their fill value (ids: -9). lens = (aperture, focus_dist): the thin lens of the new path."""
+    lib = oracle()
+    lib.oracle_set_pixel_stride(int(stride[0]), int(stride[1]))
+    lib.oracle_set_lens(*(lens if lens else (0.0, 1.0)))
+    try:
+        return _render("oracle", scene, cam, width, height, spp, max_depth, **kw)
+    finally:
+        lib.oracle_set_pixel_stride(1, 1)
+        lib.oracle_set_lens(0.0, 1.0)
 
 
 def refhost_render(scene, cam, width, height, spp, max_depth, **kw):
@@ -113,6 +125,8 @@ def refkernel():
                                          C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
         lib.refkernel_primary_ids.restype = C.c_int
         lib.refkernel_primary_ids.argtypes = [C.POINTER(capi.SceneDesc), C.POINTER(capi.InputStruct), C.c_uint32, C.c_uint32, C.c_void_p]
+        lib.refkernel_primary_ids_ieee.restype = C.c_int
+        lib.refkernel_primary_ids_ieee.argtypes = lib.refkernel_primary_ids.argtypes
         _refkernel = lib
     return _refkernel
 
@@ -128,9 +142,11 @@ def refkernel_render(scene, cam, width, height, spp, max_depth, reps=1):
     return rgba, [float(x) for x in ms[:reps]]
 
 
-def refkernel_primary_ids(scene, cam, width, height):
+def refkernel_primary_ids(scene, cam, width, height, ieee=False):
+    """The reference's device BVHNode::Hit per pixel; ieee=False: its release flags (-use_fast_math), True: IEEE arithmetic."""
     ids = np.full((height, width), -9, dtype=np.int32)
-    rc = refkernel().refkernel_primary_ids(C.byref(scene.desc), C.byref(cam), width, height, ids.ctypes.data_as(C.c_void_p))
+    fn = refkernel().refkernel_primary_ids_ieee if ieee else refkernel().refkernel_primary_ids
+    rc = fn(C.byref(scene.desc), C.byref(cam), width, height, ids.ctypes.data_as(C.c_void_p))
     if rc != 0:
         raise RuntimeError(f"refkernel_primary_ids failed with {rc}")
     return ids

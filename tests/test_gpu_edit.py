@@ -124,3 +124,74 @@ def test_refit_of_a_large_scene_is_much_cheaper_than_a_rebuild():
     print(f"refit {t_refit * 1e3:.2f} ms vs host rebuild {t_rebuild * 1e3:.2f} ms vs GPU rebuild {t_gpu * 1e3:.2f} ms")
     assert t_refit < t_rebuild and t_gpu < t_rebuild
     r.close()
+
+
+def test_unchanged_scene_upload_is_a_cache_hit_and_any_change_is_not():
+    """crt_scene_upload hashes the description: the scene already on the device is not validated, built or copied again
+    (crt_bvh_stats.cache_hits / h2d_bytes say so); a changed sphere, an edit + commit, or the switch turned off all upload."""
+    W, H = 160, 90
+    base = Scene.generate(capi.SCENE_RTIOW, 1984)
+    cam = base.default_camera(W, H)
+    hs, ms, ts = _lists(base)
+    r = Renderer(0)
+    try:
+        r.upload(base); r.set_camera(cam); r.resize(W, H)
+        st = r.bvh_stats()
+        assert st.h2d_bytes > 0 and st.cache_hits == 0
+        r.render(spp=3, max_depth=50)
+        first = r.read_accum().view(np.uint32).copy()
+        r.upload(base)
+        st = r.bvh_stats()
+        assert st.h2d_bytes == 0 and st.cache_hits == 1
+        same = Scene.from_arrays(hs, ms, ts)  # another object, other addresses, same content
+        r.upload(same)
+        assert r.bvh_stats().cache_hits == 2
+        r.clear(); r.render(spp=3, max_depth=50)
+        assert np.array_equal(first, r.read_accum().view(np.uint32))
+        hs2 = [dict(h) for h in hs]
+        hs2[7]["cy"] += 0.25
+        moved = Scene.from_arrays(hs2, ms, ts)
+        r.upload(moved)
+        st = r.bvh_stats()
+        assert st.h2d_bytes > 0 and st.cache_hits == 0
+        ref_ids = O.oracle_render(moved, cam, W, H, 0, 50, want_ids=True, want_rgba=False, want_mean=False)["ids"]
+        assert np.array_equal(r.primary_ids(), ref_ids)
+        # an edit makes the device scene differ from what was hashed: the ORIGINAL description must upload again
+        r.upload(base)
+        assert r.bvh_stats().h2d_bytes > 0
+        r.edit_hittable(7, **hs2[7])
+        r.commit()
+        r.upload(base)
+        assert r.bvh_stats().h2d_bytes > 0 and r.bvh_stats().cache_hits == 0
+        r.clear(); r.render(spp=3, max_depth=50)
+        assert np.array_equal(first, r.read_accum().view(np.uint32))
+        r.set_scene_cache(False)
+        r.upload(base)
+        assert r.bvh_stats().h2d_bytes > 0 and r.bvh_stats().cache_hits == 0
+    finally:
+        r.close()
+
+
+def test_refit_path_validates_the_material_it_packs():
+    """a hittable re-pointed (no topology change) at a material that no active hittable used at upload, whose texture
+    chain is broken, must be refused by crt_scene_commit instead of being packed (out-of-bounds reads on host and device)."""
+    hs = [dict(type=capi.SPHERE, cx=0.0, cy=-100.5, cz=-1.0, a=100.0, material=0), dict(type=capi.SPHERE, cx=0.0, cy=0.0, cz=-1.0, a=0.5, material=0),
+          dict(type=capi.SPHERE, cx=1.0, cy=0.0, cz=-1.0, a=0.5, material=0)]
+    ms = [dict(type=capi.LAMBERTIAN, texture=0), dict(type=capi.LAMBERTIAN, texture=7),   # texture index out of range, unused
+          dict(type=capi.LAMBERTIAN, texture=1)]                                         # image index out of range, unused
+    ts = [dict(type=capi.CONSTANT, color=(0.5, 0.5, 0.5)), dict(type=capi.IMAGE, image=3)]
+    s = Scene.from_arrays(hs, ms, ts)
+    r = Renderer(0)
+    try:
+        r.upload(s)
+        for bad in (1, 2):
+            h = dict(hs[1]); h["material"] = bad
+            r.edit_hittable(1, **h)
+            with pytest.raises(Exception) as e:
+                r.commit()
+            assert "material" in str(e.value) or "texture" in str(e.value)
+        h = dict(hs[1]); h["cx"] = 0.25
+        r.edit_hittable(1, **h)  # a valid edit replaces the pending bad one
+        assert r.commit() is False
+    finally:
+        r.close()

@@ -123,6 +123,59 @@ def test_image_matches_oracle_statistically(renderer, name, kind, hint, W, H):
     assert psnr >= psnr_floor - 1.0, (psnr, psnr_floor)
 
 
+def test_thin_lens_aperture_zero_is_the_pinhole_and_defocus_matches_the_oracle(renderer):
+    """north_star "camera origin/FOV/defocus", config 3 "defocus blur" (aperture 0.1, focus 10). The reference
+    renders a pinhole (its RandomInUnitDisk, Math.cuh:276-285, is unused); the lens is an extension of the new path and of
+    the oracle (oracle_set_lens). aperture 0 must be the reference camera BIT FOR BIT in every variant; aperture 0.1 / focus 10
+    must meet the image bar of this file against the oracle with the same lens, and must differ from the pinhole image."""
+    s = Scene.generate(capi.SCENE_TEXTURED, 1984, 512)
+    W, H, spp, depth = 160, 90, 64, 50
+    cam = s.default_camera(W, H)
+    _setup(renderer, s, cam, W, H)
+    try:
+        for variant in (capi.VARIANT_MEGAKERNEL, capi.VARIANT_PIPELINE):
+            renderer.set_lens(0.0, 10.0)  # the default
+            renderer.clear()
+            renderer.render(spp=4, max_depth=depth, variant=variant)
+            pin = renderer.read_accum().view(np.uint32).copy()
+            renderer.set_lens(0.0, 3.5)  # a focus distance without an aperture changes nothing
+            renderer.clear()
+            renderer.render(spp=4, max_depth=depth, variant=variant)
+            assert np.array_equal(pin, renderer.read_accum().view(np.uint32))
+        a0 = O.oracle_render(s, cam, W, H, 4, depth, lens=(0.0, 10.0))
+        a1 = O.oracle_render(s, cam, W, H, 4, depth)
+        assert np.array_equal(a0["rgba"], a1["rgba"]) and np.array_equal(a0["mean"].view(np.uint32), a1["mean"].view(np.uint32))
+
+        lens = (0.1, 10.0)
+        renderer.set_lens(*lens)
+        imgs = {}
+        for variant in (capi.VARIANT_MEGAKERNEL, capi.VARIANT_PIPELINE, capi.VARIANT_WAVEFRONT):
+            renderer.clear()
+            renderer.render(spp=spp, max_depth=depth, variant=variant)
+            imgs[variant] = renderer.read_accum()
+        assert np.array_equal(imgs[capi.VARIANT_MEGAKERNEL].view(np.uint32), imgs[capi.VARIANT_PIPELINE].view(np.uint32))
+        assert np.array_equal(imgs[capi.VARIANT_MEGAKERNEL].view(np.uint32), imgs[capi.VARIANT_WAVEFRONT].view(np.uint32))
+        acc = imgs[capi.VARIANT_MEGAKERNEL]
+        new = np.clip(acc[..., :3] / acc[..., 3:4], 0, 4)
+        O.oracle().oracle_set_seed_base(1984)
+        a = np.clip(O.oracle_render(s, cam, W, H, spp, depth, lens=lens)["mean"], 0, 4)
+        O.oracle().oracle_set_seed_base(777001)
+        b = np.clip(O.oracle_render(s, cam, W, H, spp, depth, lens=lens)["mean"], 0, 4)
+        O.oracle().oracle_set_seed_base(1984)
+        pinhole = np.clip(O.oracle_render(s, cam, W, H, spp, depth)["mean"], 0, 4)
+        floor = _rmse(a, b)
+        got = max(_rmse(new, a), _rmse(new, b))
+        assert got <= 1.25 * floor, f"lens: RMSE new-vs-oracle {got:.5f} vs noise floor {floor:.5f}"
+        # the blur is really there: the lens image is further from the pinhole image than the noise floor explains
+        assert _rmse(new, pinhole) > 1.5 * floor, (_rmse(new, pinhole), floor)
+        nb, ab, bb = _block_mean(new, 8), _block_mean(a, 8), _block_mean(b, 8)
+        sigma = max(_rmse(ab, bb), 1e-6)
+        bias = float(np.abs((nb - 0.5 * (ab + bb)).mean(axis=(0, 1))).max())
+        assert bias <= 5 * sigma / np.sqrt(nb.shape[0] * nb.shape[1]) + 0.005 * float(ab.mean()), (bias, sigma)
+    finally:
+        renderer.set_lens(0.0, 10.0)
+
+
 def test_exact_math_render_agrees_with_fast(renderer):
     s = Scene.generate(capi.SCENE_RTIOW, 1984)
     W, H = 96, 54

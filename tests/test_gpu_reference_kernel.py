@@ -18,8 +18,25 @@ SCENES = [("rtiow", capi.SCENE_RTIOW, 0, 400, 225), ("refdefault", capi.SCENE_RE
 
 @needs_refkernel
 @pytest.mark.parametrize("name,kind,hint,W,H", SCENES)
+def test_primary_ids_bit_exact_vs_reference_device_code_ieee(name, kind, hint, W, H):
+    """north_star: "primary-ray hit primitive IDs must be bit-exact against the reference kernel". The reference's own device
+    BVHNode::Hit / Sphere::Hit / rect Hit (Hittable.cuh:80-110,139-280,387-439), compiled for sm_100a with IEEE arithmetic
+    (-fmad=false, no -use_fast_math: oracle/Makefile _ref/refkernel_ids_ieee.o), against crt_primary_ids: every pixel equal."""
+    s = Scene.generate(kind, 1984, hint)
+    cam = s.default_camera(W, H)
+    r = Renderer(0)
+    r.upload(s); r.set_camera(cam); r.resize(W, H)
+    ours = r.primary_ids(capi.JITTER_CENTER)
+    r.close()
+    ref = O.refkernel_primary_ids(s, cam, W, H, ieee=True)
+    assert np.array_equal(ours, ref), f"{(ours != ref).sum()} of {ours.size} primary-hit IDs differ from the reference's device code"
+    assert (ours >= 0).any()
+
+
+@needs_refkernel
+@pytest.mark.parametrize("name,kind,hint,W,H", SCENES)
 def test_primary_ids_vs_reference_kernel(name, kind, hint, W, H):
-    """The reference GPU build is fast-math (CMakeLists.txt:36), our ID path is IEEE like the host oracle: IDs must be
+    """The second, reported flavour. The reference GPU build is fast-math (CMakeLists.txt:36), our ID path is IEEE like the host oracle: IDs must be
     identical except where fast-math rounding flips a silhouette tie; the oracle comparison (test_gpu_parity) is the
     bit-exact bar. Here: >= 99.9 % identical and every difference sits on an ID edge of the oracle map."""
     s = Scene.generate(kind, 1984, hint)

@@ -134,3 +134,34 @@ def test_empty_and_inactive_scenes():
     one = Scene.from_arrays([dict(type=capi.SPHERE, cx=0, cy=0, cz=0, a=1.0, material=0, active=1)], mat, tex)
     c = O.oracle_render(one, cam, W, H, 1, 5, want_ids=True)
     assert (c["ids"] == 0).any() and (c["ids"] == -1).any()
+
+
+def test_pixel_stride_computes_the_full_frame_rays_of_a_subset():
+    """oracle_set_pixel_stride (bench.py `parity`, full-size GPU tests): the strided pixels get exactly their full-frame IDs and
+    colours, everything else is left alone."""
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    W, H = 96, 54
+    cam = s.default_camera(W, H)
+    full = O.oracle_render(s, cam, W, H, 2, 50, want_ids=True)
+    sub = O.oracle_render(s, cam, W, H, 2, 50, want_ids=True, stride=(8, 6))
+    assert np.array_equal(sub["ids"][::6, ::8], full["ids"][::6, ::8])
+    assert np.array_equal(sub["rgba"][::6, ::8], full["rgba"][::6, ::8])
+    mask = np.ones((H, W), bool)
+    mask[::6, ::8] = False
+    assert (sub["ids"][mask] == -9).all() and (sub["rgba"][mask] == 0).all()
+    again = O.oracle_render(s, cam, W, H, 2, 50, want_ids=True)  # the stride does not stick
+    assert np.array_equal(again["ids"], full["ids"])
+
+
+def test_lens_extension_of_the_oracle():
+    """aperture 0 is the reference camera bit for bit (so the pinned oracle stays pinned); an open lens blurs what is off the
+    focus plane and leaves the mean radiance alone."""
+    s = Scene.generate(capi.SCENE_RTIOW, 1984)
+    W, H = 64, 36
+    cam = s.default_camera(W, H)
+    pin = O.oracle_render(s, cam, W, H, 8, 50)
+    zero = O.oracle_render(s, cam, W, H, 8, 50, lens=(0.0, 10.0))
+    assert np.array_equal(pin["rgba"], zero["rgba"]) and pin["rays"] == zero["rays"]
+    wide = O.oracle_render(s, cam, W, H, 8, 50, lens=(0.6, 10.0))
+    assert not np.array_equal(pin["rgba"], wide["rgba"])
+    assert abs(float(wide["mean"].mean()) - float(pin["mean"].mean())) < 0.05 * float(pin["mean"].mean())
