@@ -19,6 +19,19 @@
 #include <cstring>
 #include <mutex>
 #include <thread>
+
+// NVTX v3 is header-only (the injection library is looked up lazily; without a profiler attached a range costs a load and a
+// branch). Ranges around the phases of a frame: upload / commit / render / close-out / resolve / read-back (SURVEY.md §5 tracing).
+#include <nvtx3/nvToolsExt.h>
+namespace {
+struct NvtxRange
+{
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
+} // namespace
 #include <new>
 #include <string>
 #include <vector>
@@ -469,6 +482,7 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
 // textures of `sd` are on the device), 2 = the scene is in use.
 static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, bool keep_images, bool ploc, int* outcome)
 {
+    NvtxRange nvtx_range("bvh build: GPU LBVH");
     *outcome = 0;
     auto t0 = std::chrono::steady_clock::now();
     std::vector<uint32_t> active;
@@ -720,6 +734,7 @@ crt_status crt_set_bvh_builder(crt_context* ctx, int32_t builder)
 
 crt_status crt_scene_upload(crt_context* ctx, const crt_scene_desc* scene)
 {
+    NvtxRange nvtx_range("crt_scene_upload");
     if (!ctx || !scene) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_scene_upload: NULL argument");
     if ((scene->n_hittables && !scene->hittables) || (scene->n_materials && !scene->materials) || (scene->n_textures && !scene->textures) ||
         (scene->n_images && !scene->images))
@@ -739,10 +754,9 @@ crt_status crt_scene_upload(crt_context* ctx, const crt_scene_desc* scene)
         }
     }
     ctx->scene_hash_valid = false;
-    const uint64_t hits = ctx->stats.cache_hits;
     crt_status st = build_and_upload(ctx, scene, false, "crt_scene_upload");
     if (st != CRT_OK) return st;
-    ctx->stats.cache_hits = hits;
+    ctx->stats.cache_hits = 0;
     ctx->host.hittables.resize(scene->n_hittables);
     parallel_copy(ctx->host.hittables.data(), scene->hittables, scene->n_hittables * sizeof(crt_hittable));
     ctx->host.materials.resize(scene->n_materials);
@@ -819,6 +833,7 @@ crt_status crt_scene_edit_material(crt_context* ctx, uint64_t index, const crt_m
 
 crt_status crt_scene_commit(crt_context* ctx, int force_rebuild, int* out_rebuilt)
 {
+    NvtxRange nvtx_range("crt_scene_commit");
     if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_scene_commit: ctx is NULL");
     if (!ctx->have_scene) return crt_set_error(ctx, CRT_ERR_STATE, "crt_scene_commit: no scene uploaded");
     if (out_rebuilt) *out_rebuilt = 0;
@@ -1377,6 +1392,7 @@ uint32_t crt_row_tiles_rows(uint32_t row_tiles, uint32_t height)
 
 crt_status crt_render(crt_context* ctx, const crt_render_params* p)
 {
+    NvtxRange nvtx_range("crt_render");
     if (!ctx || !p) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_render: NULL argument");
     if (!ctx->have_scene) return crt_set_error(ctx, CRT_ERR_STATE, "crt_render: no scene uploaded");
     if (!ctx->have_cam) return crt_set_error(ctx, CRT_ERR_STATE, "crt_render: no camera set");
@@ -1445,6 +1461,7 @@ crt_status crt_last_render_ms(crt_context* ctx, float* out_ms)
 
 crt_status crt_resolve_device(crt_context* ctx, void* device_out_rgba8)
 {
+    NvtxRange nvtx_range("crt_resolve_device");
     if (!ctx || !device_out_rgba8) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_device: NULL argument");
     if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_resolve_device: no framebuffer");
     CU(cudaSetDevice(ctx->device));
@@ -1457,6 +1474,7 @@ crt_status crt_resolve_device(crt_context* ctx, void* device_out_rgba8)
 
 crt_status crt_resolve_rows(crt_context* ctx, uint32_t row_tiles, void* device_out_rgba8)
 {
+    NvtxRange nvtx_range("crt_resolve_rows");
     if (!ctx || !device_out_rgba8) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_rows: NULL argument");
     if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_resolve_rows: no framebuffer");
     uint32_t tr = 0, rank = 0, world = 0, rows = ctx->height;
@@ -1486,6 +1504,7 @@ crt_status crt_resolve(crt_context* ctx, uint32_t* out_rgba8)
 
 crt_status crt_read_rgba(crt_context* ctx, uint32_t* out_rgba8)
 {
+    NvtxRange nvtx_range("crt_read_rgba");
     if (!ctx || !out_rgba8) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_read_rgba: NULL argument");
     if (!ctx->d_rgba) return crt_set_error(ctx, CRT_ERR_STATE, "crt_read_rgba: no framebuffer");
     CU(cudaSetDevice(ctx->device));
@@ -1566,6 +1585,7 @@ crt_status crt_peer_enable(crt_context* ctx, int32_t peer_device)
 crt_status crt_resolve_peers(crt_context* ctx, const void* const* peer_accum, int32_t n_peers, uint32_t row_begin, uint32_t row_end,
                              void* device_out_rgba8, void* device_out_sum)
 {
+    NvtxRange nvtx_range("crt_resolve_peers (close-out over peer memory)");
     if (!ctx || !peer_accum || !device_out_rgba8) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_peers: NULL argument");
     if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_resolve_peers: no framebuffer");
     if (n_peers < 1 || n_peers > CRT_MAX_PEERS) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_peers: 1 <= n_peers <= 16");

@@ -1,11 +1,14 @@
 /*
- * multigpu_render.cpp — native multi-GPU host over the C ABI (include/crt.h), no Python and no NCCL: ONE process, one host
- * thread and one context per GPU, the frame closed out over peer memory. The reference has no multi-GPU path; this is what a
- * C++ host like CudaLayer would do with the library on an NVSwitch box (bench.py does the same with one PROCESS per GPU and
- * CUDA IPC handles, cudaraytracer_b200/multigpu.py).
+ * multigpu_render.cpp — native multi-GPU host over the C ABI (include/crt.h), no Python: ONE process, one host thread and
+ * one context per GPU. The reference has no multi-GPU path; this is what a C++ host like CudaLayer would do with the library on
+ * an NVSwitch box (bench.py does the same with one PROCESS per GPU, cudaraytracer_b200/multigpu.py).
  *
- *   multigpu_render [n_gpus] [mode: tiles|spp] [scene 1..5] [width] [height] [spp] [max_depth] [out.png]
+ *   multigpu_render [n_gpus] [mode: tiles|spp|nccl] [scene 1..5] [width] [height] [spp] [max_depth] [out.png]
  *
+ * nccl:  north_star's close-out, from C++: GPU g renders samples g, g + G, ... of every pixel into its int64 accumulation
+ *        buffer; ONE ncclReduce(ncclInt64, ncclSum) brings the G buffers to GPU 0, which resolves. Integer sums are exact and
+ *        order-free, so the frame has the bits of the one-GPU frame. (NCCL comes from the system libnccl; only this example
+ *        links it, libcrt.so does not.)
  * tiles: GPU g renders ALL samples of the 16-row slabs g, g + G, ... (crt_render_params::row_tiles) and resolves them straight
  *        into GPU 0's frame (crt_resolve_rows with a peer pointer): nothing to sum, 4 bytes per pixel over NVLink.
  * spp:   GPU g renders samples g, g + G, ... of every pixel; then every GPU sums, for its block of rows, the buffers of all
@@ -13,6 +16,9 @@
  * Either way the frame is bit-identical to what one GPU renders (Philox is keyed by pixel / sample / bounce).
  */
 #include "crt.h"
+
+#include <cuda_runtime.h>
+#include <nccl.h>
 
 #include <atomic>
 #include <condition_variable>
@@ -44,7 +50,9 @@ struct Barrier // std::barrier without <barrier>: every GPU thread arrives, then
 struct Shared
 {
     int G, kind;
-    bool tiles;
+    bool tiles, nccl;
+    std::vector<ncclComm_t> comm;
+    std::vector<cudaStream_t> stream;
     uint32_t W, H, spp, depth;
     std::vector<crt_context*> ctx;
     std::vector<void*> accum, rgba; // device pointers of every context's own buffers
@@ -70,6 +78,11 @@ void gpu_thread(Shared& S, int g)
     crt_input_struct cam;
     STEP(crt_context_create(g, &ctx));
     S.ctx[g] = ctx;
+    if (S.nccl && ctx) { // the render kernels and the reduce share one stream per GPU: stream order is the only synchronisation
+        cudaSetDevice(g);
+        if (cudaStreamCreateWithFlags(&S.stream[g], cudaStreamNonBlocking) != cudaSuccess) ok(S, g, CRT_ERR_CUDA, "cudaStreamCreate");
+        else STEP(crt_set_stream(ctx, S.stream[g]));
+    }
     STEP(crt_scene_generate(S.kind, 1984, 0, &sb));
     if (sb) {
         STEP(crt_scene_upload(ctx, crt_scene_builder_desc(sb))); // the scene is replicated: every GPU builds / uploads its copy
@@ -79,13 +92,28 @@ void gpu_thread(Shared& S, int g)
     STEP(crt_framebuffer_resize(ctx, S.W, S.H));
     if (ctx) { S.accum[g] = crt_accum_device_ptr(ctx); S.rgba[g] = crt_rgba_device_ptr(ctx); }
     S.bar->wait(); // every context exists, every pointer is published
-    for (int o = 0; o < S.G && !S.failed.load(); o++)
+    for (int o = 0; o < S.G && !S.failed.load() && !S.nccl; o++)
         if (o != g && (o == 0 || !S.tiles)) STEP(crt_peer_enable(ctx, o)); // tiles: only GPU 0's frame is addressed remotely
 
     crt_render_params p;
     memset(&p, 0, sizeof(p));
     p.max_depth = S.depth; p.seed = 1984; p.variant = CRT_VARIANT_AUTO; p.jitter = CRT_JITTER_RANDOM;
-    if (S.tiles) {
+    if (S.nccl) {
+        p.spp_begin = (uint32_t)g; p.spp_stride = (uint32_t)S.G;
+        p.spp_count = S.spp > (uint32_t)g ? (S.spp - (uint32_t)g + (uint32_t)S.G - 1) / (uint32_t)S.G : 0;
+        STEP(crt_render(ctx, &p));
+        // the single NCCL reduce of north_star: G x (W x H x 4) int64 -> GPU 0, in place there, on the render stream
+        if (!S.failed.load()) {
+            const size_t count = (size_t)S.W * S.H * 4;
+            cudaSetDevice(g);
+            const ncclResult_t nr = ncclReduce(S.accum[g], S.accum[0], count, ncclInt64, ncclSum, 0, S.comm[g], S.stream[g]);
+            if (nr != ncclSuccess) { ok(S, g, CRT_ERR_CUDA, ncclGetErrorString(nr)); }
+        }
+        if (g == 0) STEP(crt_resolve_device(ctx, S.rgba[0]));
+        STEP(crt_synchronize(ctx));
+        S.bar->wait();
+    }
+    else if (S.tiles) {
         p.spp_begin = 0; p.spp_count = S.spp; p.spp_stride = 1;
         p.row_tiles = CRT_ROW_TILES(g, S.G, 16);
         STEP(crt_render(ctx, &p));
@@ -114,13 +142,21 @@ int main(int argc, char** argv)
 {
     Shared S;
     S.G = argc > 1 ? atoi(argv[1]) : 1;
-    S.tiles = !(argc > 2 && !strcmp(argv[2], "spp"));
+    S.nccl = argc > 2 && !strcmp(argv[2], "nccl");
+    S.tiles = !S.nccl && !(argc > 2 && !strcmp(argv[2], "spp"));
     S.kind = argc > 3 ? atoi(argv[3]) : CRT_SCENE_RTIOW;
     S.W = argc > 4 ? (uint32_t)atoi(argv[4]) : 400; S.H = argc > 5 ? (uint32_t)atoi(argv[5]) : 225;
     S.spp = argc > 6 ? (uint32_t)atoi(argv[6]) : 16; S.depth = argc > 7 ? (uint32_t)atoi(argv[7]) : 50;
     const char* out = argc > 8 ? argv[8] : "frame.png";
     if (S.G < 1 || S.G > 16) { fprintf(stderr, "n_gpus must be 1..16\n"); return 2; }
     S.ctx.assign((size_t)S.G, nullptr); S.accum.assign((size_t)S.G, nullptr); S.rgba.assign((size_t)S.G, nullptr);
+    S.comm.assign((size_t)S.G, nullptr); S.stream.assign((size_t)S.G, nullptr);
+    if (S.nccl) { // one communicator per GPU of this process
+        std::vector<int> devs((size_t)S.G);
+        for (int g = 0; g < S.G; g++) devs[(size_t)g] = g;
+        const ncclResult_t nr = ncclCommInitAll(S.comm.data(), S.G, devs.data());
+        if (nr != ncclSuccess) { fprintf(stderr, "ncclCommInitAll: %s\n", ncclGetErrorString(nr)); return 1; }
+    }
     Barrier bar(S.G);
     S.bar = &bar;
     std::vector<std::thread> pool;
@@ -137,8 +173,14 @@ int main(int argc, char** argv)
             fprintf(stderr, "%s\n", crt_last_error_string(S.ctx[0]));
             rc = 1;
         }
-        else printf("%d GPU(s), %s sharding, %ux%u, %u spp, depth %u: %llu rays -> %s\n", S.G, S.tiles ? "tile" : "spp", S.W, S.H, S.spp, S.depth, rays, out);
+        else printf("%d GPU(s), %s, %ux%u, %u spp, depth %u: %llu rays -> %s\n", S.G,
+                    S.nccl ? "spp sharding + one ncclReduce(int64, sum)" : S.tiles ? "tile sharding" : "spp sharding + peer-memory close-out", S.W, S.H,
+                    S.spp, S.depth, rays, out);
     }
     for (crt_context* c : S.ctx) crt_context_destroy(c);
+    for (int g = 0; g < S.G; g++) {
+        if (S.comm[(size_t)g]) ncclCommDestroy(S.comm[(size_t)g]);
+        if (S.stream[(size_t)g]) { cudaSetDevice(g); cudaStreamDestroy(S.stream[(size_t)g]); }
+    }
     return rc;
 }

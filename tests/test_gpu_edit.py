@@ -175,8 +175,9 @@ def test_unchanged_scene_upload_is_a_cache_hit_and_any_change_is_not():
 def test_refit_path_validates_the_material_it_packs():
     """a hittable re-pointed (no topology change) at a material that no active hittable used at upload, whose texture
     chain is broken, must be refused by crt_scene_commit instead of being packed (out-of-bounds reads on host and device)."""
-    hs = [dict(type=capi.SPHERE, cx=0.0, cy=-100.5, cz=-1.0, a=100.0, material=0), dict(type=capi.SPHERE, cx=0.0, cy=0.0, cz=-1.0, a=0.5, material=0),
-          dict(type=capi.SPHERE, cx=1.0, cy=0.0, cz=-1.0, a=0.5, material=0)]
+    hs = [dict(type=capi.SPHERE, active=1, cx=0.0, cy=-100.5, cz=-1.0, a=100.0, b=0.0, material=0),
+          dict(type=capi.SPHERE, active=1, cx=0.0, cy=0.0, cz=-1.0, a=0.5, b=0.0, material=0),
+          dict(type=capi.SPHERE, active=1, cx=1.0, cy=0.0, cz=-1.0, a=0.5, b=0.0, material=0)]
     ms = [dict(type=capi.LAMBERTIAN, texture=0), dict(type=capi.LAMBERTIAN, texture=7),   # texture index out of range, unused
           dict(type=capi.LAMBERTIAN, texture=1)]                                         # image index out of range, unused
     ts = [dict(type=capi.CONSTANT, color=(0.5, 0.5, 0.5)), dict(type=capi.IMAGE, image=3)]

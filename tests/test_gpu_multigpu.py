@@ -160,8 +160,6 @@ print("sha1", hashlib.sha1(img.tobytes()).hexdigest())
 """
 
 
-@pytest.mark.skipif(not os.environ.get("CRT_TEST_EXPERIMENTAL"), reason="two-process CUDA IPC on one GPU: harness not yet run on a B200 "
-                    "(the same entry points are exercised across two GPUs by tools/peer_check.py); CRT_TEST_EXPERIMENTAL=1 runs it")
 def test_ipc_export_open_close_across_processes():
     """crt_ipc_export in this process, crt_ipc_open + crt_resolve_peers in a child process on the same GPU."""
     import hashlib
@@ -181,23 +179,45 @@ def test_ipc_export_open_close_across_processes():
     r.close()
 
 
-@pytest.mark.skipif(not os.environ.get("CRT_TEST_EXPERIMENTAL"), reason="examples/multigpu_render.cpp has not run on a B200 yet "
-                    "(its entry points have, one by one); CRT_TEST_EXPERIMENTAL=1 runs it")
 def test_native_multigpu_host_example(tmp_path):
-    """examples/multigpu_render.cpp on every GPU of the box, tile- and spp-sharded: the PNG must be byte-identical to the
-    one-GPU frame (one GPU: the two modes and the peer close-out with a single buffer)."""
+    """examples/multigpu_render.cpp (C++ over the C ABI, one thread per GPU) on one GPU and on every GPU of the box, with each of
+    its close-outs - ONE ncclReduce(ncclInt64, ncclSum) to GPU 0 issued from C++ (north_star), the peer-memory sum + resolve
+    (crt_peer_enable + crt_resolve_peers), image tiles (crt_resolve_rows into GPU 0's frame): every PNG byte-identical to the
+    one-GPU frame."""
     import subprocess
     import torch
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     exe = os.path.join(root, "examples", "multigpu_render")
     G = torch.cuda.device_count()
     files = []
-    for g, mode in [(1, "tiles"), (1, "spp"), (G, "tiles"), (G, "spp")]:
-        out = str(tmp_path / f"f_{g}_{mode}.png")
-        r = subprocess.run([exe, str(g), mode, "1", "200", "113", "6", "50", out], capture_output=True, text=True, timeout=300)
-        assert r.returncode == 0, r.stderr
-        files.append(open(out, "rb").read())
-    assert files[0].startswith(b"\x89PNG") and all(f == files[0] for f in files[1:])
+    for g in sorted({1, G}):
+        for mode in ("nccl", "spp", "tiles"):
+            out = str(tmp_path / f"f_{g}_{mode}.png")
+            r = subprocess.run([exe, str(g), mode, "1", "200", "113", "6", "50", out], capture_output=True, text=True, timeout=300)
+            assert r.returncode == 0, (g, mode, r.stdout, r.stderr)
+            files.append(((g, mode), open(out, "rb").read()))
+    assert files[0][1].startswith(b"\x89PNG")
+    for key, f in files[1:]:
+        assert f == files[0][1], f"{key} differs from {files[0][0]}"
+
+
+def test_close_outs_across_real_gpus_under_torchrun():
+    """tools/peer_check.py as a gated test: one process per GPU (torchrun, NCCL), the three close-outs of bench.py - NCCL reduce
+    + resolve, the peer-memory kernel, image tiles - must give one frame, identical to what one GPU renders alone. Needs two
+    GPUs; the one-GPU box of the default run skips it (tests/test_multigpu_cpu.py covers the shard arithmetic on gloo)."""
+    import subprocess
+    import sys
+    import torch
+    G = torch.cuda.device_count()
+    if G < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for scene, W, H, spp in (("rtiow", 640, 360, 2 * G + 1), ("stress", 320, 200, G)):
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={G}", "--master-addr", "127.0.0.1",
+               "--master-port", "29541", os.path.join(root, "tools", "peer_check.py"), str(W), str(H), str(spp), scene]
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+        assert "frames identical (peer == nccl == tiles == one GPU): True" in r.stdout
 
 
 def test_c_host_example_renders_a_ppm(tmp_path):

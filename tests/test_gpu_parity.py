@@ -166,8 +166,17 @@ def test_thin_lens_aperture_zero_is_the_pinhole_and_defocus_matches_the_oracle(r
         floor = _rmse(a, b)
         got = max(_rmse(new, a), _rmse(new, b))
         assert got <= 1.25 * floor, f"lens: RMSE new-vs-oracle {got:.5f} vs noise floor {floor:.5f}"
-        # the blur is really there: the lens image is further from the pinhole image than the noise floor explains
-        assert _rmse(new, pinhole) > 1.5 * floor, (_rmse(new, pinhole), floor)
+        # the blur is really there (aperture 0.1 is subtle at this size, so look at a wide lens): the wide-lens image follows the
+        # oracle's wide-lens image, block mean for block mean, and is far from the pinhole image
+        wide = (1.0, 10.0)
+        renderer.set_lens(*wide)
+        renderer.clear()
+        renderer.render(spp=spp, max_depth=depth)
+        acc_w = renderer.read_accum()
+        new_w = _block_mean(np.clip(acc_w[..., :3] / acc_w[..., 3:4], 0, 4), 8)
+        ora_w = _block_mean(np.clip(O.oracle_render(s, cam, W, H, spp, depth, lens=wide)["mean"], 0, 4), 8)
+        pin_b = _block_mean(pinhole, 8)
+        assert _rmse(new_w, ora_w) < 0.5 * _rmse(new_w, pin_b), (_rmse(new_w, ora_w), _rmse(new_w, pin_b))
         nb, ab, bb = _block_mean(new, 8), _block_mean(a, 8), _block_mean(b, 8)
         sigma = max(_rmse(ab, bb), 1e-6)
         bias = float(np.abs((nb - 0.5 * (ab + bb)).mean(axis=(0, 1))).max())
