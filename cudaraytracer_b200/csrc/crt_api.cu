@@ -1338,6 +1338,8 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
     W.shards = ctx->d_shards;
     W.stat = ctx->d_counters;
     W.n_pixels_cover = (uint32_t)P;
+    W.inv_pixels = ~0ull / P + 1ull; // pipe_item: division by multiplication (d == 1 is special-cased there)
+    W.inv_cover_w = ~0ull / A.cover_w + 1ull;
     W.n_slots = n_slots;
     W.thresh = ctx->pipe_thresh > 0 ? std::min(ctx->pipe_thresh, 32) : (all ? 14 : 1);
     // Scene entirely in shared memory: the kernel is issue-bound, lanes are refilled as soon as 18 of 32 are idle (sweep 6..24:

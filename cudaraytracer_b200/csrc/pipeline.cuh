@@ -31,6 +31,7 @@ struct PipeArgs
     WfShard* shards;         // WF_SHARDS global work counters over the (pixel, sample) items of this launch
     DevCounters* stat;       // CRT_COUNTER_SHARDS ray/path counters
     uint32_t n_pixels_cover; // work item w -> sample w / n_pixels_cover, pixel w % n_pixels_cover
+    unsigned long long inv_pixels, inv_cover_w; // floor(2^64 / d) + 1: w / d == umul64hi(w, inv) for every 32-bit w (pipe_item)
     int n_slots;             // N, a power of two
     int thresh;              // traversal leaves its loop when fewer lanes than this are busy (a refill is due)
     int max_rounds;          // traversal rounds between two refills at most
@@ -43,7 +44,6 @@ struct PipeCtl
     unsigned int head[PQ_COUNT + 1];
     unsigned int tail[PQ_COUNT + 1];
     int live; // slots not yet retired; the CTA exits at 0
-    unsigned int n_rays, n_paths; // this CTA's ray / path counts: one shared atomic per batch instead of two registers per thread
 };
 
 struct PipePool
@@ -147,8 +147,10 @@ __device__ __forceinline__ int pipe_pop(const PipePool& P, PipeCtl* ctl, int q, 
 
 __device__ __forceinline__ void pipe_item(const PipeArgs& A, uint32_t w, int& x, int& y, uint32_t& pixel, uint32_t& sample)
 {
-    const uint32_t s = w / A.n_pixels_cover, q = w - s * A.n_pixels_cover;
-    const int lr = (int)(q / A.R.cover_w);
+    // two divisions by launch constants per generated path were 1.2 % of all instructions (profiles/r02_f): multiply instead
+    // (inv = floor((2^64 - 1) / d) + 1 is exact for 2 <= d < 2^32 and every 32-bit dividend; d == 1 has no such multiplier)
+    const uint32_t s = A.n_pixels_cover == 1u ? w : (uint32_t)__umul64hi((unsigned long long)w, A.inv_pixels), q = w - s * A.n_pixels_cover;
+    const int lr = A.R.cover_w == 1u ? (int)q : (int)__umul64hi((unsigned long long)q, A.inv_cover_w);
     x = (int)(q - (uint32_t)lr * A.R.cover_w);
     y = crt_image_row(A.R.tile_rows, A.R.tile_rank, A.R.tile_world, lr);
     pixel = (uint32_t)y * A.R.width + (uint32_t)x;
@@ -217,15 +219,11 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
             }
             done += g;
         }
-        if (lane == 0) {
-            if (done > 0) atomicAdd(&ctl->n_paths, (unsigned)done);
-            if (done < n) atomicSub(&ctl->live, n - done); // no work left: these slots retire
-        }
+        if (lane == 0 && done < n) atomicSub(&ctl->live, n - done); // no work left: these slots retire
             pipe_push(P, ctl, PQ_EXT, started, slot, lt);
         return;
     }
     bool alive = false, ended = false;
-    if (lane == 0) atomicAdd(&ctl->n_rays, (unsigned)n);
     if (mine) {
         const float4 a0 = P.a[slot], b0 = P.b[slot], c0 = P.c[slot];
         const uint2 ps = P.px[slot];
@@ -279,7 +277,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
     const SceneView S = stage_scene<true, PAIR>(A.R.scene, smem + (3 * P.n + P.n / 2) + (PQ_COUNT * P.n) / 8);
     for (int i = threadIdx.x; i < PQ_COUNT * P.n; i += PIPE_THREADS) P.ring[i] = (unsigned short)(i >= PQ_GEN * P.n ? i - PQ_GEN * P.n : PIPE_EMPTY);
     if (threadIdx.x <= PQ_COUNT) { ctl.head[threadIdx.x] = 0u; ctl.tail[threadIdx.x] = threadIdx.x == PQ_GEN ? (unsigned int)P.n : 0u; }
-    if (threadIdx.x == 0) { ctl.live = P.n; ctl.n_rays = 0u; ctl.n_paths = 0u; } // every slot starts in the GEN queue
+    if (threadIdx.x == 0) ctl.live = P.n; // every slot starts in the GEN queue
     __syncthreads();
 
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, lt = (1u << lane) - 1u;
@@ -382,11 +380,14 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
             if (fin) slot = -1;
         }
     }
-    // ray / path counters of the CTA into one of the counter shards
+    // Ray / path counters of the CTA, read off the queues instead of being counted: every ray is popped once from one of the
+    // five class queues when it is shaded, and every path ends exactly once, by a push into GEN (which started with N entries).
     __syncthreads();
     if (threadIdx.x == 0) {
+        unsigned long long rays = 0;
+        for (int q = PQ_MISS; q <= PQ_LIGHT; q++) rays += ctl.head[q];
         DevCounters* c = A.stat + (blockIdx.x & (CRT_COUNTER_SHARDS - 1));
-        atomicAdd(&c->paths, (unsigned long long)ctl.n_paths);
-        atomicAdd(&c->rays, (unsigned long long)ctl.n_rays);
+        atomicAdd(&c->paths, (unsigned long long)(ctl.tail[PQ_GEN] - (unsigned int)P.n));
+        atomicAdd(&c->rays, rays);
     }
 }

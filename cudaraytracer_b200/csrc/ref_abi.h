@@ -4,8 +4,9 @@
 //   Hittables/Hittable.cuh:47-67 (Hittable), :69-78 (Sphere), :128-137 (XYRect; XZRect/YZRect identical),
 //   :296-301,467 (BVHNode), Hittables/AABB.cuh:5-9, Hittables/Material.cuh:19-32,34-41,65-73,97-104,148-156,
 //   Hittables/Texture.cuh:18-30,32-40,47-56,70-81,106-108, Utils/Math.cuh:94 (Vec3 = float e[3]).
-// tests/test_ref_abi.py compiles a probe that includes BOTH this file and the reference headers and
-// static_asserts every sizeof/offsetof below (runs only where /root/reference is present).
+// oracle/ref_abi_probe.cpp includes BOTH this file and the reference headers and static_asserts every sizeof / offsetof
+// below against the real classes; tests/test_ref_abi.py compiles it (where /root/reference is present), and so does
+// `make -C oracle ref`.
 #pragma once
 
 #include <cstddef>
@@ -47,6 +48,12 @@ struct BVHNode
     Hittable* left;
     Hittable* right;
     char* memory;
+};
+
+struct HittableList // Hittable.cuh:532-581: every element is treated as a BVHNode hittable (its Hit calls list[i]->Object->bvh_node)
+{
+    Hittable** list;
+    int list_size;
 };
 
 struct Texture
@@ -92,6 +99,7 @@ static_assert(sizeof(Hittable) == 16 && offsetof(Hittable, Object) == 8, "Hittab
 static_assert(sizeof(Sphere) == 24 && offsetof(Sphere, mat_ptr) == 16, "Sphere");
 static_assert(sizeof(Rect) == 32 && offsetof(Rect, mat_ptr) == 24, "Rect");
 static_assert(sizeof(BVHNode) == 48 && offsetof(BVHNode, left) == 24, "BVHNode");
+static_assert(sizeof(HittableList) == 16 && offsetof(HittableList, list_size) == 8, "HittableList");
 static_assert(sizeof(Material) == 16 && sizeof(Texture) == 16, "Material/Texture");
 static_assert(sizeof(Constant) == 16 && sizeof(Checker) == 16 && sizeof(Image) == 32, "textures");
 static_assert(sizeof(Metal) == 16 && sizeof(DiffuseLight) == 16, "materials");

@@ -149,12 +149,30 @@ struct Walker
 bool crt_flatten_reference_world(const void* world, CrtFlatScene* out, std::string* err)
 {
     const ref_abi::Hittable* w = (const ref_abi::Hittable*)world;
-    if (w->type != ref_abi::HT_BVHNODE) {
-        *err = "reference scene: world must be a Hittable of type BVHNODE (Kernel.cu:40)";
-        return false;
-    }
     Walker W;
     W.out = out;
     W.err = err;
+    if (w->type == ref_abi::HT_HITTABLELIST) {
+        // HittableList::Hit (Hittable.cuh:545-560) takes the closest hit over its elements and treats every one of them as a
+        // BVHNode hittable: the scene is the union of the hittables under those trees
+        const ref_abi::HittableList* l = w->Object ? (const ref_abi::HittableList*)*w->Object : nullptr;
+        if (!l || l->list_size < 0 || (l->list_size > 0 && !l->list)) {
+            *err = "reference scene: HittableList without a list";
+            return false;
+        }
+        for (int i = 0; i < l->list_size; i++) {
+            const ref_abi::Hittable* e = l->list[i];
+            if (!e || e->type != ref_abi::HT_BVHNODE) {
+                *err = "reference scene: the elements of a HittableList must be BVHNode hittables (Hittable.cuh:552)";
+                return false;
+            }
+            if (!W.walk(e)) return false;
+        }
+        return true;
+    }
+    if (w->type != ref_abi::HT_BVHNODE) {
+        *err = "reference scene: world must be a Hittable of type BVHNODE (Kernel.cu:40) or HITTABLELIST (Hittable.cuh:532-581)";
+        return false;
+    }
     return W.walk(w);
 }

@@ -278,6 +278,24 @@ void* refhost_world_list(void* handle)
 {
     return handle ? (void*)((RefScene*)handle)->list : nullptr;
 }
+// The same world behind a HittableList root (Hittable.cuh:532-581): a list whose single element is the BVH root hittable.
+// For the drop-in test of crt_scene_from_reference / LaunchKernel with a list root. Freed with the process.
+void* refhost_world_list_root(void* handle)
+{
+    if (!handle) return nullptr;
+    RefScene* rs = (RefScene*)handle;
+    struct Wrap { char h[sizeof(Hittable)]; Hittable::ObjectUnion u; char l[sizeof(HittableList)]; Hittable* elems[1]; };
+    Wrap* w = (Wrap*)calloc(1, sizeof(Wrap));
+    if (!w) return nullptr;
+    w->elems[0] = rs->world;
+    HittableList* l = new (w->l) HittableList(w->elems, 1);
+    w->u.hittable_list = l;
+    Hittable* h = (Hittable*)w->h;
+    h->type = HittableType::HITTABLELIST;
+    h->isActive = true;
+    h->Object = &w->u;
+    return h;
+}
 void refhost_world_destroy(void* handle)
 {
     if (!handle) return;

@@ -166,5 +166,13 @@ def refhost_world(scene):
     return h, lib.refhost_world_root(h)
 
 
+def refhost_world_list_root(handle):
+    """The same world behind a HittableList root (Hittable.cuh:532-581)."""
+    lib = refhost()
+    lib.refhost_world_list_root.restype = C.c_void_p
+    lib.refhost_world_list_root.argtypes = [C.c_void_p]
+    return lib.refhost_world_list_root(handle)
+
+
 def refhost_world_destroy(handle):
     refhost().refhost_world_destroy(handle)
