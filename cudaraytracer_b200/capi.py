@@ -17,6 +17,7 @@ CRT_OK, CRT_ERR_INVALID, CRT_ERR_CUDA, CRT_ERR_NOMEM, CRT_ERR_UNSUPPORTED, CRT_E
 SPHERE, XYRECT, XZRECT, YZRECT = 0, 1, 2, 3
 LAMBERTIAN, METAL, DIELECTRIC, DIFFUSELIGHT = 0, 1, 2, 3
 CONSTANT, CHECKER, IMAGE = 0, 1, 2
+STATIC_ACCUM_MAX_PIXELS = 262144  # CRT_STATIC_ACCUM_MAX_PIXELS, include/crt.h
 BUILDER_AUTO, BUILDER_HOST_SAH, BUILDER_GPU_LBVH, BUILDER_GPU_PLOC = 0, 1, 2, 3
 VARIANT_AUTO, VARIANT_MEGAKERNEL, VARIANT_WAVEFRONT, VARIANT_PIPELINE = 0, 1, 2, 3
 JITTER_RANDOM, JITTER_CENTER = 0, 1
@@ -123,6 +124,7 @@ SIGNATURES = {
     "crt_resolve": (C.c_int, [_P, _P]),
     "crt_resolve_device": (C.c_int, [_P, _P]),
     "crt_read_accum": (C.c_int, [_P, _P]),
+    "crt_read_accum_static": (C.c_int, [_P, _P, C.c_uint32, _P]),
     "crt_resolve_rows": (C.c_int, [_P, C.c_uint32, _P]),
     "crt_row_tiles_rows": (C.c_uint32, [C.c_uint32, C.c_uint32]),
     "crt_read_rgba": (C.c_int, [_P, _P]),

@@ -1783,3 +1783,66 @@ crt_status crt_write_png(const char* path, const uint32_t* rgba8, uint32_t width
 }
 
 } // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// crt_read_accum_static: crt_read_accum for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc). No counterpart in the reference.
+//
+// crt_read_accum converts the fixed-point buffer into a staging array that crt_framebuffer_resize cudaMalloc'ed (d_accum_f) and
+// copies that to the host. Here the staging array is a file-scope __device__ array of CRT_STATIC_ACCUM_MAX_PIXELS float4
+// (4 MiB; every GPU that loads libcrt.so holds it until the process exits), and the call uses no cudaMalloc, cudaFree or
+// allocating library routine.
+//   * In HOST code the name g_static_accum_stage is a host-side stand-in for the symbol, NOT a device address: a kernel given
+//     it faults, or - where the GPU can reach host memory - silently reads and writes the wrong memory. Its device address is
+//     asked for once per device, with that device current, by cudaGetSymbolAddress, and that pointer is what the kernel gets.
+//   * Every call shares the one array, and the array keeps the last call's contents. Nothing in it has to start at zero: the
+//     kernel overwrites entries [0, n_pixels) before the copy reads exactly that range. Two calls that OVERLAP on one GPU
+//     (different streams, or different host threads) race on the array; calls on one stream are ordered and safe.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) float4 g_static_accum_stage[CRT_STATIC_ACCUM_MAX_PIXELS];
+
+// the variant of k_accum_to_float (kernels.cuh) that writes into the static staging array
+__global__ void k_accum_to_float_static(const long long* __restrict__ accum, float4* __restrict__ stage, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const longlong2* px = reinterpret_cast<const longlong2*>(accum + 4 * (size_t)i);
+    const longlong2 rg = px[0], bn = px[1];
+    stage[i] = make_float4(crt_from_fixed(rg.x), crt_from_fixed(rg.y), crt_from_fixed(bn.x), (float)bn.y);
+}
+
+// Device address of the staging array on `device` (which must be current): looked up once per device.
+static cudaError_t static_accum_stage_ptr(int device, float4** out)
+{
+    static std::mutex mu;
+    static float4* ptr[CRT_MAX_DEVICES] = {};
+    if (device < 0 || device >= CRT_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[device]) {
+        float4* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_static_accum_stage);
+        if (e != cudaSuccess) return e;
+        ptr[device] = p;
+    }
+    *out = ptr[device];
+    return cudaSuccess;
+}
+
+extern "C" crt_status crt_read_accum_static(crt_context* ctx, const void* device_accum_int64x4, uint32_t n_pixels, float* out_float4)
+{
+    if (!ctx || !device_accum_int64x4 || !out_float4) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_read_accum_static: NULL argument");
+    if (n_pixels > (uint32_t)CRT_STATIC_ACCUM_MAX_PIXELS)
+        return crt_set_error(ctx, CRT_ERR_INVALID, "crt_read_accum_static: n_pixels exceeds CRT_STATIC_ACCUM_MAX_PIXELS (262144), the size of the "
+                                                  "static staging array; use crt_read_accum, or read the buffer in pieces");
+    if (n_pixels == 0) return CRT_OK;
+    if (((uintptr_t)device_accum_int64x4 & 15u) != 0) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_read_accum_static: the buffer must be 16-byte aligned");
+    CU(cudaSetDevice(ctx->device));
+    float4* stage = nullptr;
+    CU(static_accum_stage_ptr(ctx->device, &stage)); // NOT g_static_accum_stage itself: that name is a host-side stand-in here
+    k_accum_to_float_static<<<(n_pixels + 255) / 256, 256, 0, ctx->stream>>>((const long long*)device_accum_int64x4, stage, n_pixels);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(out_float4, stage, (size_t)n_pixels * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return CRT_OK;
+}

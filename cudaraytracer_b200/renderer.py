@@ -276,6 +276,15 @@ class Renderer:
         self._ck(self.lib.crt_read_accum(self.ctx, out.ctypes.data_as(C.c_void_p)))
         return out
 
+    def read_accum_static(self, device_ptr: int = 0, n_pixels: int = None) -> np.ndarray:
+        """crt_read_accum_static: the float4 view of n_pixels entries of an int64x4 accumulation buffer (default: this renderer's
+        own buffer, all of it) through the library's STATIC staging array - no allocation on the device side of the call."""
+        n = self.width * self.height if n_pixels is None else int(n_pixels)
+        out = np.empty((n, 4), dtype=np.float32)
+        ptr = device_ptr or self.accum_ptr()
+        self._ck(self.lib.crt_read_accum_static(self.ctx, C.c_void_p(ptr), n, out.ctypes.data_as(C.c_void_p)))
+        return out
+
     def primary_ids(self, jitter: int = capi.JITTER_CENTER, seed: int = 1984) -> np.ndarray:
         out = np.empty((self.height, self.width), dtype=np.int32)
         self._ck(self.lib.crt_primary_ids(self.ctx, jitter, seed, out.ctypes.data_as(C.c_void_p)))

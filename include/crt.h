@@ -221,6 +221,17 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* params);
 crt_status crt_resolve(crt_context* ctx, uint32_t* out_rgba8);
 crt_status crt_resolve_device(crt_context* ctx, void* device_out_rgba8); /* async */
 crt_status crt_read_accum(crt_context* ctx, float* out_float4);          /* width*height*4 floats, synchronises */
+/* crt_read_accum for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc). NO COUNTERPART IN THE REFERENCE. Converts n_pixels entries of the
+ * int64x4 accumulation buffer at device_accum_int64x4 (device memory of ctx's GPU, 16-byte aligned; e.g. crt_accum_device_ptr
+ * or a caller-owned buffer, or a sub-range of one) to float4 {sum r, g, b, samples} in HOST memory at out_float4, exactly as
+ * crt_read_accum does, and synchronises ctx's stream. The staging array is a static __device__ array inside libcrt.so of
+ * CRT_STATIC_ACCUM_MAX_PIXELS float4 (4 MiB on every GPU that loads the library, until the process exits): the call uses no
+ * cudaMalloc, cudaFree or allocating library routine. More pixels than that: CRT_ERR_INVALID (read the buffer in pieces).
+ * All calls share the one array, which keeps the last call's contents (nothing in it needs clearing: entries [0, n_pixels)
+ * are overwritten before they are read). Calls that OVERLAP on one GPU - different streams or host threads - race on it. */
+#define CRT_STATIC_ACCUM_MAX_PIXELS 262144
+crt_status crt_read_accum_static(crt_context* ctx, const void* device_accum_int64x4, uint32_t n_pixels, float* out_float4);
 /* Resolve only the rows of a row-tile shard (row_tiles as in crt_render_params; 0 = all rows) from this context's accumulation
  * buffer into the frame at device_out_rgba8 (pixel 0 of a full frame; may be a peer mapping of another GPU's frame). Async. */
 crt_status crt_resolve_rows(crt_context* ctx, uint32_t row_tiles, void* device_out_rgba8);
