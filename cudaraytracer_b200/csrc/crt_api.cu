@@ -1354,6 +1354,10 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
         W.R.spp_begin = A.spp_begin + done * stride;
         W.R.spp_count = spp;
         W.R.spp_stride = stride;
+        // Three launches per pass. Folding the two small ones into the render kernel (work counters reset by the last CTA to exit,
+        // sample counts added at kernel start) was built and measured in round 2: the C1 step did not move (0.490 vs 0.493 ms: that
+        // frame is bound by the fill and drain of the path pool, not by launches), and the __threadfence() the exit ticket needs
+        // made ptxas turn every accumulation RED of the kernel into an ATOM with a discarded result: -3.4 % on C2. Dropped.
         k_pipe_init<<<1, WF_SHARDS, 0, ctx->stream>>>(ctx->d_shards, (uint32_t)(P * spp));
         CU(cudaGetLastError());
         CU(dispatch_pipe(W, ctx->sm_count, smem, ctx->stream, all));
@@ -1425,6 +1429,17 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
     const bool exact = (p->flags & CRT_FLAG_EXACT_MATH) != 0, count = (p->flags & CRT_FLAG_COUNT_TESTS) != 0;
 
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    if (p->max_depth == 0 && p->spp_count > 0 && A.cover_w > 0 && A.cover_h > 0) {
+        // color() with max_depth 0 (Kernel.cu:39: the bounce loop runs zero times; :79 returns black) traces nothing: every
+        // sample is black. The samples still count: the frame resolves to opaque black, as the reference's does.
+        const uint32_t npx = A.cover_w * A.cover_h;
+        k_wf_add_count<<<(npx + 255) / 256, 256, 0, ctx->stream>>>(A.accum, A.width, A.cover_w, A.cover_h, (long long)p->spp_count, A.tile_rows, A.tile_rank, A.tile_world);
+        ctx->launches++;
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(ctx->ev1, ctx->stream));
+        ctx->timed = true;
+        return CRT_OK;
+    }
     if (p->spp_count > 0 && A.cover_w > 0 && A.cover_h > 0) {
         // AUTO, chosen by measurement (DESIGN.md "variant choice"): the pipelined persistent kernel wins as soon as traversal
         // dominates (RTIOW 486 prims: 13.0 vs 11.5 Grays/s; 10k prims: 7.5 vs 5.4); below a few hundred primitives its

@@ -183,6 +183,19 @@ __device__ __forceinline__ float fast_rcp(float x) { float r; asm("rcp.approx.ft
 __device__ __forceinline__ float fast_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 #endif
 __device__ __forceinline__ float fast_div(float a, float b) { return __fdividef(a, b); }
+// float -> int as the GPU converts it (cvt.rzi.s32.f32: NaN -> 0, saturating); the host build of the same code (tests/sim) must
+// not run into x86's undefined conversion of a NaN
+__device__ __forceinline__ int crt_f2i(float x)
+{
+#ifdef CRT_HOST_SIM
+    if (!(x == x)) return 0;
+    if (x >= 2147483648.0f) return 2147483647;
+    if (x <= -2147483648.0f) return -2147483647 - 1;
+    return (int)x;
+#else
+    return __float2int_rz(x);
+#endif
+}
 
 // IEEE, never-contracted versions used by the exact path (bit-for-bit the host oracle's arithmetic).
 __device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }

@@ -89,10 +89,14 @@ __device__ __forceinline__ float3 image_value(const DevImage* images, int image_
     if (image_plus1 == 0)
         return f3(0.f, 1.f, 1.f);
     DevImage im = images[image_plus1 - 1];
-    u = fminf(fmaxf(u, 0.0f), 1.0f);
-    v = 1.0f - fminf(fmaxf(v, 0.0f), 1.0f);
-    int i = (int)(u * (float)im.width);
-    int j = (int)(v * (float)im.height);
+    // Clamp of Math.cuh:307-310 is (x < a) ? a : ((x > b) ? b : x): a NaN passes THROUGH it (fminf / fmaxf would drop it). At a
+    // sphere pole |n.y| can round above 1, acos gives NaN, v = 1 - NaN stays NaN and the GPU's float -> int conversion makes it
+    // row 0 (Texture.cuh:88-89): the same texel the reference kernel and the oracle (f2i_gpu) fetch there.
+    u = (u < 0.0f) ? 0.0f : ((u > 1.0f) ? 1.0f : u);
+    v = (v < 0.0f) ? 0.0f : ((v > 1.0f) ? 1.0f : v);
+    v = 1.0f - v;
+    int i = crt_f2i(u * (float)im.width);
+    int j = crt_f2i(v * (float)im.height);
     if (i >= im.width) i = im.width - 1;
     if (j >= im.height) j = im.height - 1;
     uchar4 p = __ldg(im.texels + (size_t)j * im.width + i);

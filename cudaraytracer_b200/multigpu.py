@@ -72,7 +72,12 @@ class PeerFrame:
     that sums the rows this rank owns over all ranks' buffers (int64: the same bits as the NCCL sum), resolves them and stores
     the packed pixels into the root's frame over NVLink. Two one-element all-reduces on the launching stream order it after
     every rank's render and before anybody's next clear; nothing synchronises with the host. torch.distributed stays the
-    plumbing (handle exchange, the two stream-ordered barriers); the data moves inside our kernel."""
+    plumbing (handle exchange, the two stream-ordered barriers); the data moves inside our kernel.
+
+    PRECONDITION: the renderer runs on torch's CURRENT stream - renderer.set_stream(torch.cuda.current_stream().cuda_stream)
+    before constructing this, and the same stream current at every close_frame*(). The fences are all-reduces on torch's current
+    stream; with the render / resolve kernels on another stream they would order nothing, and a rank could read a peer's buffer
+    while that peer is still rendering into it (or clearing it for the next frame). Checked at construction and at every fence."""
 
     def __init__(self, renderer, rank: int, world: int, dst: int = 0, group=None):
         import torch
@@ -80,6 +85,7 @@ class PeerFrame:
         from . import capi
 
         self.r, self.rank, self.world, self.dst, self.group = renderer, rank, world, dst, group
+        self._check_stream()
         self.rows = row_shard(rank, world, renderer.height)
         mine = (renderer.ipc_export(capi.BUFFER_ACCUM), renderer.ipc_export(capi.BUFFER_RGBA) if rank == dst else b"")
         handles = [None] * world
@@ -100,9 +106,17 @@ class PeerFrame:
         self.out_ptr = mapped(handles[dst][1], renderer.rgba_ptr(), dst)
         self._token = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", torch.cuda.current_device()))
 
+    def _check_stream(self):
+        import torch
+        cur = int(torch.cuda.current_stream().cuda_stream)
+        if self.r.stream_handle is None or int(self.r.stream_handle) != cur:
+            raise RuntimeError("PeerFrame: the renderer must run on torch's current stream (renderer.set_stream(torch.cuda.current_stream()"
+                               ".cuda_stream)): the stream-ordered fences are issued there and would not order kernels on another stream")
+
     def _fence(self):
         """Stream-ordered barrier: completes on this rank's stream only after every rank's earlier work on its stream."""
         import torch.distributed as dist
+        self._check_stream()
         if self.world > 1:
             dist.all_reduce(self._token, group=self.group)
 

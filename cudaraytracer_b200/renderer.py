@@ -154,11 +154,14 @@ class Renderer:
         except Exception:
             pass
 
+    stream_handle = None
+
     def _ck(self, st):
         _check(st, self.ctx)
 
     def set_stream(self, cuda_stream: int):
         self._ck(self.lib.crt_set_stream(self.ctx, C.c_void_p(cuda_stream)))
+        self.stream_handle = int(cuda_stream)  # None until set: the context then runs on its own non-blocking stream
 
     def set_bvh_builder(self, builder: int):
         """capi.BUILDER_AUTO / BUILDER_HOST_SAH (threaded SAH on the host) / BUILDER_GPU_LBVH (Morton LBVH on the device)."""

@@ -281,6 +281,16 @@ def test_max_depth_one_and_truncated_grid(renderer):
             interior &= (pad[dy:dy + H, dx:dx + W] >= 0)
     assert interior.any() and (acc[..., :3][interior] == 0).all()
     assert (acc[..., :3][ids < 0].sum(axis=-1) > 0).mean() > 0.9
+    # depth 0: color()'s loop runs zero times (Kernel.cu:39) and returns black without tracing; the samples still count
+    for variant in (capi.VARIANT_AUTO, capi.VARIANT_MEGAKERNEL, capi.VARIANT_PIPELINE, capi.VARIANT_WAVEFRONT):
+        renderer.clear()
+        renderer.reset_counters()
+        renderer.render(spp=3, max_depth=0, variant=variant)
+        acc = renderer.read_accum()
+        assert (acc[..., :3] == 0).all() and (acc[..., 3] == 3).all() and renderer.counters().rays == 0
+        assert (renderer.resolve() == 0xFF000000).all()
+    ref0 = O.oracle_render(s, cam, W, H, 3, 0)
+    assert (ref0["rgba"] == 0xFF000000).all() and ref0["rays"] == 0
     renderer.clear()
     renderer.render(spp=1, max_depth=5, flags=capi.FLAG_TRUNCATED_GRID)  # Kernel.cu:183-184: 48 x 32 covered
     acc = renderer.read_accum()

@@ -111,3 +111,46 @@ def test_legacy_launchkernel_drop_in():
     finally:
         lib.crt_legacy_shutdown()
         O.refhost_world_destroy(handle)
+
+
+@needs_refhost
+def test_scene_from_reference_accepts_a_hittablelist_root():
+    """crt_scene_from_reference with the reference's scene graph behind a HittableList root (Hittable.cuh:532-581: a list whose
+    elements are BVHNode hittables) flattens to the same scene as the BVH root itself (what Kernel.cu:40 is handed): identical
+    primary-hit IDs, equal to the oracle's. A root of any other type is refused."""
+    lib = capi.load()
+    W, H = 160, 120
+    s = Scene.generate(capi.SCENE_REFERENCE_DEFAULT, 1984)
+    cam = s.default_camera(W, H)
+    handle, world = O.refhost_world(s)
+    try:
+        list_root = O.refhost_world_list_root(handle)
+        assert list_root
+        ids = []
+        for root in (world, list_root):
+            r = Renderer(0)
+            try:
+                st = lib.crt_scene_from_reference(r.ctx, C.c_void_p(root))
+                assert st == capi.CRT_OK, lib.crt_last_error_string(r.ctx)
+                assert r.bvh_stats().n_prims == sum(1 for i in range(s.n_hittables) if s.desc.hittables[i].active)
+                r.set_camera(cam); r.resize(W, H)
+                ids.append(r.primary_ids(capi.JITTER_CENTER))
+            finally:
+                r.close()
+        assert np.array_equal(ids[0], ids[1])
+        # the flattener numbers hittables in tree order, the oracle in list order: compare WHAT is hit through the geometry
+        ref = O.oracle_render(s, cam, W, H, 0, 5, want_ids=True, want_rgba=False, want_mean=False)["ids"]
+        assert np.array_equal(ids[0] >= 0, ref >= 0) and (ids[0] >= 0).any()
+        # a leaf as the root is not a world
+        rh = O.refhost()
+        rh.refhost_world_list.restype = C.c_void_p
+        rh.refhost_world_list.argtypes = [C.c_void_p]
+        leaf = C.cast(rh.refhost_world_list(handle), C.POINTER(C.c_void_p))[0]
+        r = Renderer(0)
+        try:
+            assert lib.crt_scene_from_reference(r.ctx, C.c_void_p(leaf)) == capi.CRT_ERR_INVALID
+            assert b"BVHNODE" in lib.crt_last_error_string(r.ctx)
+        finally:
+            r.close()
+    finally:
+        O.refhost_world_destroy(handle)
