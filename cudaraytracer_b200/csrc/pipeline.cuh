@@ -285,10 +285,12 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
     int slot = -1, cur = CRT_TRAV_DONE, sp = 0;
     TravRay r = trav_setup<false>(f3(0.f, 0.f, 0.f), f3(0.f, 0.f, 1.f));
     Hit h;
-    h.t = 0.f;
+    h.t = 3.402823466e+38f; // node_visit_pair: t_hit >= t_min in every lane, also in those that have no ray yet
     h.leaf = -1;
     int stack[CRT_STACK_SIZE];
-    if (PAIR) stack[0] = CRT_TRAV_DONE; // sentinel: a pop of the empty stack yields "finished" (node_visit_pair)
+    StackPtr top = 0; // PAIR: the stack is reached through `top` (sentinel below the first entry), otherwise through `sp`
+    if (PAIR) top = stk_begin(stack);
+    const StackPtr top0 = top;
     unsigned int shard_cursor = (blockIdx.x * PIPE_WARPS + warp) & (WF_SHARDS - 1);
     bool exhausted = false;
 
@@ -341,8 +343,9 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
                 r = trav_setup<false>(f3(a0.x, a0.y, a0.z), f3(a0.w, b0.x, b0.y));
                 h.t = 3.402823466e+38f;
                 h.leaf = -1;
-                cur = trav_begin<false, SMEM_ALL>(S, r, t_min, h);
-                sp = PAIR ? 1 : 0;
+                cur = trav_begin<false, SMEM_ALL, SPH>(S, r, t_min, h);
+                sp = 0;
+                top = top0;
             }
             refill_short = n < __popc(m);
         }
@@ -354,12 +357,12 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         const int leave_below = refill_short ? 1 : A.thresh; // EXT ran dry: leaving early would only spin
         for (int rounds_left = A.max_rounds; rounds_left > 0; rounds_left--) {
             if (PAIR) {
-                node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
-                node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
-                node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
+                node_visit_pair(S, r, t_min, h.t, cur, top);
+                node_visit_pair(S, r, t_min, h.t, cur, top);
+                node_visit_pair(S, r, t_min, h.t, cur, top);
                 if (cur < 0 && cur != CRT_TRAV_DONE) {
-                    if (SPH) leaf_step_sphere(S, r, t_min, h, cur, sp, stack);
-                    else leaf_step<false, SMEM_ALL, true>(S, r, t_min, h, cur, sp, stack);
+                    if (SPH) leaf_step_sphere(S, r, t_min, h, cur, top);
+                    else leaf_step_pair<SMEM_ALL>(S, r, t_min, h, cur, top);
                 }
             }
             else {

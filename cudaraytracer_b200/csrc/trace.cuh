@@ -24,6 +24,7 @@ struct SceneView
     int smem_nodes, smem_prims, smem_mats;
     int entry, n_top;
     int top_code[CRT_MAX_TOP];
+    int dummy; // PAIR staging: byte offset of the dummy node that lanes which are not at an inner node visit (node_visit_pair)
 };
 
 // 32 bytes through the read-only path in one instruction (PTX 8.8 ld.global.nc.v8, 32-byte aligned address).
@@ -110,7 +111,7 @@ template <bool PAD, bool PAIR = false> __device__ __forceinline__ SceneView stag
     S.entry = D.entry; S.n_top = D.n_top;
     for (int k = 0; k < CRT_MAX_TOP; k++) S.top_code[k] = D.top_code[k];
     float4* sn = smem;
-    float4* sp = sn + (PAD ? CRT_SMEM_NODE_F4 : 4) * (size_t)D.smem_nodes;
+    float4* sp = sn + (PAD ? CRT_SMEM_NODE_F4 : 4) * (size_t)(D.smem_nodes + (PAIR ? 1 : 0));
     float4* sm = sp + D.smem_prims;
     const int tid = threadIdx.x, nt = blockDim.x;
     if (PAIR) {
@@ -124,6 +125,12 @@ template <bool PAD, bool PAIR = false> __device__ __forceinline__ SceneView stag
             else if (k < 14) { const int c = __float_as_int(v); v = __int_as_float(c >= 0 ? c * (16 * CRT_SMEM_NODE_F4) : c); }
             dst[4 * CRT_SMEM_NODE_F4 * node + at] = v;
         }
+        // The dummy node behind the last one: child 0 is the whole space (centre 0, half-extent +inf), child 1 is empty
+        // (half-extent -inf: near = +inf, far = -inf). A lane that visits it hits child 0 only: no push, no pop.
+        for (int k = tid; k < 16; k += nt) {
+            const float inf = __int_as_float(0x7f800000);
+            dst[4 * CRT_SMEM_NODE_F4 * D.smem_nodes + k] = k < 6 || k >= 12 ? 0.f : ((k & 1) ? -inf : inf);
+        }
     }
     else
     for (int i = tid; i < 4 * D.smem_nodes; i += nt) {
@@ -131,6 +138,7 @@ template <bool PAD, bool PAIR = false> __device__ __forceinline__ SceneView stag
         sn[PAD ? CRT_SMEM_NODE_F4 * (i >> 2) + (i & 3) : (i & 3) * D.smem_nodes + (i >> 2)] = v;
     }
     if (PAIR && S.entry >= 0) S.entry *= 16 * CRT_SMEM_NODE_F4;
+    S.dummy = 16 * CRT_SMEM_NODE_F4 * D.smem_nodes;
     for (int i = tid; i < D.smem_prims; i += nt) sp[i] = __ldg(D.prims + i);
     for (int i = tid; i < 2 * D.smem_mats; i += nt) sm[i] = __ldg(D.mats + i);
     S.s_nodes = sn; S.s_prims = sp; S.s_mats = sm;
@@ -294,15 +302,54 @@ __device__ __forceinline__ float2 fma2ss(float2 a, float s, float t)
 #endif
 }
 
-// The inner-node visit of the kernels that hold the WHOLE tree in shared memory in the PAIR layout (stage_scene<true, true, true>),
-// executed by every lane of the warp like node_step_all. `cur` >= 0 is the byte offset of a staged node; the stack holds a
-// CRT_TRAV_DONE sentinel below the first entry, so a pop needs no emptiness test (sp >= 1 while a ray is in flight).
-// Per visit: 1 VIMNMX + 4 LDS + 9 FFMA2 + 8 min/max + 3 FSETP + the select / push / pop, no branch: ~40 instructions against
-// the 55 of node_step_all (profiles/r01_l_pipe_c2_spp128.txt).
-__device__ __forceinline__ void node_visit_pair(const SceneView& S, const TravRay& r, float t_min, float t_hit, int& cur, int& sp, int* stack)
+// The traversal stack of the PAIR kernels: a pointer to the next free entry of a per-thread array whose entry 0 is a
+// CRT_TRAV_DONE sentinel, so that a pop needs no emptiness test. On the device the pointer is the 32-bit local-window address
+// and the push / pop of a node visit are four PREDICATED instructions (STL, LDL, two adds) written in PTX: from `if (push) sp++`
+// the compiler makes an add and a predicated move per case, plus an address computation per access (10 instructions of the 42
+// of a visit, profiles/r02_v_pipe_c2_by_line.txt). The host build (tests/sim) runs the same logic on a plain pointer.
+#ifdef CRT_HOST_SIM
+typedef int* StackPtr;
+__device__ __forceinline__ StackPtr stk_begin(int* stack) { stack[0] = CRT_TRAV_DONE; return stack + 1; }
+__device__ __forceinline__ void stk_visit(StackPtr& top, bool push, bool pop, int other, int& next)
+{
+    if (push) *top = other;
+    if (pop) next = top[-1];
+    if (push) top++;
+    if (pop) top--;
+}
+__device__ __forceinline__ int stk_pop(StackPtr& top) { return *--top; }
+#else
+typedef unsigned StackPtr;
+__device__ __forceinline__ StackPtr stk_begin(int* stack)
+{
+    stack[0] = CRT_TRAV_DONE;
+    return (unsigned)__cvta_generic_to_local(stack) + 4u;
+}
+// push and pop exclude each other
+__device__ __forceinline__ void stk_visit(StackPtr& top, bool push, bool pop, int other, int& next)
+{
+    asm volatile("{ .reg .pred p, q; setp.ne.s32 p, %2, 0; setp.ne.s32 q, %3, 0;\n"
+                 " @p st.local.b32 [%0], %4;\n @q ld.local.b32 %1, [%0+-4];\n @p add.u32 %0, %0, 4;\n @q add.u32 %0, %0, -4; }"
+                 : "+r"(top), "+r"(next) : "r"((int)push), "r"((int)pop), "r"(other) : "memory");
+}
+__device__ __forceinline__ int stk_pop(StackPtr& top)
+{
+    int v;
+    asm volatile("add.u32 %0, %0, -4;\n ld.local.b32 %1, [%0];" : "+r"(top), "=r"(v) : : "memory");
+    return v;
+}
+#endif
+
+// The inner-node visit of the kernels that hold the WHOLE tree in shared memory in the PAIR layout (stage_scene<true, true>),
+// executed by every lane of the warp like node_step_all. `cur` >= 0 is the byte offset of a staged node.
+// A lane that is NOT at an inner node (it waits for the leaf visit of the round, or it has no ray) visits the dummy node staged
+// behind the tree: child 0 always hits, child 1 never does, so it neither pushes nor pops and the hit tests need no `at` term -
+// PROVIDED t_hit >= t_min in every lane at all times (a lane without a ray keeps the t of its last one, or FLT_MAX).
+// Per visit: 1 ISETP + 1 SEL + 4 LDS + 9 FFMA2 + 8 min/max + 3 FSETP + 2-3 PLOP3 + 3 SEL + the four stack instructions, no branch.
+__device__ __forceinline__ void node_visit_pair(const SceneView& S, const TravRay& r, float t_min, float t_hit, int& cur, StackPtr& top)
 {
     const bool at = cur >= 0;
-    const float4* p = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(S.s_nodes) + max(cur, 0));
+    const float4* p = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(S.s_nodes) + (at ? cur : S.dummy));
     const float4 w0 = p[0], w1 = p[1], w2 = p[2];
     const int2 ch = *reinterpret_cast<const int2*>(p + 3);
     const float2 mx = fma2ss(make_float2(w0.x, w0.y), r.id.x, -r.ood.x);
@@ -313,14 +360,11 @@ __device__ __forceinline__ void node_visit_pair(const SceneView& S, const TravRa
     const float2 nz = fma2s(make_float2(-w2.z, -w2.w), r.aid.z, mz), fz = fma2s(make_float2(w2.z, w2.w), r.aid.z, mz);
     const float tn0 = fmaxf(fmaxf(nx.x, ny.x), fmaxf(nz.x, t_min)), tf0 = fminf(fminf(fx.x, fy.x), fminf(fz.x, t_hit));
     const float tn1 = fmaxf(fmaxf(nx.y, ny.y), fmaxf(nz.y, t_min)), tf1 = fminf(fminf(fx.y, fy.y), fminf(fz.y, t_hit));
-    const bool h0 = at && tn0 <= tf0, h1 = at && tn1 <= tf1;
+    const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
     const bool second_first = h1 && (tn1 < tn0 || !h0); // child 1 is the nearer hit child, or the only one
     const int first = second_first ? ch.y : ch.x, other = second_first ? ch.x : ch.y;
-    const bool push = h0 && h1, pop = at && !(h0 || h1);
-    if (push) stack[sp] = other;
     int next = first;
-    if (pop) next = stack[sp - 1];
-    sp += (push ? 1 : 0) - (pop ? 1 : 0);
+    stk_visit(top, h0 && h1, !(h0 || h1), other, next);
     if (at) cur = next;
 }
 
@@ -371,8 +415,7 @@ __device__ __forceinline__ void node_step_all(const SceneView& S, const TravRay&
 }
 
 // One leaf visit: test the primitive, shrink the hit distance, pop. `cur` < 0 and != CRT_TRAV_DONE on entry.
-// SENT: the stack has a CRT_TRAV_DONE sentinel at its bottom (node_visit_pair), so the pop is unconditional.
-template <bool EXACT, bool SMEM_ALL, bool SENT = false>
+template <bool EXACT, bool SMEM_ALL>
 __device__ __forceinline__ void leaf_step(const SceneView& S, const TravRay& r, float t_min, Hit& h, int& cur, int& sp, const int* stack)
 {
     const int code = ~cur;
@@ -381,15 +424,26 @@ __device__ __forceinline__ void leaf_step(const SceneView& S, const TravRay& r, 
         h.t = t;
         h.leaf = code;
     }
-    if (SENT) cur = stack[--sp];
-    else cur = sp ? stack[--sp] : CRT_TRAV_DONE;
+    cur = sp ? stack[--sp] : CRT_TRAV_DONE;
+}
+
+// The leaf visit of the PAIR kernels (sentinel stack: the pop is unconditional), any primitive type.
+template <bool SMEM_ALL>
+__device__ __forceinline__ void leaf_step_pair(const SceneView& S, const TravRay& r, float t_min, Hit& h, int& cur, StackPtr& top)
+{
+    const int code = ~cur;
+    float t;
+    if (leaf_test<false, SMEM_ALL>(S, code, r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) {
+        h.t = t;
+        h.leaf = code;
+    }
+    cur = stk_pop(top);
 }
 
 // The leaf visit of a scene that holds only spheres, in shared memory, with the sentinel stack: no type dispatch, no branch
 // (the two roots are tried by selects). The arithmetic is sphere_test<false>'s, operation for operation.
-__device__ __forceinline__ void leaf_step_sphere(const SceneView& S, const TravRay& r, float t_min, Hit& h, int& cur, int& sp, const int* stack)
+__device__ __forceinline__ void sphere_visit(const SceneView& S, int code, const TravRay& r, float t_min, Hit& h)
 {
-    const int code = ~cur;
     const float4 sph = S.s_prims[code & CRT_LEAF_INDEX_MASK];
     const float3 oc = r.o - f3(sph.x, sph.y, sph.z);
     const float b = dot3(oc, r.d);
@@ -403,22 +457,29 @@ __device__ __forceinline__ void leaf_step_sphere(const SceneView& S, const TravR
         h.t = ok1 ? t1 : t2;
         h.leaf = code;
     }
-    cur = stack[--sp];
+}
+__device__ __forceinline__ void leaf_step_sphere(const SceneView& S, const TravRay& r, float t_min, Hit& h, int& cur, StackPtr& top)
+{
+    sphere_visit(S, ~cur, r, t_min, h);
+    cur = stk_pop(top);
 }
 
 // Start of a closest-hit query: the primitives peeled off the top of the tree (DevScene::top_code) are tested here, without
 // their boxes, and the descent starts below them. Returns the node to start at.
-template <bool EXACT, bool SMEM_ALL>
+template <bool EXACT, bool SMEM_ALL, bool SPH = false>
 __device__ __forceinline__ int trav_begin(const SceneView& S, const TravRay& r, float t_min, Hit& h)
 {
 #pragma unroll
     for (int k = 0; k < CRT_MAX_TOP; k++) {
         if (k < S.n_top) {
             const int code = S.top_code[k];
-            float t;
-            if (leaf_test<EXACT, SMEM_ALL>(S, code, r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) {
-                h.t = t;
-                h.leaf = code;
+            if (SPH) sphere_visit(S, code, r, t_min, h); // spheres only, all staged: no type dispatch, no branch
+            else {
+                float t;
+                if (leaf_test<EXACT, SMEM_ALL>(S, code, r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) {
+                    h.t = t;
+                    h.leaf = code;
+                }
             }
         }
     }

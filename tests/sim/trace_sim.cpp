@@ -100,17 +100,29 @@ template <bool SPH> Hit pair_lane(const SceneView& S, const TravRay& r, float t_
     Hit h;
     h.t = 3.402823466e+38f;
     h.leaf = -1;
-    int stack[CRT_STACK_SIZE], sp = 1;
-    stack[0] = CRT_TRAV_DONE;
+    int stack[CRT_STACK_SIZE];
+    StackPtr top = stk_begin(stack);
     int cur = trav_begin<false, true>(S, r, t_min, h);
     while (cur != CRT_TRAV_DONE) {
-        for (int k = 0; k < 3; k++) node_visit_pair(S, r, t_min, h.t, cur, sp, stack);
+        // a lane that reached a leaf sits the remaining node visits of the round out ON THE DUMMY NODE: it must neither push nor pop
+        for (int k = 0; k < 3; k++) {
+            StackPtr before = top;
+            const bool at = cur >= 0;
+            node_visit_pair(S, r, t_min, h.t, cur, top);
+            if (!at && top != before) { fprintf(stderr, "the dummy node moved the stack\n"); exit(3); }
+        }
         if (cur < 0 && cur != CRT_TRAV_DONE) {
-            if (SPH) leaf_step_sphere(S, r, t_min, h, cur, sp, stack);
-            else leaf_step<false, true, true>(S, r, t_min, h, cur, sp, stack);
+            if (SPH) leaf_step_sphere(S, r, t_min, h, cur, top);
+            else leaf_step_pair<true>(S, r, t_min, h, cur, top);
         }
         if (++visits > 100000000L) { fprintf(stderr, "traversal does not terminate\n"); exit(3); }
-        if (sp < 0 || sp > CRT_STACK_SIZE) { fprintf(stderr, "stack pointer out of range: %d\n", sp); exit(3); }
+        if (top - stack < 0 || top - stack > CRT_STACK_SIZE) { fprintf(stderr, "stack pointer out of range: %d\n", (int)(top - stack)); exit(3); }
+    }
+    // a lane without a ray (cur == CRT_TRAV_DONE) keeps visiting the dummy node: nothing may move
+    for (int k = 0; k < 3; k++) {
+        StackPtr before = top;
+        node_visit_pair(S, r, t_min, h.t, cur, top);
+        if (cur != CRT_TRAV_DONE || top != before) { fprintf(stderr, "an idle lane moved on the dummy node\n"); exit(3); }
     }
     return h;
 }
