@@ -1308,15 +1308,17 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
     const long per_slot = 3 * 16 + 8 + 2 * PQ_COUNT;
     const long budget = (ctx->smem_budget_override >= 0 ? std::min<long>(ctx->smem_budget_override, ctx->smem_optin) : (long)ctx->smem_optin) - 1024;
     const long node_b = 16 * CRT_SMEM_NODE_F4;
-    const long full = ((long)A.scene.n_nodes + 1) * node_b + (long)A.scene.n_prims * 48; // + the dummy node of the PAIR staging (trace.cuh)
-    int n_slots = ctx->pipe_slots > 0 ? ctx->pipe_slots : (full + 2048 * per_slot <= budget ? 2048 : 1024);
+    // whole scene staged: the PAIR layout of trace.cuh, 48-byte nodes + a dummy node, 16-bit references
+    const long full = ((long)A.scene.n_nodes + 1) * 16 * CRT_PAIR_NODE_F4 + (long)A.scene.n_prims * 48;
+    const bool pair_ok = A.scene.n_prims <= CRT_PAIR_MAX_PRIMS && CRT_PAIR_NODE_F4 * ((long)A.scene.n_nodes + 1) < CRT_PAIR_LEAF;
+    int n_slots = ctx->pipe_slots > 0 ? ctx->pipe_slots : (pair_ok && full + 2048 * per_slot <= budget ? 2048 : 1024);
     while (n_slots & (n_slots - 1)) n_slots &= n_slots - 1; // power of two
     n_slots = std::min(std::max(n_slots, 64), 32768); // ring entries are 16-bit slot ids, 0xffff = empty
     if ((long)n_slots * per_slot > budget) return crt_set_error(ctx, CRT_ERR_INVALID, "render_pipeline: CRT_PIPE_SLOTS does not fit in shared memory");
     bool all = false;
     long rem = budget - (long)n_slots * per_slot;
     long budget_used = budget;
-    if (full <= rem) {
+    if (pair_ok && full <= rem) {
         A.scene.smem_nodes = A.scene.n_nodes; A.scene.smem_prims = A.scene.n_prims; A.scene.smem_mats = A.scene.n_prims;
         all = true;
         rem -= full;

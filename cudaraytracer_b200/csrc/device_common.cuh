@@ -2,6 +2,9 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#ifndef CRT_HOST_SIM
+#include <cuda_fp16.h>
+#endif
 #include <stdint.h>
 
 #define CRT_STACK_SIZE 64

@@ -257,7 +257,8 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
 // A traversal round is node, node, node, leaf: a lane that reaches a leaf sits the remaining node visits of the round out, and
 // ONE leaf visit serves them all (measured against node, leaf, node, leaf: +7 % on C2, +4 % on the 1 M-sphere scene; two or
 // four node visits per leaf visit are slower, profiles/r02_a_*).
-// SMEM_ALL (the whole scene is staged): the nodes take the PAIR layout and node_visit_pair (FFMA2, branch-free, sentinel stack).
+// SMEM_ALL (the whole scene is staged): the nodes take the PAIR layout of trace.cuh (48-byte nodes: binary16 half-extents,
+// 16-bit references) and node_visit_pair (FFMA2, branch-free, dummy node for idle lanes, sentinel stack pushed / popped in PTX).
 // SPH: the scene holds only spheres (DevScene::spheres_only, chosen by the host): leaf visits without the type dispatch.
 template <int NSLOTS, bool SMEM_ALL, bool SPH = false>
 __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_constant__ PipeArgs A)
@@ -343,7 +344,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
                 r = trav_setup<false>(f3(a0.x, a0.y, a0.z), f3(a0.w, b0.x, b0.y));
                 h.t = 3.402823466e+38f;
                 h.leaf = -1;
-                cur = trav_begin<false, SMEM_ALL, SPH>(S, r, t_min, h);
+                cur = trav_begin<false, SMEM_ALL, PAIR, SPH>(S, r, t_min, h);
                 sp = 0;
                 top = top0;
             }
@@ -360,7 +361,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
                 node_visit_pair(S, r, t_min, h.t, cur, top);
                 node_visit_pair(S, r, t_min, h.t, cur, top);
                 node_visit_pair(S, r, t_min, h.t, cur, top);
-                if (cur < 0 && cur != CRT_TRAV_DONE) {
+                if (pair_at_leaf(cur)) {
                     if (SPH) leaf_step_sphere(S, r, t_min, h, cur, top);
                     else leaf_step_pair<SMEM_ALL>(S, r, t_min, h, cur, top);
                 }
@@ -377,8 +378,10 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
         const bool fin = cur == CRT_TRAV_DONE && slot >= 0;
         {
             // the leaf code carries the material type of what was hit (crt_internal.h): no load needed to bin the ray
-            const int cls = h.leaf < 0 ? PQ_MISS : PQ_LAMBERTIAN + ((h.leaf >> CRT_LEAF_MAT_SHIFT) & 3);
-            if (fin) reinterpret_cast<float2*>(P.b + slot)[1] = make_float2(h.t, __int_as_float(h.leaf));
+            // (PAIR: the traversal worked on 16-bit references; the pool gets the leaf code the shading expects)
+            const int leaf = PAIR && h.leaf >= 0 ? pair_leaf_code(h.leaf) : h.leaf;
+            const int cls = leaf < 0 ? PQ_MISS : PQ_LAMBERTIAN + ((leaf >> CRT_LEAF_MAT_SHIFT) & 3);
+            if (fin) reinterpret_cast<float2*>(P.b + slot)[1] = make_float2(h.t, __int_as_float(leaf));
                     pipe_push_binned(P, &ctl, cls, fin, slot, lt);
             if (fin) slot = -1;
         }

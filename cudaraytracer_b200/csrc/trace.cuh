@@ -24,7 +24,8 @@ struct SceneView
     int smem_nodes, smem_prims, smem_mats;
     int entry, n_top;
     int top_code[CRT_MAX_TOP];
-    int dummy; // PAIR staging: byte offset of the dummy node that lanes which are not at an inner node visit (node_visit_pair)
+    int top_pair[CRT_MAX_TOP]; // PAIR staging: the peeled leaves as 16-bit references
+    int dummy; // PAIR staging: the dummy node that lanes which are not at an inner node visit (node_visit_pair)
 };
 
 // 32 bytes through the read-only path in one instruction (PTX 8.8 ld.global.nc.v8, 32-byte aligned address).
@@ -98,47 +99,124 @@ template <bool SMEM_ALL> __device__ __forceinline__ void load_mat(const SceneVie
 
 #define CRT_TRAV_DONE ((int)0x80000000)
 
+// ---- The PAIR staging (one-CTA-per-SM kernels, whole scene in shared memory): 48-byte nodes ----
+// The shared-memory pipe is what k_render_pipe runs into once its instruction count is down (profiles/r02_y: issue 73.5 %,
+// l1tex 91 %; a node visit is 14 wavefronts of loads against 37 instructions = 9.3 issue cycles per SM). So the staged node is
+// made SMALLER at the price of a few more instructions: half-extents as binary16 rounded UP (the box only grows: it culls, it
+// never decides a hit), child references as 16-bit codes. A node is 40 bytes in a 48-byte stride (an odd multiple of 16: lanes
+// at different nodes spread over all eight 16-byte bank groups), fetched by LDS.128 + LDS.128 + LDS.64 = 10 wavefronts:
+//   +0  {c0.x, c1.x, c0.y, c1.y}                 centres, binary32, the two children interleaved (one FFMA2 serves both)
+//   +16 {c0.z, c1.z, half2(h0.x, h1.x), half2(h0.y, h1.y)}
+//   +32 {half2(h0.z, h1.z), ref0 | ref1 << 16}
+// A 16-bit reference: inner node = its offset in 16-byte units (< 0x8000); leaf = 0x8000 | type << 13 | material type << 11 |
+// primitive slot (< 2048: more primitives than that do not fit in shared memory next to the path pool). Inside the PAIR
+// traversal `cur`, the stack entries and Hit::leaf hold these codes (CRT_TRAV_DONE stays what it is: neither test below
+// matches it); pair_leaf_code() turns a leaf reference back into the leaf code of crt_internal.h when the ray is finished.
+#define CRT_PAIR_NODE_F4 3
+#define CRT_PAIR_LEAF 0x8000
+#define CRT_PAIR_MAX_PRIMS 2048
+__device__ __forceinline__ int pair_ref(int ref)
+{
+    if (ref == CRT_TRAV_DONE) return ref;
+    if (ref >= 0) return ref * CRT_PAIR_NODE_F4;
+    const int code = ~ref;
+    return CRT_PAIR_LEAF | (((code >> CRT_LEAF_TYPE_SHIFT) & 3) << 13) | (((code >> CRT_LEAF_MAT_SHIFT) & 3) << 11) | (code & (CRT_PAIR_MAX_PRIMS - 1));
+}
+__device__ __forceinline__ int pair_leaf_code(int v)
+{
+    return (((v >> 13) & 3) << CRT_LEAF_TYPE_SHIFT) | (((v >> 11) & 3) << CRT_LEAF_MAT_SHIFT) | (v & (CRT_PAIR_MAX_PRIMS - 1));
+}
+__device__ __forceinline__ bool pair_at_node(int cur) { return (unsigned)cur < (unsigned)CRT_PAIR_LEAF; }
+__device__ __forceinline__ bool pair_at_leaf(int cur) { return (cur & CRT_PAIR_LEAF) != 0; }
+
+// binary32 >= 0 -> binary16 bits, rounded towards +inf (overflow gives +inf: the box side becomes unbounded, still correct)
+__device__ __forceinline__ unsigned crt_f2h_ru(float x)
+{
+#ifdef CRT_HOST_SIM
+    const unsigned b = __float_as_uint(fabsf(x));
+    if (b >= 0x7f800000u) return 0x7c00u;
+    const int e = (int)(b >> 23) - 127;
+    if (e > 15) return 0x7c00u;
+    if (b == 0u) return 0u;
+    if (e >= -14) { // normal in binary16; a carry out of the mantissa moves into the exponent (up to 0x7c00 = +inf)
+        unsigned h = ((unsigned)(e + 15) << 10) | ((b & 0x7fffffu) >> 13);
+        if (b & 0x1fffu) h++;
+        return h;
+    }
+    const unsigned m = (b & 0x7fffffu) | 0x800000u; // subnormal: units of 2^-24
+    const int shift = -e - 1; // value = m * 2^(e - 23) = (m >> shift) * 2^-24
+    if (shift >= 32) return 1u;
+    unsigned h = m >> shift;
+    if (m & ((1u << shift) - 1u)) h++;
+    return h;
+#else
+    return (unsigned)__half_as_ushort(__float2half_ru(fabsf(x)));
+#endif
+}
+// two binary16 in one word -> {low, high} as binary32
+__device__ __forceinline__ float2 crt_h2_to_f2(unsigned w)
+{
+#ifdef CRT_HOST_SIM
+    float2 r;
+    for (int k = 0; k < 2; k++) {
+        const unsigned h = (w >> (16 * k)) & 0xffffu, sgn = (h & 0x8000u) << 16, e = (h >> 10) & 31u, m = h & 0x3ffu;
+        float v;
+        if (e == 31u) v = __uint_as_float(sgn | 0x7f800000u | (m << 13));
+        else if (e == 0u) v = (sgn ? -1.f : 1.f) * (float)m * 5.9604644775390625e-8f; // m * 2^-24
+        else v = __uint_as_float(sgn | ((e + 112u) << 23) | (m << 13));
+        (k ? r.y : r.x) = v;
+    }
+    return r;
+#else
+    return __half22float2(*reinterpret_cast<const __half2*>(&w));
+#endif
+}
+
 // Stages the first smem_* entries of each table into dynamic shared memory. Call from every thread, then __syncthreads().
-// PAIR (needs PAD and the whole tree in shared memory): inner-child references of the staged nodes, and the entry node, become
-// BYTE OFFSETS into the staged table (index * 80), so a visit needs no address arithmetic; the twelve box words of a staged node are interleaved child-wise, {c0.x, c1.x, c0.y, c1.y | c0.z, c1.z,
-// h0.x, h1.x | h0.y, h1.y, h0.z, h1.z}, so that each 64-bit register pair of the three 128-bit loads holds the same quantity of
-// BOTH children and one packed FFMA2 (fma.rn.f32x2, new on sm_100) does the work of two FFMA (node_visit_pair below).
+// PAIR (needs PAD and the whole tree in shared memory): the 48-byte nodes above, plus a dummy node behind the last one.
 template <bool PAD, bool PAIR = false> __device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem)
 {
     SceneView S;
     S.g_nodes = D.nodes; S.g_prims = D.prims; S.g_prim_k = D.prim_k; S.g_mats = D.mats; S.images = D.images;
     S.smem_nodes = D.smem_nodes; S.smem_prims = D.smem_prims; S.smem_mats = D.smem_mats;
     S.entry = D.entry; S.n_top = D.n_top;
-    for (int k = 0; k < CRT_MAX_TOP; k++) S.top_code[k] = D.top_code[k];
+    for (int k = 0; k < CRT_MAX_TOP; k++) { S.top_code[k] = D.top_code[k]; S.top_pair[k] = PAIR ? pair_ref(~D.top_code[k]) : 0; }
     float4* sn = smem;
-    float4* sp = sn + (PAD ? CRT_SMEM_NODE_F4 : 4) * (size_t)(D.smem_nodes + (PAIR ? 1 : 0));
+    float4* sp = sn + (PAIR ? CRT_PAIR_NODE_F4 * (size_t)(D.smem_nodes + 1) : (PAD ? CRT_SMEM_NODE_F4 : 4) * (size_t)D.smem_nodes);
     float4* sm = sp + D.smem_prims;
     const int tid = threadIdx.x, nt = blockDim.x;
     if (PAIR) {
-        const float* src = reinterpret_cast<const float*>(D.nodes);
-        float* dst = reinterpret_cast<float*>(sn);
-        for (int i = tid; i < 16 * D.smem_nodes; i += nt) {
-            const int node = i >> 4, k = i & 15;
-            float v = __ldg(src + i);
-            int at = k;
-            if (k < 12) at = 2 * (k % 6) + k / 6; // child c, quantity j (centre xyz, half xyz) -> word 2 j + c
-            else if (k < 14) { const int c = __float_as_int(v); v = __int_as_float(c >= 0 ? c * (16 * CRT_SMEM_NODE_F4) : c); }
-            dst[4 * CRT_SMEM_NODE_F4 * node + at] = v;
+        for (int i = tid; i <= D.smem_nodes; i += nt) {
+            float4 w0, w1;
+            uint2 w2;
+            if (i < D.smem_nodes) {
+                const float4 g0 = __ldg(D.nodes + 4 * i), g1 = __ldg(D.nodes + 4 * i + 1), g2 = __ldg(D.nodes + 4 * i + 2), g3 = __ldg(D.nodes + 4 * i + 3);
+                // global: {c0.c.xyz, c0.h.x} {c0.h.yz, c1.c.xy} {c1.c.z, c1.h.xyz} {child0, child1}
+                w0 = make_float4(g0.x, g1.z, g0.y, g1.w);
+                w1 = make_float4(g0.z, g2.x, __uint_as_float(crt_f2h_ru(g0.w) | (crt_f2h_ru(g2.y) << 16)), __uint_as_float(crt_f2h_ru(g1.x) | (crt_f2h_ru(g2.z) << 16)));
+                w2 = make_uint2(crt_f2h_ru(g1.y) | (crt_f2h_ru(g2.w) << 16),
+                                ((unsigned)pair_ref(__float_as_int(g3.x)) & 0xffffu) | ((unsigned)pair_ref(__float_as_int(g3.y)) << 16));
+            }
+            else {
+                // The dummy node: child 0 is the whole space (centre 0, half-extent +inf), child 1 is empty (half-extent -inf:
+                // near = +inf, far = -inf). A lane that visits it hits child 0 only: no push, no pop.
+                const unsigned pm = 0x7c00u | (0xfc00u << 16);
+                w0 = make_float4(0.f, 0.f, 0.f, 0.f);
+                w1 = make_float4(0.f, 0.f, __uint_as_float(pm), __uint_as_float(pm));
+                w2 = make_uint2(pm, 0u);
+            }
+            sn[CRT_PAIR_NODE_F4 * i] = w0;
+            sn[CRT_PAIR_NODE_F4 * i + 1] = w1;
+            *reinterpret_cast<uint2*>(sn + CRT_PAIR_NODE_F4 * i + 2) = w2;
         }
-        // The dummy node behind the last one: child 0 is the whole space (centre 0, half-extent +inf), child 1 is empty
-        // (half-extent -inf: near = +inf, far = -inf). A lane that visits it hits child 0 only: no push, no pop.
-        for (int k = tid; k < 16; k += nt) {
-            const float inf = __int_as_float(0x7f800000);
-            dst[4 * CRT_SMEM_NODE_F4 * D.smem_nodes + k] = k < 6 || k >= 12 ? 0.f : ((k & 1) ? -inf : inf);
-        }
+        S.entry = pair_ref(D.entry);
     }
     else
     for (int i = tid; i < 4 * D.smem_nodes; i += nt) {
         const float4 v = __ldg(D.nodes + i);
         sn[PAD ? CRT_SMEM_NODE_F4 * (i >> 2) + (i & 3) : (i & 3) * D.smem_nodes + (i >> 2)] = v;
     }
-    if (PAIR && S.entry >= 0) S.entry *= 16 * CRT_SMEM_NODE_F4;
-    S.dummy = 16 * CRT_SMEM_NODE_F4 * D.smem_nodes;
+    S.dummy = CRT_PAIR_NODE_F4 * D.smem_nodes; // in 16-byte units, like every PAIR node reference
     for (int i = tid; i < D.smem_prims; i += nt) sp[i] = __ldg(D.prims + i);
     for (int i = tid; i < 2 * D.smem_mats; i += nt) sm[i] = __ldg(D.mats + i);
     S.s_nodes = sn; S.s_prims = sp; S.s_mats = sm;
@@ -341,28 +419,31 @@ __device__ __forceinline__ int stk_pop(StackPtr& top)
 #endif
 
 // The inner-node visit of the kernels that hold the WHOLE tree in shared memory in the PAIR layout (stage_scene<true, true>),
-// executed by every lane of the warp like node_step_all. `cur` >= 0 is the byte offset of a staged node.
+// executed by every lane of the warp like node_step_all. `cur` is a 16-bit PAIR reference (or CRT_TRAV_DONE).
 // A lane that is NOT at an inner node (it waits for the leaf visit of the round, or it has no ray) visits the dummy node staged
 // behind the tree: child 0 always hits, child 1 never does, so it neither pushes nor pops and the hit tests need no `at` term -
 // PROVIDED t_hit >= t_min in every lane at all times (a lane without a ray keeps the t of its last one, or FLT_MAX).
-// Per visit: 1 ISETP + 1 SEL + 4 LDS + 9 FFMA2 + 8 min/max + 3 FSETP + 2-3 PLOP3 + 3 SEL + the four stack instructions, no branch.
+// Per visit: 3 LDS (10 wavefronts) + 6 binary16 conversions + 9 FFMA2 + 8 min/max + 3 FSETP + the reference select, the four
+// stack instructions, no branch.
 __device__ __forceinline__ void node_visit_pair(const SceneView& S, const TravRay& r, float t_min, float t_hit, int& cur, StackPtr& top)
 {
-    const bool at = cur >= 0;
-    const float4* p = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(S.s_nodes) + (at ? cur : S.dummy));
-    const float4 w0 = p[0], w1 = p[1], w2 = p[2];
-    const int2 ch = *reinterpret_cast<const int2*>(p + 3);
+    const bool at = pair_at_node(cur);
+    const char* p = reinterpret_cast<const char*>(S.s_nodes) + 16 * (at ? cur : S.dummy);
+    const float4 w0 = *reinterpret_cast<const float4*>(p), w1 = *reinterpret_cast<const float4*>(p + 16);
+    const uint2 w2 = *reinterpret_cast<const uint2*>(p + 32);
+    const float2 hx = crt_h2_to_f2(__float_as_uint(w1.z)), hy = crt_h2_to_f2(__float_as_uint(w1.w)), hz = crt_h2_to_f2(w2.x);
     const float2 mx = fma2ss(make_float2(w0.x, w0.y), r.id.x, -r.ood.x);
     const float2 my = fma2ss(make_float2(w0.z, w0.w), r.id.y, -r.ood.y);
     const float2 mz = fma2ss(make_float2(w1.x, w1.y), r.id.z, -r.ood.z);
-    const float2 nx = fma2s(make_float2(-w1.z, -w1.w), r.aid.x, mx), fx = fma2s(make_float2(w1.z, w1.w), r.aid.x, mx);
-    const float2 ny = fma2s(make_float2(-w2.x, -w2.y), r.aid.y, my), fy = fma2s(make_float2(w2.x, w2.y), r.aid.y, my);
-    const float2 nz = fma2s(make_float2(-w2.z, -w2.w), r.aid.z, mz), fz = fma2s(make_float2(w2.z, w2.w), r.aid.z, mz);
+    const float2 nx = fma2s(make_float2(-hx.x, -hx.y), r.aid.x, mx), fx = fma2s(hx, r.aid.x, mx);
+    const float2 ny = fma2s(make_float2(-hy.x, -hy.y), r.aid.y, my), fy = fma2s(hy, r.aid.y, my);
+    const float2 nz = fma2s(make_float2(-hz.x, -hz.y), r.aid.z, mz), fz = fma2s(hz, r.aid.z, mz);
     const float tn0 = fmaxf(fmaxf(nx.x, ny.x), fmaxf(nz.x, t_min)), tf0 = fminf(fminf(fx.x, fy.x), fminf(fz.x, t_hit));
     const float tn1 = fmaxf(fmaxf(nx.y, ny.y), fmaxf(nz.y, t_min)), tf1 = fminf(fminf(fx.y, fy.y), fminf(fz.y, t_hit));
     const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
     const bool second_first = h1 && (tn1 < tn0 || !h0); // child 1 is the nearer hit child, or the only one
-    const int first = second_first ? ch.y : ch.x, other = second_first ? ch.x : ch.y;
+    const int r0 = (int)(w2.y & 0xffffu), r1 = (int)(w2.y >> 16);
+    const int first = second_first ? r1 : r0, other = second_first ? r0 : r1;
     int next = first;
     stk_visit(top, h0 && h1, !(h0 || h1), other, next);
     if (at) cur = next;
@@ -427,24 +508,24 @@ __device__ __forceinline__ void leaf_step(const SceneView& S, const TravRay& r, 
     cur = sp ? stack[--sp] : CRT_TRAV_DONE;
 }
 
-// The leaf visit of the PAIR kernels (sentinel stack: the pop is unconditional), any primitive type.
+// The leaf visit of the PAIR kernels (sentinel stack: the pop is unconditional), any primitive type. `cur` is a PAIR leaf
+// reference, and so is what goes into Hit::leaf.
 template <bool SMEM_ALL>
 __device__ __forceinline__ void leaf_step_pair(const SceneView& S, const TravRay& r, float t_min, Hit& h, int& cur, StackPtr& top)
 {
-    const int code = ~cur;
     float t;
-    if (leaf_test<false, SMEM_ALL>(S, code, r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) {
+    if (leaf_test<false, SMEM_ALL>(S, pair_leaf_code(cur), r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) {
         h.t = t;
-        h.leaf = code;
+        h.leaf = cur;
     }
     cur = stk_pop(top);
 }
 
-// The leaf visit of a scene that holds only spheres, in shared memory, with the sentinel stack: no type dispatch, no branch
-// (the two roots are tried by selects). The arithmetic is sphere_test<false>'s, operation for operation.
-__device__ __forceinline__ void sphere_visit(const SceneView& S, int code, const TravRay& r, float t_min, Hit& h)
+// The sphere test of a scene that holds only spheres, in shared memory: no type dispatch, no branch (the two roots are tried by
+// selects). The arithmetic is sphere_test<false>'s, operation for operation. `ref` is a PAIR leaf reference.
+__device__ __forceinline__ void sphere_visit(const SceneView& S, int ref, const TravRay& r, float t_min, Hit& h)
 {
-    const float4 sph = S.s_prims[code & CRT_LEAF_INDEX_MASK];
+    const float4 sph = S.s_prims[ref & (CRT_PAIR_MAX_PRIMS - 1)];
     const float3 oc = r.o - f3(sph.x, sph.y, sph.z);
     const float b = dot3(oc, r.d);
     const float c = fmaf(-sph.w, sph.w, dot3(oc, oc));
@@ -455,30 +536,32 @@ __device__ __forceinline__ void sphere_visit(const SceneView& S, int code, const
     const bool hit = disc > 0.f && (ok1 || ok2);
     if (hit) {
         h.t = ok1 ? t1 : t2;
-        h.leaf = code;
+        h.leaf = ref;
     }
 }
 __device__ __forceinline__ void leaf_step_sphere(const SceneView& S, const TravRay& r, float t_min, Hit& h, int& cur, StackPtr& top)
 {
-    sphere_visit(S, ~cur, r, t_min, h);
+    sphere_visit(S, cur, r, t_min, h);
     cur = stk_pop(top);
 }
 
 // Start of a closest-hit query: the primitives peeled off the top of the tree (DevScene::top_code) are tested here, without
 // their boxes, and the descent starts below them. Returns the node to start at.
-template <bool EXACT, bool SMEM_ALL, bool SPH = false>
+// PAIR: Hit::leaf and the returned entry are PAIR references (pipelined kernel with the whole scene staged); SPH: that scene
+// holds only spheres.
+template <bool EXACT, bool SMEM_ALL, bool PAIR = false, bool SPH = false>
 __device__ __forceinline__ int trav_begin(const SceneView& S, const TravRay& r, float t_min, Hit& h)
 {
 #pragma unroll
     for (int k = 0; k < CRT_MAX_TOP; k++) {
         if (k < S.n_top) {
             const int code = S.top_code[k];
-            if (SPH) sphere_visit(S, code, r, t_min, h); // spheres only, all staged: no type dispatch, no branch
+            if (SPH) sphere_visit(S, S.top_pair[k], r, t_min, h); // spheres only, all staged: no type dispatch, no branch
             else {
                 float t;
                 if (leaf_test<EXACT, SMEM_ALL>(S, code, r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) {
                     h.t = t;
-                    h.leaf = code;
+                    h.leaf = PAIR ? S.top_pair[k] : code;
                 }
             }
         }

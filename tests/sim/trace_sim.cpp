@@ -102,16 +102,16 @@ template <bool SPH> Hit pair_lane(const SceneView& S, const TravRay& r, float t_
     h.leaf = -1;
     int stack[CRT_STACK_SIZE];
     StackPtr top = stk_begin(stack);
-    int cur = trav_begin<false, true>(S, r, t_min, h);
+    int cur = trav_begin<false, true, true, SPH>(S, r, t_min, h);
     while (cur != CRT_TRAV_DONE) {
         // a lane that reached a leaf sits the remaining node visits of the round out ON THE DUMMY NODE: it must neither push nor pop
         for (int k = 0; k < 3; k++) {
             StackPtr before = top;
-            const bool at = cur >= 0;
+            const bool at = pair_at_node(cur);
             node_visit_pair(S, r, t_min, h.t, cur, top);
             if (!at && top != before) { fprintf(stderr, "the dummy node moved the stack\n"); exit(3); }
         }
-        if (cur < 0 && cur != CRT_TRAV_DONE) {
+        if (pair_at_leaf(cur)) {
             if (SPH) leaf_step_sphere(S, r, t_min, h, cur, top);
             else leaf_step_pair<true>(S, r, t_min, h, cur, top);
         }
@@ -124,6 +124,7 @@ template <bool SPH> Hit pair_lane(const SceneView& S, const TravRay& r, float t_
         node_visit_pair(S, r, t_min, h.t, cur, top);
         if (cur != CRT_TRAV_DONE || top != before) { fprintf(stderr, "an idle lane moved on the dummy node\n"); exit(3); }
     }
+    if (h.leaf >= 0) h.leaf = pair_leaf_code(h.leaf); // the traversal worked on 16-bit PAIR references
     return h;
 }
 
@@ -177,7 +178,9 @@ int main(int argc, char** argv)
     std::vector<float4> smem3(smem1.size());
     const SceneView Sw = stage_scene<false>(D, smem3.data()); // word-major table: what the megakernel stages
     const SceneView Sp = stage_scene<true, false>(D, smem1.data());
-    const SceneView So = stage_scene<true, true>(D, smem2.data());
+    // the PAIR staging exists for scenes that fit in shared memory: 16-bit references (trace.cuh)
+    const bool pair_ok = np <= CRT_PAIR_MAX_PRIMS && CRT_PAIR_NODE_F4 * (nn + 1) < CRT_PAIR_LEAF;
+    const SceneView So = pair_ok ? stage_scene<true, true>(D, smem2.data()) : Sp;
     bool spheres_only = true;
     for (int c : leaf_code) if (((c >> CRT_LEAF_TYPE_SHIFT) & 3) != CRT_SPHERE) spheres_only = false;
 
@@ -214,8 +217,8 @@ int main(int argc, char** argv)
         got[1] = closest_hit<false, false, true>(Sw, o, d, t_min, 3.402823466e+38f, nb, npr);  // ... tables in 'shared memory'
         got[2] = pipe_lane<true>(Sp, r, t_min, visits);
         got[3] = pipe_lane<false>(Sg, r, t_min, visits); // nodes behind the 'global' pointers (scenes that do not fit)
-        got[4] = pair_lane<false>(So, r, t_min, visits);
-        got[5] = spheres_only ? pair_lane<true>(So, r, t_min, visits) : got[4];
+        got[4] = pair_ok ? pair_lane<false>(So, r, t_min, visits) : got[2];
+        got[5] = pair_ok && spheres_only ? pair_lane<true>(So, r, t_min, visits) : got[4];
         hits += want.leaf >= 0;
         for (int k = 0; k < 6; k++)
             if (got[k].leaf != want.leaf || memcmp(&got[k].t, &want.t, 4) != 0) {
