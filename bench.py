@@ -371,7 +371,7 @@ def run_gpu_arm(args):
     e2e_value = e_rays / (sum(e_times) / 1e3) / 1e6
     e2e_stats = r.bvh_stats()  # of the last e2e step: h2d_bytes == 0 and cache_hits > 0 when the unchanged scene was recognised
     e2e_full = None
-    if scene.n_hittables > 4096:  # the same step with the unchanged-scene cache off: every step validates, builds the BVH and copies
+    if True:  # the same step with the unchanged-scene cache off: every step validates, builds the BVH and copies the whole description
         r.set_scene_cache(False)
         f_times, (f_rays, _, _) = leg.timed(leg.e2e_step, max(2, args.steps // 2), 1, flush)
         r.set_scene_cache(True)

@@ -128,6 +128,55 @@ template <bool SPH> Hit pair_lane(const SceneView& S, const TravRay& r, float t_
     return h;
 }
 
+// Statistic only: what a 4-wide tree would cost. The binary tree is collapsed on the fly - a 4-wide node is a
+// binary node with each inner child replaced by that child's two children - and traversed near-first with the same slab
+// arithmetic; counted are 4-wide node visits, box tests and primitive tests. The closest hit must be the binary tree's.
+long g_wide_visits = 0, g_wide_boxes = 0, g_wide_prims = 0;
+struct WideCand { float tn; int ref; };
+void wide_visit(const SceneView& S, const CrtPackedNode* nodes, int node, const TravRay& r, float t_min, Hit& h)
+{
+    g_wide_visits++;
+    WideCand cand[4];
+    int nc = 0;
+    auto test = [&](int owner, int c) { // child c of node `owner`: its box is stored in the owner
+        float4 w0, w1, w2; int2 ch;
+        load_node<false, false>(S, owner, w0, w1, w2, ch);
+        float tn0, tf0, tn1, tf1;
+        slab2(r, w0, w1, w2, t_min, h.t, tn0, tf0, tn1, tf1);
+        g_wide_boxes++;
+        if (c == 0 ? tn0 <= tf0 : tn1 <= tf1) { cand[nc].tn = c == 0 ? tn0 : tn1; cand[nc].ref = nodes[owner].child[c]; nc++; }
+    };
+    for (int c = 0; c < 2; c++) {
+        const int ref = nodes[node].child[c];
+        if (ref >= 0) { test(ref, 0); test(ref, 1); } // inner child: its two children join the wide node
+        else if (ref != CRT_TRAV_DONE) test(node, c);
+    }
+    std::sort(cand, cand + nc, [](const WideCand& a, const WideCand& b) { return a.tn < b.tn; });
+    for (int k = 0; k < nc; k++) {
+        if (cand[k].tn > h.t) continue; // culled by a hit found in a nearer child
+        if (cand[k].ref >= 0) wide_visit(S, nodes, cand[k].ref, r, t_min, h);
+        else {
+            g_wide_prims++;
+            float t;
+            const int code = ~cand[k].ref;
+            if (leaf_test<false, false>(S, code, r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) { h.t = t; h.leaf = code; }
+        }
+    }
+}
+Hit wide_lane(const SceneView& S, const CrtPackedNode* nodes, const TravRay& r, float t_min)
+{
+    Hit h;
+    h.t = 3.402823466e+38f;
+    h.leaf = -1;
+    const int cur = trav_begin<false, false>(S, r, t_min, h);
+    if (cur >= 0) wide_visit(S, nodes, cur, r, t_min, h);
+    else if (cur != CRT_TRAV_DONE) {
+        float t;
+        if (leaf_test<false, false>(S, ~cur, r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) { h.t = t; h.leaf = ~cur; }
+    }
+    return h;
+}
+
 } // namespace
 
 int main(int argc, char** argv)
@@ -220,6 +269,10 @@ int main(int argc, char** argv)
         got[4] = pair_ok ? pair_lane<false>(So, r, t_min, visits) : got[2];
         got[5] = pair_ok && spheres_only ? pair_lane<true>(So, r, t_min, visits) : got[4];
         hits += want.leaf >= 0;
+        {
+            const Hit w = wide_lane(Sg, P.nodes.data(), r, t_min);
+            if (w.leaf != want.leaf || memcmp(&w.t, &want.t, 4) != 0) { if (mism++ < 5) fprintf(stderr, "ray %d 4-wide walk: leaf %d t %.9g, brute force: leaf %d t %.9g\n", i, w.leaf, w.t, want.leaf, want.t); }
+        }
         for (int k = 0; k < 6; k++)
             if (got[k].leaf != want.leaf || memcmp(&got[k].t, &want.t, 4) != 0) {
                 if (mism++ < 5)
@@ -229,6 +282,8 @@ int main(int argc, char** argv)
     printf("scene %d (%d primitives, %d nodes, %d peeled): %d rays, %ld hits, %ld mismatches\n", kind, np, nn, D.n_top, n_rays, hits, mism);
     printf("tree: SAH cost %.3f, depth %d; per ray %.3f node visits, %.3f leaf visits (+ %d peeled tests)\n", P.stats.sah_cost, (int)P.stats.max_depth,
            (double)g_node_visits / (2.0 * n_rays), (double)g_leaf_visits / (2.0 * n_rays), D.n_top);
+    printf("the same tree collapsed 4-wide: per ray %.3f node visits, %.3f box tests, %.3f primitive tests\n", (double)g_wide_visits / n_rays,
+           (double)g_wide_boxes / n_rays, (double)g_wide_prims / n_rays);
     crt_scene_builder_free(sb);
     return mism ? 1 : 0;
 }
