@@ -52,6 +52,11 @@ struct crt_context
 
     // scene
     float4* d_nodes = nullptr;
+    // the node table in the child-interleaved layout of the pipelined kernel's global path (trace.cuh node_visit_pairg): made on
+    // the device from d_nodes when a render needs it and d_nodes has changed since (nodes_gen != pair_gen)
+    float4* d_nodes_pair = nullptr;
+    size_t cap_pair = 0;
+    uint64_t nodes_gen = 1, pair_gen = 0;
     float4* d_prims = nullptr;
     float* d_prim_k = nullptr;
     float4* d_mats = nullptr;
@@ -144,6 +149,7 @@ static crt_status cuda_fail(crt_context* ctx, cudaError_t e, const char* what)
 static void free_geometry(crt_context* ctx)
 {
     cudaFree(ctx->d_nodes); ctx->d_nodes = nullptr;
+    cudaFree(ctx->d_nodes_pair); ctx->d_nodes_pair = nullptr; ctx->cap_pair = 0;
     cudaFree(ctx->d_prims); ctx->d_prims = nullptr;
     cudaFree(ctx->d_prim_k); ctx->d_prim_k = nullptr;
     cudaFree(ctx->d_mats); ctx->d_mats = nullptr;
@@ -163,6 +169,7 @@ static crt_status ensure_geometry(crt_context* ctx, size_t nn, size_t np)
     nn = std::max<size_t>(nn, 1);
     np = std::max<size_t>(np, 1);
     ctx->have_scene = false;
+    ctx->nodes_gen++; // whoever asks for geometry is about to write d_nodes
     if (ctx->d_nodes && nn <= ctx->cap_nodes && np <= ctx->cap_prims && nn * 2 > ctx->cap_nodes && np * 2 > ctx->cap_prims) return CRT_OK;
     free_geometry(ctx);
     CU(cudaMalloc(&ctx->d_nodes, nn * 64));
@@ -900,6 +907,7 @@ crt_status crt_scene_commit(crt_context* ctx, int force_rebuild, int* out_rebuil
         const int np = ctx->scene.n_prims;
         k_bvh_refit<<<(np + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_nodes, ctx->d_prims, ctx->d_prim_k, ctx->d_parent, ctx->d_leaf_ref,
                                                               ctx->d_visits, np, ctx->abs_pad);
+        ctx->nodes_gen++;
         CU(cudaGetLastError());
         ctx->launches += 2;
         CU(cudaStreamSynchronize(ctx->stream)); // recs is a local
@@ -1329,11 +1337,28 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
         // scene and 7 % on the 10k glass/metal scene).
         rem = std::min<long>(rem, ctx->pipe_prefix_bytes);
         budget_used = (long)n_slots * per_slot + rem;
-        A.scene.smem_nodes = (int)std::min<long>(A.scene.n_nodes, rem / node_b); rem -= (long)A.scene.smem_nodes * node_b;
+        // slot 0 of the staged table is the dummy node of node_visit_pairg
+        A.scene.smem_nodes = (int)std::max<long>(0, std::min<long>(A.scene.n_nodes, rem / node_b - 1)); rem -= ((long)A.scene.smem_nodes + 1) * node_b;
         A.scene.smem_prims = (int)std::min<long>(A.scene.n_prims, rem / 16); rem -= (long)A.scene.smem_prims * 16;
         A.scene.smem_mats = (int)std::min<long>(A.scene.n_prims, rem / 32); rem -= (long)A.scene.smem_mats * 32;
     }
     const size_t smem = (size_t)(budget_used - rem);
+    if (!all) { // the nodes behind the staged prefix are read in the child-interleaved layout
+        const size_t nn = (size_t)A.scene.n_nodes;
+        if (ctx->cap_pair < nn || !ctx->d_nodes_pair) {
+            cudaFree(ctx->d_nodes_pair); ctx->d_nodes_pair = nullptr; ctx->cap_pair = 0;
+            CU(cudaMalloc(&ctx->d_nodes_pair, std::max<size_t>(nn, 1) * 64));
+            ctx->cap_pair = nn;
+            ctx->pair_gen = 0;
+        }
+        if (ctx->pair_gen != ctx->nodes_gen && nn) {
+            k_pair_nodes<<<(unsigned)((nn + 255) / 256), 256, 0, ctx->stream>>>(A.scene.nodes, ctx->d_nodes_pair, (int)nn);
+            CU(cudaGetLastError());
+            ctx->launches++;
+            ctx->pair_gen = ctx->nodes_gen;
+        }
+        A.scene.nodes_pair = ctx->d_nodes_pair;
+    }
 
     PipeArgs W;
     memset(&W, 0, sizeof(W));

@@ -21,6 +21,7 @@ struct DevImage
 struct DevScene
 {
     const float4* nodes;   // 4 x float4 per node
+    const float4* nodes_pair; // the same nodes child-interleaved (trace.cuh crt_pair_node), or NULL: only k_render_pipe's global path reads it
     const float4* prims;   // 1 x float4 per primitive
     const float* prim_k;   // rect plane offsets
     const float4* mats;    // 2 x float4 per primitive

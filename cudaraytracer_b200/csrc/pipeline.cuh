@@ -251,12 +251,24 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
     pipe_push(P, ctl, PQ_GEN, ended, slot, lt);
 }
 
+// The child-interleaved copy of the packed node table that the global path of k_render_pipe reads (trace.cuh crt_pair_node).
+__global__ void k_pair_nodes(const float4* __restrict__ nodes, float4* __restrict__ out, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 q0, q1, q2, q3;
+    crt_pair_node(nodes[4 * (size_t)i], nodes[4 * (size_t)i + 1], nodes[4 * (size_t)i + 2], nodes[4 * (size_t)i + 3], q0, q1, q2, q3);
+    out[4 * (size_t)i] = q0; out[4 * (size_t)i + 1] = q1; out[4 * (size_t)i + 2] = q2; out[4 * (size_t)i + 3] = q3;
+}
+
 // NSLOTS > 0: the pool size is a compile-time constant. The pool sits at the START of dynamic shared memory, so every pool
 // and ring address is `constant + index`: with a run-time N behind the scene tables the compiler re-derived those addresses from
 // kernel parameters at each use (3.7 % of the executed instructions, profiles/r01_j). NSLOTS == 0 takes N from the arguments.
 // A traversal round is node, node, node, leaf: a lane that reaches a leaf sits the remaining node visits of the round out, and
 // ONE leaf visit serves them all (measured against node, leaf, node, leaf: +7 % on C2, +4 % on the 1 M-sphere scene; two or
 // four node visits per leaf visit are slower, profiles/r02_a_*).
+// Both paths: branch-free node visit on child-interleaved nodes (FFMA2), dummy node for idle lanes, sentinel stack in PTX.
+// Scene larger than shared memory: 64-byte nodes from the child-interleaved global table, a prefix of it staged (node_visit_pairg).
 // SMEM_ALL (the whole scene is staged): the nodes take the PAIR layout of trace.cuh (48-byte nodes: binary16 half-extents,
 // 16-bit references) and node_visit_pair (FFMA2, branch-free, dummy node for idle lanes, sentinel stack pushed / popped in PTX).
 // SPH: the scene holds only spheres (DevScene::spheres_only, chosen by the host): leaf visits without the type dispatch.
@@ -275,7 +287,7 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
     P.ring = reinterpret_cast<unsigned short*>(smem + 3 * P.n + P.n / 2);
     // 70 bytes per slot: N is a multiple of 64, so the scene tables that follow stay 16-byte aligned
     constexpr bool PAIR = SMEM_ALL;
-    const SceneView S = stage_scene<true, PAIR>(A.R.scene, smem + (3 * P.n + P.n / 2) + (PQ_COUNT * P.n) / 8);
+    const SceneView S = stage_scene<true, PAIR, !PAIR>(A.R.scene, smem + (3 * P.n + P.n / 2) + (PQ_COUNT * P.n) / 8);
     for (int i = threadIdx.x; i < PQ_COUNT * P.n; i += PIPE_THREADS) P.ring[i] = (unsigned short)(i >= PQ_GEN * P.n ? i - PQ_GEN * P.n : PIPE_EMPTY);
     if (threadIdx.x <= PQ_COUNT) { ctl.head[threadIdx.x] = 0u; ctl.tail[threadIdx.x] = threadIdx.x == PQ_GEN ? (unsigned int)P.n : 0u; }
     if (threadIdx.x == 0) ctl.live = P.n; // every slot starts in the GEN queue
@@ -283,14 +295,13 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
 
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, lt = (1u << lane) - 1u;
     const float t_min = 0.001f;
-    int slot = -1, cur = CRT_TRAV_DONE, sp = 0;
+    int slot = -1, cur = CRT_TRAV_DONE;
     TravRay r = trav_setup<false>(f3(0.f, 0.f, 0.f), f3(0.f, 0.f, 1.f));
     Hit h;
     h.t = 3.402823466e+38f; // node_visit_pair: t_hit >= t_min in every lane, also in those that have no ray yet
     h.leaf = -1;
     int stack[CRT_STACK_SIZE];
-    StackPtr top = 0; // PAIR: the stack is reached through `top` (sentinel below the first entry), otherwise through `sp`
-    if (PAIR) top = stk_begin(stack);
+    StackPtr top = stk_begin(stack); // sentinel below the first entry: a pop of the empty stack yields "finished"
     const StackPtr top0 = top;
     unsigned int shard_cursor = (blockIdx.x * PIPE_WARPS + warp) & (WF_SHARDS - 1);
     bool exhausted = false;
@@ -345,7 +356,6 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
                 h.t = 3.402823466e+38f;
                 h.leaf = -1;
                 cur = trav_begin<false, SMEM_ALL, PAIR, SPH>(S, r, t_min, h);
-                sp = 0;
                 top = top0;
             }
             refill_short = n < __popc(m);
@@ -367,10 +377,10 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
                 }
             }
             else {
-                node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
-                node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
-                node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
-                if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack);
+                node_visit_pairg(S, r, t_min, h.t, cur, top);
+                node_visit_pairg(S, r, t_min, h.t, cur, top);
+                node_visit_pairg(S, r, t_min, h.t, cur, top);
+                if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step_pairg<SMEM_ALL>(S, r, t_min, h, cur, top);
             }
             if (__popc(__ballot_sync(0xffffffffu, cur != CRT_TRAV_DONE)) < leave_below) break;
         }

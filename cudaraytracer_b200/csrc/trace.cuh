@@ -14,6 +14,7 @@
 struct SceneView
 {
     const float4* g_nodes;
+    const float4* g_nodes_pair; // child-interleaved copy of g_nodes (crt_pair_node), for node_visit_pairg
     const float4* g_prims;
     const float* g_prim_k;
     const float4* g_mats;
@@ -172,17 +173,33 @@ __device__ __forceinline__ float2 crt_h2_to_f2(unsigned w)
 #endif
 }
 
+// ---- The child-interleaved 64-byte node of the pipelined kernel's GLOBAL path (scenes that do not fit in shared memory) ----
+// Same content as the packed node of crt_internal.h, reordered so that each 64-bit half of a 128-bit word holds the same
+// quantity of BOTH children ({c0.x, c1.x, c0.y, c1.y} {c0.z, c1.z, h0.x, h1.x} {h0.y, h1.y, h0.z, h1.z} {child0, child1, -, -}):
+// node_visit_pairg then runs the FFMA2 arithmetic of the PAIR path on two LDG.256. The table is made on the device
+// (k_pair_nodes) whenever the packed nodes have changed; the first smem_nodes of it are staged, behind a dummy node.
+__host__ __device__ __forceinline__ void crt_pair_node(const float4& g0, const float4& g1, const float4& g2, const float4& g3, float4& q0,
+                                                       float4& q1, float4& q2, float4& q3)
+{
+    q0 = make_float4(g0.x, g1.z, g0.y, g1.w);
+    q1 = make_float4(g0.z, g2.x, g0.w, g2.y);
+    q2 = make_float4(g1.x, g2.z, g1.y, g2.w);
+    q3 = g3;
+}
+
 // Stages the first smem_* entries of each table into dynamic shared memory. Call from every thread, then __syncthreads().
 // PAIR (needs PAD and the whole tree in shared memory): the 48-byte nodes above, plus a dummy node behind the last one.
-template <bool PAD, bool PAIR = false> __device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem)
+// PAIRG (needs PAD): 80-byte slots holding child-interleaved nodes; slot 0 is the dummy node, node i sits in slot i + 1.
+template <bool PAD, bool PAIR = false, bool PAIRG = false> __device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem)
 {
     SceneView S;
-    S.g_nodes = D.nodes; S.g_prims = D.prims; S.g_prim_k = D.prim_k; S.g_mats = D.mats; S.images = D.images;
+    S.g_nodes = D.nodes; S.g_nodes_pair = D.nodes_pair; S.g_prims = D.prims; S.g_prim_k = D.prim_k; S.g_mats = D.mats; S.images = D.images;
     S.smem_nodes = D.smem_nodes; S.smem_prims = D.smem_prims; S.smem_mats = D.smem_mats;
     S.entry = D.entry; S.n_top = D.n_top;
     for (int k = 0; k < CRT_MAX_TOP; k++) { S.top_code[k] = D.top_code[k]; S.top_pair[k] = PAIR ? pair_ref(~D.top_code[k]) : 0; }
     float4* sn = smem;
-    float4* sp = sn + (PAIR ? CRT_PAIR_NODE_F4 * (size_t)(D.smem_nodes + 1) : (PAD ? CRT_SMEM_NODE_F4 : 4) * (size_t)D.smem_nodes);
+    float4* sp = sn + (PAIR ? CRT_PAIR_NODE_F4 * (size_t)(D.smem_nodes + 1) : PAIRG ? CRT_SMEM_NODE_F4 * (size_t)(D.smem_nodes + 1)
+                                                                                    : (PAD ? CRT_SMEM_NODE_F4 : 4) * (size_t)D.smem_nodes);
     float4* sm = sp + D.smem_prims;
     const int tid = threadIdx.x, nt = blockDim.x;
     if (PAIR) {
@@ -211,12 +228,30 @@ template <bool PAD, bool PAIR = false> __device__ __forceinline__ SceneView stag
         }
         S.entry = pair_ref(D.entry);
     }
+    else if (PAIRG) {
+        for (int i = tid; i <= D.smem_nodes; i += nt) {
+            float4 q0, q1, q2, q3;
+            if (i == 0) { // the dummy node (see above), binary32 here
+                const float inf = __uint_as_float(0x7f800000u);
+                q0 = make_float4(0.f, 0.f, 0.f, 0.f);
+                q1 = make_float4(0.f, 0.f, inf, -inf);
+                q2 = make_float4(inf, -inf, inf, -inf);
+                q3 = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            else {
+                const float4* g = D.nodes + 4 * (size_t)(i - 1);
+                crt_pair_node(__ldg(g), __ldg(g + 1), __ldg(g + 2), __ldg(g + 3), q0, q1, q2, q3);
+            }
+            float4* d = sn + CRT_SMEM_NODE_F4 * (size_t)i;
+            d[0] = q0; d[1] = q1; d[2] = q2; d[3] = q3;
+        }
+    }
     else
     for (int i = tid; i < 4 * D.smem_nodes; i += nt) {
         const float4 v = __ldg(D.nodes + i);
         sn[PAD ? CRT_SMEM_NODE_F4 * (i >> 2) + (i & 3) : (i & 3) * D.smem_nodes + (i >> 2)] = v;
     }
-    S.dummy = CRT_PAIR_NODE_F4 * D.smem_nodes; // in 16-byte units, like every PAIR node reference
+    S.dummy = CRT_PAIR_NODE_F4 * D.smem_nodes; // PAIR: in 16-byte units, like every PAIR node reference
     for (int i = tid; i < D.smem_prims; i += nt) sp[i] = __ldg(D.prims + i);
     for (int i = tid; i < 2 * D.smem_mats; i += nt) sm[i] = __ldg(D.mats + i);
     S.s_nodes = sn; S.s_prims = sp; S.s_mats = sm;
@@ -447,6 +482,56 @@ __device__ __forceinline__ void node_visit_pair(const SceneView& S, const TravRa
     int next = first;
     stk_visit(top, h0 && h1, !(h0 || h1), other, next);
     if (at) cur = next;
+}
+
+// The same visit for scenes that do NOT fit in shared memory (stage_scene<true, false, true>): `cur` >= 0 is a node index, the
+// child references are those of crt_internal.h. Nodes below smem_nodes come from the staged prefix (slot i + 1; slot 0 is the
+// dummy node, which lanes that are not at an inner node visit as index -1), the others from the child-interleaved global
+// table with two LDG.256. Everything after the loads is the arithmetic of node_visit_pair in binary32.
+__device__ __forceinline__ void node_visit_pairg(const SceneView& S, const TravRay& r, float t_min, float t_hit, int& cur, StackPtr& top)
+{
+    const bool at = cur >= 0;
+    const int i = at ? cur : -1;
+    float4 q0, q1, q2;
+    int2 ch;
+    if (i < S.smem_nodes) {
+        const float4* p = S.s_nodes + CRT_SMEM_NODE_F4 * (i + 1);
+        q0 = p[0]; q1 = p[1]; q2 = p[2];
+        ch = *reinterpret_cast<const int2*>(p + 3);
+    }
+    else {
+        const float4* p = S.g_nodes_pair + 4 * (size_t)i;
+        float4 q3;
+        ldg256(p, q0, q1);
+        ldg256(p + 2, q2, q3);
+        ch = make_int2(__float_as_int(q3.x), __float_as_int(q3.y));
+    }
+    const float2 mx = fma2ss(make_float2(q0.x, q0.y), r.id.x, -r.ood.x);
+    const float2 my = fma2ss(make_float2(q0.z, q0.w), r.id.y, -r.ood.y);
+    const float2 mz = fma2ss(make_float2(q1.x, q1.y), r.id.z, -r.ood.z);
+    const float2 nx = fma2s(make_float2(-q1.z, -q1.w), r.aid.x, mx), fx = fma2s(make_float2(q1.z, q1.w), r.aid.x, mx);
+    const float2 ny = fma2s(make_float2(-q2.x, -q2.y), r.aid.y, my), fy = fma2s(make_float2(q2.x, q2.y), r.aid.y, my);
+    const float2 nz = fma2s(make_float2(-q2.z, -q2.w), r.aid.z, mz), fz = fma2s(make_float2(q2.z, q2.w), r.aid.z, mz);
+    const float tn0 = fmaxf(fmaxf(nx.x, ny.x), fmaxf(nz.x, t_min)), tf0 = fminf(fminf(fx.x, fy.x), fminf(fz.x, t_hit));
+    const float tn1 = fmaxf(fmaxf(nx.y, ny.y), fmaxf(nz.y, t_min)), tf1 = fminf(fminf(fx.y, fy.y), fminf(fz.y, t_hit));
+    const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+    const bool second_first = h1 && (tn1 < tn0 || !h0); // child 1 is the nearer hit child, or the only one
+    const int first = second_first ? ch.y : ch.x, other = second_first ? ch.x : ch.y;
+    int next = first;
+    stk_visit(top, h0 && h1, !(h0 || h1), other, next);
+    if (at) cur = next;
+}
+// ... and its leaf visit: `cur` = ~leaf code, sentinel stack.
+template <bool SMEM_ALL>
+__device__ __forceinline__ void leaf_step_pairg(const SceneView& S, const TravRay& r, float t_min, Hit& h, int& cur, StackPtr& top)
+{
+    const int code = ~cur;
+    float t;
+    if (leaf_test<false, SMEM_ALL>(S, code, r.o, r.d, r.a, r.inv_a, t_min, h.t, t)) {
+        h.t = t;
+        h.leaf = code;
+    }
+    cur = stk_pop(top);
 }
 
 // One inner-node visit: slab-test both child boxes against (t_min, t_hit), descend into the nearer hit child and push the

@@ -128,6 +128,34 @@ template <bool SPH> Hit pair_lane(const SceneView& S, const TravRay& r, float t_
     return h;
 }
 
+// the lane of the scenes that do not fit in shared memory: node_visit_pairg on the child-interleaved global table, part of it staged
+Hit pairg_lane(const SceneView& S, const TravRay& r, float t_min, long& visits)
+{
+    Hit h;
+    h.t = 3.402823466e+38f;
+    h.leaf = -1;
+    int stack[CRT_STACK_SIZE];
+    StackPtr top = stk_begin(stack);
+    int cur = trav_begin<false, false>(S, r, t_min, h);
+    while (cur != CRT_TRAV_DONE) {
+        for (int k = 0; k < 3; k++) {
+            StackPtr before = top;
+            const bool at = cur >= 0;
+            node_visit_pairg(S, r, t_min, h.t, cur, top);
+            if (!at && top != before) { fprintf(stderr, "the dummy node moved the stack (global path)\n"); exit(3); }
+        }
+        if (cur < 0 && cur != CRT_TRAV_DONE) leaf_step_pairg<false>(S, r, t_min, h, cur, top);
+        if (++visits > 100000000L) { fprintf(stderr, "traversal does not terminate\n"); exit(3); }
+        if (top - stack < 0 || top - stack > CRT_STACK_SIZE) { fprintf(stderr, "stack pointer out of range: %d\n", (int)(top - stack)); exit(3); }
+    }
+    for (int k = 0; k < 3; k++) {
+        StackPtr before = top;
+        node_visit_pairg(S, r, t_min, h.t, cur, top);
+        if (cur != CRT_TRAV_DONE || top != before) { fprintf(stderr, "an idle lane moved on the dummy node (global path)\n"); exit(3); }
+    }
+    return h;
+}
+
 // Statistic only: what a 4-wide tree would cost. The binary tree is collapsed on the fly - a 4-wide node is a
 // binary node with each inner child replaced by that child's two children - and traversed near-first with the same slab
 // arithmetic; counted are 4-wide node visits, box tests and primitive tests. The closest hit must be the binary tree's.
@@ -230,6 +258,17 @@ int main(int argc, char** argv)
     // the PAIR staging exists for scenes that fit in shared memory: 16-bit references (trace.cuh)
     const bool pair_ok = np <= CRT_PAIR_MAX_PRIMS && CRT_PAIR_NODE_F4 * (nn + 1) < CRT_PAIR_LEAF;
     const SceneView So = pair_ok ? stage_scene<true, true>(D, smem2.data()) : Sp;
+    // the global path of the pipelined kernel: child-interleaved table behind the 'global' pointer, the first half of it staged
+    std::vector<float4> pair_tab((size_t)std::max(nn, 1) * 4);
+    for (int i = 0; i < nn; i++) {
+        const float4* g = D.nodes + 4 * (size_t)i;
+        crt_pair_node(g[0], g[1], g[2], g[3], pair_tab[4 * (size_t)i], pair_tab[4 * (size_t)i + 1], pair_tab[4 * (size_t)i + 2], pair_tab[4 * (size_t)i + 3]);
+    }
+    D.nodes_pair = pair_tab.data();
+    D.smem_nodes = nn / 2; D.smem_prims = 0; D.smem_mats = 0;
+    std::vector<float4> smem4((size_t)(nn / 2 + 1) * CRT_SMEM_NODE_F4 + 16);
+    const SceneView Sq = stage_scene<true, false, true>(D, smem4.data());
+    D.smem_nodes = nn; D.smem_prims = np; D.smem_mats = np;
     bool spheres_only = true;
     for (int c : leaf_code) if (((c >> CRT_LEAF_TYPE_SHIFT) & 3) != CRT_SPHERE) spheres_only = false;
 
@@ -261,19 +300,20 @@ int main(int argc, char** argv)
         const TravRay r = trav_setup<false>(o, d);
         const Hit want = brute_force(Sp, np, leaf_code, r, t_min);
         unsigned nb = 0, npr = 0;
-        Hit got[6];
+        Hit got[7];
         got[0] = closest_hit<false, false, false>(Sg, o, d, t_min, 3.402823466e+38f, nb, npr); // megakernel form, global tables
         got[1] = closest_hit<false, false, true>(Sw, o, d, t_min, 3.402823466e+38f, nb, npr);  // ... tables in 'shared memory'
         got[2] = pipe_lane<true>(Sp, r, t_min, visits);
         got[3] = pipe_lane<false>(Sg, r, t_min, visits); // nodes behind the 'global' pointers (scenes that do not fit)
         got[4] = pair_ok ? pair_lane<false>(So, r, t_min, visits) : got[2];
         got[5] = pair_ok && spheres_only ? pair_lane<true>(So, r, t_min, visits) : got[4];
+        got[6] = pairg_lane(Sq, r, t_min, visits);
         hits += want.leaf >= 0;
         {
             const Hit w = wide_lane(Sg, P.nodes.data(), r, t_min);
             if (w.leaf != want.leaf || memcmp(&w.t, &want.t, 4) != 0) { if (mism++ < 5) fprintf(stderr, "ray %d 4-wide walk: leaf %d t %.9g, brute force: leaf %d t %.9g\n", i, w.leaf, w.t, want.leaf, want.t); }
         }
-        for (int k = 0; k < 6; k++)
+        for (int k = 0; k < 7; k++)
             if (got[k].leaf != want.leaf || memcmp(&got[k].t, &want.t, 4) != 0) {
                 if (mism++ < 5)
                     fprintf(stderr, "ray %d form %d: leaf %d t %.9g, brute force: leaf %d t %.9g\n", i, k, got[k].leaf, got[k].t, want.leaf, want.t);
