@@ -123,6 +123,7 @@ SIGNATURES = {
     "crt_render": (C.c_int, [_P, C.POINTER(RenderParams)]),
     "crt_resolve": (C.c_int, [_P, _P]),
     "crt_resolve_device": (C.c_int, [_P, _P]),
+    "crt_resolve_device_truncated": (C.c_int, [_P, _P]),
     "crt_read_accum": (C.c_int, [_P, _P]),
     "crt_read_accum_static": (C.c_int, [_P, _P, C.c_uint32, _P]),
     "crt_resolve_rows": (C.c_int, [_P, C.c_uint32, _P]),

@@ -1516,6 +1516,21 @@ crt_status crt_resolve_device(crt_context* ctx, void* device_out_rgba8)
     return CRT_OK;
 }
 
+crt_status crt_resolve_device_truncated(crt_context* ctx, void* device_out_rgba8)
+{
+    NvtxRange nvtx_range("crt_resolve_device_truncated");
+    if (!ctx || !device_out_rgba8) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_resolve_device_truncated: NULL argument");
+    if (!ctx->d_accum) return crt_set_error(ctx, CRT_ERR_STATE, "crt_resolve_device_truncated: no framebuffer");
+    CU(cudaSetDevice(ctx->device));
+    const uint32_t cw = ctx->width / 16 * 16, ch = ctx->height / 16 * 16; // Kernel.cu:183-184: grid = (W / 16, H / 16) blocks of 16 x 16
+    const uint32_t n = cw * ch;
+    if (n == 0) return CRT_OK;
+    k_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_accum, (uint32_t*)device_out_rgba8, ctx->width, cw, ch, 0u, 0u, 0u);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return CRT_OK;
+}
+
 crt_status crt_resolve_rows(crt_context* ctx, uint32_t row_tiles, void* device_out_rgba8)
 {
     NvtxRange nvtx_range("crt_resolve_rows");

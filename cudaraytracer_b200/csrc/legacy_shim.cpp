@@ -134,7 +134,8 @@ void LaunchKernel(unsigned int* pos, unsigned int image_width, unsigned int imag
     p.jitter = CRT_JITTER_RANDOM;
     const char* trunc = getenv("CRT_LEGACY_TRUNCATED_GRID");
     p.flags = (trunc && atoi(trunc)) ? CRT_FLAG_TRUNCATED_GRID : 0;
-    if (crt_render(ctx, &p) != CRT_OK || crt_resolve_device(ctx, pos) != CRT_OK || crt_synchronize(ctx) != CRT_OK) {
+    // truncated grid: the pixels the reference's launch does not cover keep what the caller's buffer held
+    if (crt_render(ctx, &p) != CRT_OK || (p.flags ? crt_resolve_device_truncated(ctx, pos) : crt_resolve_device(ctx, pos)) != CRT_OK || crt_synchronize(ctx) != CRT_OK) {
         fprintf(stderr, "[crt] LaunchKernel: %s\n", crt_last_error_string(ctx));
         return;
     }

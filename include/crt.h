@@ -220,6 +220,9 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* params);
 /* mean -> 255*sqrt -> clamp -> pack A<<24|B<<16|G<<8|R (Kernel.cu:12-19,151-157). out is HOST memory. Synchronises. */
 crt_status crt_resolve(crt_context* ctx, uint32_t* out_rgba8);
 crt_status crt_resolve_device(crt_context* ctx, void* device_out_rgba8); /* async */
+/* The same for the pixels a CRT_FLAG_TRUNCATED_GRID render covers, (W / 16 * 16) x (H / 16 * 16): the other pixels of the
+ * buffer are left untouched, as the reference's launch grid leaves them (Kernel.cu:183-184 with :117-119). Async. */
+crt_status crt_resolve_device_truncated(crt_context* ctx, void* device_out_rgba8);
 crt_status crt_read_accum(crt_context* ctx, float* out_float4);          /* width*height*4 floats, synchronises */
 /* crt_read_accum for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
  * cudaMalloc). NO COUNTERPART IN THE REFERENCE. Converts n_pixels entries of the

@@ -114,6 +114,57 @@ def test_legacy_launchkernel_drop_in():
 
 
 @needs_refhost
+def test_legacy_launchkernel_coverage_in_both_grid_modes(monkeypatch):
+    """W and H that are NOT multiples of 16. The reference launches (W / 16) x (H / 16) blocks of 16 x 16 (Kernel.cu:183-184), so it
+    leaves the last W % 16 columns and H % 16 rows of the caller's buffer untouched. The drop-in LaunchKernel renders EVERY
+    pixel by default (documented deviation) and reproduces the reference's coverage exactly when
+    CRT_LEGACY_TRUNCATED_GRID=1 - checked here against the reference kernel's own output where its build is present.
+    Also times the shim's per-frame host work (pointer walk + hash of the caller's scene graph) against the frame it wraps."""
+    import time
+    import torch
+    lib = capi.load()
+    W, H, spp, depth = 200, 150, 4, 12
+    sentinel = 0x11223344
+    s = Scene.generate(capi.SCENE_REFERENCE_DEFAULT, 1984)
+    cam = s.default_camera(W, H)
+    handle, world = O.refhost_world(s)
+    yy, xx = np.mgrid[0:H, 0:W]
+    covered = (xx < W // 16 * 16) & (yy < H // 16 * 16)
+    try:
+        pos = torch.full((W * H,), sentinel, dtype=torch.int32, device="cuda")
+        monkeypatch.delenv("CRT_LEGACY_TRUNCATED_GRID", raising=False)
+        lib.LaunchKernel(C.c_void_p(pos.data_ptr()), W, H, spp, depth, C.c_void_p(world), None, cam)
+        img = pos.cpu().numpy().view(np.uint32).reshape(H, W)
+        assert (img >> 24 == 255).all(), "default mode: every pixel is rendered"
+        assert (img != sentinel).all()
+
+        pos.fill_(sentinel)
+        monkeypatch.setenv("CRT_LEGACY_TRUNCATED_GRID", "1")
+        lib.LaunchKernel(C.c_void_p(pos.data_ptr()), W, H, spp, depth, C.c_void_p(world), None, cam)
+        img = pos.cpu().numpy().view(np.uint32).reshape(H, W)
+        assert (img[covered] >> 24 == 255).all()
+        assert (img[~covered] == sentinel).all(), "truncated mode: the pixels outside the reference's grid keep the caller's bytes"
+        if O.have_refkernel():
+            ref, _ = O.refkernel_render(s, cam, W, H, spp, depth)  # its harness hands the kernel a zeroed buffer
+            assert np.array_equal(ref >> 24 == 255, covered), "the reference kernel covers exactly the truncated grid"
+
+        # the shim's own cost per frame on an unchanged scene: wall clock of LaunchKernel minus the device time of the frame
+        monkeypatch.delenv("CRT_LEGACY_TRUNCATED_GRID", raising=False)
+        lib.LaunchKernel(C.c_void_p(pos.data_ptr()), W, H, spp, depth, C.c_void_p(world), None, cam)
+        t0 = time.perf_counter()
+        n = 20
+        for _ in range(n):
+            lib.LaunchKernel(C.c_void_p(pos.data_ptr()), W, H, spp, depth, C.c_void_p(world), None, cam)
+        wall_ms = (time.perf_counter() - t0) / n * 1e3
+        print(f"LaunchKernel drop-in, reference default scene {W}x{H} {spp} spp: {wall_ms:.3f} ms per frame wall clock "
+              f"(flatten + hash of the scene graph, clear, render, resolve, synchronise)")
+        assert wall_ms < 50.0
+    finally:
+        lib.crt_legacy_shutdown()
+        O.refhost_world_destroy(handle)
+
+
+@needs_refhost
 def test_scene_from_reference_accepts_a_hittablelist_root():
     """crt_scene_from_reference with the reference's scene graph behind a HittableList root (Hittable.cuh:532-581: a list whose
     elements are BVHNode hittables) flattens to the same scene as the BVH root itself (what Kernel.cu:40 is handed): identical
