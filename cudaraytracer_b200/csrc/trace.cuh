@@ -480,7 +480,9 @@ __device__ __forceinline__ void node_visit_pair(const SceneView& S, const TravRa
     const int r0 = (int)(w2.y & 0xffffu), r1 = (int)(w2.y >> 16);
     const int first = second_first ? r1 : r0, other = second_first ? r0 : r1;
     int next = first;
-    stk_visit(top, h0 && h1, !(h0 || h1), other, next);
+    // `at` on the push: a lane that is not at a node reads the dummy node, whose child 1 can only "hit" if the lane's ray constants
+    // are not finite (NaN drops out of min / max); such a lane must still not move its stack
+    stk_visit(top, at && h0 && h1, !(h0 || h1), other, next);
     if (at) cur = next;
 }
 
@@ -518,7 +520,9 @@ __device__ __forceinline__ void node_visit_pairg(const SceneView& S, const TravR
     const bool second_first = h1 && (tn1 < tn0 || !h0); // child 1 is the nearer hit child, or the only one
     const int first = second_first ? ch.y : ch.x, other = second_first ? ch.x : ch.y;
     int next = first;
-    stk_visit(top, h0 && h1, !(h0 || h1), other, next);
+    // `at` on the push: a lane that is not at a node reads the dummy node, whose child 1 can only "hit" if the lane's ray constants
+    // are not finite (NaN drops out of min / max); such a lane must still not move its stack
+    stk_visit(top, at && h0 && h1, !(h0 || h1), other, next);
     if (at) cur = next;
 }
 // ... and its leaf visit: `cur` = ~leaf code, sentinel stack.
