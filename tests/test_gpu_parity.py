@@ -360,6 +360,33 @@ def test_variants_bit_identical_to_megakernel(renderer, name, kind, hint, W, H, 
         f"{(mega != wave).any(axis=-1).sum()} of {W * H} pixels differ between the variants"
 
 
+@pytest.mark.parametrize("what", ["nan_origin", "nan_direction", "inf_direction"])
+@pytest.mark.parametrize("kind,hint", [(capi.SCENE_RTIOW, 0), (capi.SCENE_GRID_1M, 60)], ids=["staged_tree", "tree_behind_l1"])
+def test_non_finite_rays_terminate_and_the_variants_agree(renderer, kind, hint, what):
+    """Rays whose origin or direction is not finite (a camera the caller filled with NaN / Inf; in a long render also the rare
+    degenerate scatter). NaN drops out of the min / max of a slab test, so such a ray "hits" every box: it must walk the tree
+    once and end (no stack corruption - lanes waiting on the pipelined kernel's dummy node included), and every variant must put
+    the same bits into the accumulation buffer. The reference accepts any InputStruct too (Kernel.cu:130-146)."""
+    W, H = 96, 54
+    s = Scene.generate(kind, 1984, hint)
+    cam = s.default_camera(W, H)
+    if what == "nan_origin":
+        cam.origin_x = float("nan")
+    elif what == "nan_direction":
+        cam.orientation_y = float("nan")
+    else:
+        cam.far_plane = float("inf")
+    _setup(renderer, s, cam, W, H)
+    bufs = []
+    for variant in (capi.VARIANT_MEGAKERNEL, capi.VARIANT_PIPELINE, capi.VARIANT_WAVEFRONT):
+        renderer.clear()
+        renderer.render(spp=3, max_depth=8, variant=variant)
+        bufs.append(renderer.read_accum().view(np.uint32).copy())
+    assert (bufs[0].view(np.float32)[..., 3] == 3).all()
+    assert np.array_equal(bufs[0], bufs[1]), "pipeline differs from the megakernel"
+    assert np.array_equal(bufs[0], bufs[2]), "wavefront differs from the megakernel"
+
+
 @pytest.mark.parametrize("variant", [capi.VARIANT_WAVEFRONT, capi.VARIANT_PIPELINE], ids=["wavefront", "pipeline"])
 def test_small_pool_progressive_and_sharded(monkeypatch, variant):
     """A pool much smaller than the work (regeneration + drain), progressive calls, and spp sharding: all bit-identical."""
