@@ -1485,7 +1485,21 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
         bool all = false;
         size_t smem = plan_smem(ctx, mega_blocks_per_sm(exact, count), A.scene, all);
         dim3 grid(((A.cover_w + 15) / 16) * ((A.cover_h + 15) / 16));
-        CU(dispatch_mega(A, grid, smem, ctx->stream, exact, count, all));
+        const bool pair_ok = A.scene.n_prims <= CRT_PAIR_MAX_PRIMS && CRT_PAIR_NODE_F4 * ((long)A.scene.n_nodes + 1) < CRT_PAIR_LEAF;
+        if (all && !exact && !count && pair_ok && !getenv("CRT_MEGA_NO_PAIR")) {
+            // whole scene staged: the PAIR layout of trace.cuh (48-byte nodes + a dummy node), never larger than the planned table + 48 B
+            smem = ((size_t)A.scene.n_nodes + 1) * 16 * CRT_PAIR_NODE_F4 + (size_t)A.scene.n_prims * 48;
+            if (A.scene.spheres_only) {
+                CU(cudaFuncSetAttribute(k_render_mega<false, false, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                k_render_mega<false, false, true, 2><<<grid, CRT_BLOCK_THREADS, smem, ctx->stream>>>(A);
+            }
+            else {
+                CU(cudaFuncSetAttribute(k_render_mega<false, false, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                k_render_mega<false, false, true, 1><<<grid, CRT_BLOCK_THREADS, smem, ctx->stream>>>(A);
+            }
+            CU(cudaGetLastError());
+        }
+        else CU(dispatch_mega(A, grid, smem, ctx->stream, exact, count, all));
         ctx->launches++;
     }
     CU(cudaEventRecord(ctx->ev1, ctx->stream));

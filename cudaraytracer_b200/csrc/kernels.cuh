@@ -44,11 +44,13 @@ __device__ __forceinline__ void flush_counters(DevCounters* c, unsigned paths, u
     }
 }
 
-template <bool EXACT, bool COUNT, bool SMEM_ALL>
+// PAIRM (whole scene staged, fast arithmetic, no counting): 0 = the word-major node table and closest_hit; 1 / 2 = the PAIR
+// staging of trace.cuh and closest_hit_pair, 2 when the scene holds only spheres.
+template <bool EXACT, bool COUNT, bool SMEM_ALL, int PAIRM = 0>
 __global__ void __launch_bounds__(CRT_BLOCK_THREADS) k_render_mega(const __grid_constant__ RenderArgs A)
 {
     extern __shared__ float4 smem[];
-    const SceneView S = stage_scene<false>(A.scene, smem);
+    const SceneView S = PAIRM ? stage_scene<true, true>(A.scene, smem) : stage_scene<false>(A.scene, smem);
     __syncthreads();
 
     int x, y;
@@ -78,7 +80,8 @@ __global__ void __launch_bounds__(CRT_BLOCK_THREADS) k_render_mega(const __grid_
             n_paths++;
         }
         n_rays++;
-        Hit h = closest_hit<EXACT, COUNT, SMEM_ALL>(S, o, d, 0.001f, 3.402823466e+38f, n_box, n_prim);
+        Hit h = PAIRM ? closest_hit_pair<PAIRM == 2>(S, o, d, 0.001f, 3.402823466e+38f)
+                      : closest_hit<EXACT, COUNT, SMEM_ALL>(S, o, d, 0.001f, 3.402823466e+38f, n_box, n_prim);
         float3 add;
         if (!scatter_step<SMEM_ALL>(A, S, h, pixel, sample, bounce, o, d, thr, add)) {
             acc_r += crt_to_fixed(add.x); acc_g += crt_to_fixed(add.y); acc_b += crt_to_fixed(add.z);
