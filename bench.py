@@ -361,6 +361,9 @@ def run_gpu_arm(args):
     if rank == 0:
         sampler.start()
     times, (rays, paths, launches) = leg.timed(leg.device_step, args.steps, args.warmup, flush)
+    if args.variant == "auto":  # what AUTO ran: measured by the library where both kernels can stage the scene (crt_last_variant)
+        resolved = {capi.VARIANT_MEGAKERNEL: "mega", capi.VARIANT_WAVEFRONT: "wavefront", capi.VARIANT_PIPELINE: "pipeline"}.get(r.last_variant(), resolved)
+        kernel_name = {"mega": "k_render_mega", "wavefront": "k_wf_extend + k_wf_shade", "pipeline": "k_render_pipe"}[resolved]
     clocks = sampler.stop() if rank == 0 else None
     total_s = sum(times) / 1e3
     value = rays / total_s / 1e6

@@ -122,6 +122,7 @@ SIGNATURES = {
     "crt_accum_device_ptr": (_P, [_P]),
     "crt_render": (C.c_int, [_P, C.POINTER(RenderParams)]),
     "crt_resolve": (C.c_int, [_P, _P]),
+    "crt_last_variant": (C.c_int32, [_P]),
     "crt_resolve_device": (C.c_int, [_P, _P]),
     "crt_resolve_device_truncated": (C.c_int, [_P, _P]),
     "crt_read_accum": (C.c_int, [_P, _P]),

@@ -57,6 +57,12 @@ struct crt_context
     float4* d_nodes_pair = nullptr;
     size_t cap_pair = 0;
     uint64_t nodes_gen = 1, pair_gen = 0;
+    // CRT_VARIANT_AUTO on scenes both kernels can stage completely: the choice is MEASURED on the first samples of a frame and
+    // kept while the tree, the frame size and the depth stay the same (crt_render)
+    uint64_t auto_key = 0;
+    int auto_variant = 0, last_variant = 0;
+    bool auto_calibrate = true; // CRT_AUTO_CALIBRATE=0: the static rule (pipeline from 256 primitives up)
+    cudaEvent_t ev_cal[3] = {nullptr, nullptr, nullptr};
     float4* d_prims = nullptr;
     float* d_prim_k = nullptr;
     float4* d_mats = nullptr;
@@ -246,6 +252,7 @@ crt_status crt_context_create(int device, crt_context** out)
     if ((env = getenv("CRT_PIPE_THRESH")) && atoi(env) > 0) ctx->pipe_thresh = atoi(env);
     if ((env = getenv("CRT_PIPE_ROUNDS")) && atoi(env) > 0) ctx->pipe_rounds = atoi(env);
     if ((env = getenv("CRT_PIPE_SLOTS")) && atoi(env) > 0) ctx->pipe_slots = atoi(env);
+    if ((env = getenv("CRT_AUTO_CALIBRATE"))) ctx->auto_calibrate = atoi(env) != 0;
     if ((env = getenv("CRT_PIPE_PREFIX_KB")) && atoi(env) >= 0) ctx->pipe_prefix_bytes = 1024L * atoi(env);
     if ((env = getenv("CRT_SCENE_CACHE"))) ctx->scene_cache = atoi(env) != 0;
     if ((env = getenv("CRT_BVH_BUILDER"))) {
@@ -287,6 +294,7 @@ void crt_context_destroy(crt_context* ctx)
     cudaFree(ctx->build_arena);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    for (int k = 0; k < 3; k++) if (ctx->ev_cal[k]) cudaEventDestroy(ctx->ev_cal[k]);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
@@ -1412,6 +1420,30 @@ static uint32_t crt_row_tiles_local_rows(uint32_t row_tiles, uint32_t rows, uint
     return (full / world + (rank < full % world ? 1u : 0u)) * tr + (full % world == rank ? rem : 0u);
 }
 
+static crt_status render_mega(crt_context* ctx, RenderArgs A, bool exact, bool count)
+{
+    bool all = false;
+    size_t smem = plan_smem(ctx, mega_blocks_per_sm(exact, count), A.scene, all);
+    dim3 grid(((A.cover_w + 15) / 16) * ((A.cover_h + 15) / 16));
+    const bool pair_ok = A.scene.n_prims <= CRT_PAIR_MAX_PRIMS && CRT_PAIR_NODE_F4 * ((long)A.scene.n_nodes + 1) < CRT_PAIR_LEAF;
+    if (all && !exact && !count && pair_ok && !getenv("CRT_MEGA_NO_PAIR")) {
+        // whole scene staged: the PAIR layout of trace.cuh (48-byte nodes + a dummy node), never larger than the planned table + 48 B
+        smem = ((size_t)A.scene.n_nodes + 1) * 16 * CRT_PAIR_NODE_F4 + (size_t)A.scene.n_prims * 48;
+        if (A.scene.spheres_only) {
+            CU(cudaFuncSetAttribute(k_render_mega<false, false, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_render_mega<false, false, true, 2><<<grid, CRT_BLOCK_THREADS, smem, ctx->stream>>>(A);
+        }
+        else {
+            CU(cudaFuncSetAttribute(k_render_mega<false, false, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_render_mega<false, false, true, 1><<<grid, CRT_BLOCK_THREADS, smem, ctx->stream>>>(A);
+        }
+        CU(cudaGetLastError());
+    }
+    else CU(dispatch_mega(A, grid, smem, ctx->stream, exact, count, all));
+    ctx->launches++;
+    return CRT_OK;
+}
+
 extern "C" {
 
 uint32_t crt_row_tiles_rows(uint32_t row_tiles, uint32_t height)
@@ -1472,8 +1504,56 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
         // dominates (RTIOW 486 prims: 13.0 vs 11.5 Grays/s; 10k prims: 7.5 vs 5.4); below a few hundred primitives its
         // queue handling costs more than the divergence it removes (67 prims: 16.4 vs 21.1) and the megakernel is used.
         int variant = p->variant;
-        if (variant == CRT_VARIANT_AUTO)
+        if (variant == CRT_VARIANT_AUTO) {
             variant = (exact || count || ctx->scene.n_prims < 256) ? CRT_VARIANT_MEGAKERNEL : CRT_VARIANT_PIPELINE;
+            // Where both kernels hold the whole scene in shared memory the better one depends on the scene AND the view (DESIGN.md
+            // 3.1: the pipeline runs at 17-23 Grays/s whatever it is given, the megakernel at 12-64), and every variant writes the
+            // same bits. So the first samples of the frame are rendered by both, timed, and the rest goes to the winner; the choice
+            // is kept while tree, frame size and depth stay what they are. One host synchronisation per such change.
+            const bool both = !exact && !count && ctx->scene.n_prims >= 1 && ctx->scene.n_prims <= CRT_PAIR_MAX_PRIMS;
+            if (both && ctx->auto_calibrate) {
+                uint64_t key = ctx->nodes_gen * 0x9E3779B97F4A7C15ull;
+                for (uint64_t v : {(uint64_t)A.cover_w, (uint64_t)A.cover_h, (uint64_t)A.max_depth, (uint64_t)p->row_tiles, (uint64_t)A.jitter})
+                    key = (key ^ v) * 0x100000001B3ull;
+                key |= 1ull;
+                const uint32_t c = std::min<uint32_t>(8u, A.spp_count / 16u); // samples each kernel is timed on
+                // ... provided they are a launch like the one that follows: on a small frame a few samples measure the fixed cost of a
+                // launch (the pipelined kernel's pool fill and drain), not its rate (400x225: 1 spp 0.14 vs 0.27 ms, 16 spp 1.55 vs 0.46 ms)
+                const bool representative = (uint64_t)A.cover_w * A.cover_h * c >= 1500000ull;
+                if (ctx->auto_key == key) variant = ctx->auto_variant;
+                else if (c >= 1u && representative) {
+                    for (int k = 0; k < 3; k++)
+                        if (!ctx->ev_cal[k]) CU(cudaEventCreate(&ctx->ev_cal[k]));
+                    RenderArgs W = A; // one untimed sample each first (module load, attribute set-up), then c timed samples each
+                    uint32_t at = A.spp_begin;
+                    auto part = [&](int v, uint32_t n) -> crt_status {
+                        W.spp_begin = at; W.spp_count = n;
+                        at += n * A.spp_stride;
+                        return v == CRT_VARIANT_MEGAKERNEL ? render_mega(ctx, W, false, false) : render_pipeline(ctx, W);
+                    };
+                    crt_status cs;
+                    if ((cs = part(CRT_VARIANT_MEGAKERNEL, 1)) != CRT_OK || (cs = part(CRT_VARIANT_PIPELINE, 1)) != CRT_OK) return cs;
+                    CU(cudaEventRecord(ctx->ev_cal[0], ctx->stream));
+                    if ((cs = part(CRT_VARIANT_MEGAKERNEL, c)) != CRT_OK) return cs;
+                    CU(cudaEventRecord(ctx->ev_cal[1], ctx->stream));
+                    if ((cs = part(CRT_VARIANT_PIPELINE, c)) != CRT_OK) return cs;
+                    CU(cudaEventRecord(ctx->ev_cal[2], ctx->stream));
+                    CU(cudaEventSynchronize(ctx->ev_cal[2]));
+                    float t_mega = 0.f, t_pipe = 0.f;
+                    CU(cudaEventElapsedTime(&t_mega, ctx->ev_cal[0], ctx->ev_cal[1]));
+                    CU(cudaEventElapsedTime(&t_pipe, ctx->ev_cal[1], ctx->ev_cal[2]));
+                    variant = t_pipe < t_mega ? CRT_VARIANT_PIPELINE : CRT_VARIANT_MEGAKERNEL;
+                    ctx->auto_key = key;
+                    ctx->auto_variant = variant;
+                    if (getenv("CRT_VERBOSE"))
+                        fprintf(stderr, "[crt] AUTO: megakernel %.3f ms, pipeline %.3f ms for %u samples of %ux%u -> %s\n", t_mega, t_pipe, c, A.cover_w, A.cover_h,
+                                variant == CRT_VARIANT_PIPELINE ? "pipeline" : "megakernel");
+                    A.spp_begin = at;
+                    A.spp_count -= 2u + 2u * c;
+                }
+            }
+        }
+        ctx->last_variant = variant;
         if (variant == CRT_VARIANT_WAVEFRONT || variant == CRT_VARIANT_PIPELINE) {
             if (exact || count) return crt_set_error(ctx, CRT_ERR_UNSUPPORTED, "crt_render: EXACT_MATH / COUNT_TESTS are megakernel-only");
             crt_status ws = variant == CRT_VARIANT_WAVEFRONT ? render_wavefront(ctx, A) : render_pipeline(ctx, A);
@@ -1482,29 +1562,17 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
             ctx->timed = true;
             return CRT_OK;
         }
-        bool all = false;
-        size_t smem = plan_smem(ctx, mega_blocks_per_sm(exact, count), A.scene, all);
-        dim3 grid(((A.cover_w + 15) / 16) * ((A.cover_h + 15) / 16));
-        const bool pair_ok = A.scene.n_prims <= CRT_PAIR_MAX_PRIMS && CRT_PAIR_NODE_F4 * ((long)A.scene.n_nodes + 1) < CRT_PAIR_LEAF;
-        if (all && !exact && !count && pair_ok && !getenv("CRT_MEGA_NO_PAIR")) {
-            // whole scene staged: the PAIR layout of trace.cuh (48-byte nodes + a dummy node), never larger than the planned table + 48 B
-            smem = ((size_t)A.scene.n_nodes + 1) * 16 * CRT_PAIR_NODE_F4 + (size_t)A.scene.n_prims * 48;
-            if (A.scene.spheres_only) {
-                CU(cudaFuncSetAttribute(k_render_mega<false, false, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                k_render_mega<false, false, true, 2><<<grid, CRT_BLOCK_THREADS, smem, ctx->stream>>>(A);
-            }
-            else {
-                CU(cudaFuncSetAttribute(k_render_mega<false, false, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                k_render_mega<false, false, true, 1><<<grid, CRT_BLOCK_THREADS, smem, ctx->stream>>>(A);
-            }
-            CU(cudaGetLastError());
-        }
-        else CU(dispatch_mega(A, grid, smem, ctx->stream, exact, count, all));
-        ctx->launches++;
+        crt_status ms_ = render_mega(ctx, A, exact, count);
+        if (ms_ != CRT_OK) return ms_;
     }
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->timed = true;
     return CRT_OK;
+}
+
+int32_t crt_last_variant(crt_context* ctx)
+{
+    return ctx ? ctx->last_variant : 0;
 }
 
 crt_status crt_last_render_ms(crt_context* ctx, float* out_ms)

@@ -223,6 +223,10 @@ class Renderer:
         self._ck(self.lib.crt_last_render_ms(self.ctx, C.byref(ms)))
         return float(ms.value)
 
+    def last_variant(self) -> int:
+        """The variant the last render() ran (capi.VARIANT_*): what AUTO resolved to, measured where both kernels apply."""
+        return int(self.lib.crt_last_variant(self.ctx))
+
     def resolve(self, out: np.ndarray | None = None) -> np.ndarray:
         if out is None:
             out = np.empty((self.height, self.width), dtype=np.uint32)

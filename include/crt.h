@@ -276,6 +276,14 @@ crt_status crt_get_counters(crt_context* ctx, crt_counters* out);   /* synchroni
 crt_status crt_reset_counters(crt_context* ctx);
 /* GPU milliseconds between the CUDA events that bracketed the last crt_render call (synchronises). */
 crt_status crt_last_render_ms(crt_context* ctx, float* out_ms);
+/* The kernel variant the last crt_render call ran (CRT_VARIANT_MEGAKERNEL / _WAVEFRONT / _PIPELINE; 0 before the first call).
+ * With CRT_VARIANT_AUTO on a scene that both the megakernel and the pipelined kernel can stage completely (up to 2048
+ * primitives), a call of at least 16 samples on a frame large enough for a few samples to be representative (1.5 M paths in
+ * the timed part) renders its first samples with both, times them and gives the rest to the faster
+ * one (the variants write identical bits, so the frame does not depend on the choice); the choice is kept until the tree, the
+ * frame size or the depth changes. CRT_AUTO_CALIBRATE=0 keeps the static rule (pipeline from 256 primitives up). The reference
+ * has one kernel (Kernel.cu:102): no counterpart. */
+int32_t crt_last_variant(crt_context* ctx);
 
 /* ---- synthetic scenes of BASELINE.json, splitmix64-seeded; host-only, no GPU needed ---- */
 enum { CRT_SCENE_RTIOW = 1, CRT_SCENE_TEXTURED = 2, CRT_SCENE_GRID_1M = 3, CRT_SCENE_STRESS_10K = 4,

@@ -360,6 +360,36 @@ def test_variants_bit_identical_to_megakernel(renderer, name, kind, hint, W, H, 
         f"{(mega != wave).any(axis=-1).sum()} of {W * H} pixels differ between the variants"
 
 
+@pytest.mark.parametrize("kind,hint", [(capi.SCENE_GRID_1M, 10), (capi.SCENE_TEXTURED, 512), (capi.SCENE_REFERENCE_DEFAULT, 0)],
+                         ids=["grid101", "textured67", "default17"])
+def test_auto_measures_both_kernels_and_the_frame_does_not_depend_on_the_choice(renderer, kind, hint):
+    """CRT_VARIANT_AUTO on a scene both kernels can stage completely (crt.h crt_last_variant): the first samples of a call of
+    >= 16 samples are rendered by the megakernel AND the pipelined kernel, timed, and the rest goes to the winner. Whatever it
+    picks, the buffer is the megakernel's bit for bit, every sample is counted once, and the next call keeps the choice."""
+    W, H, spp = 960, 540, 48  # 3 timed samples per kernel = 1.56 M paths: enough to be measured on
+    s = Scene.generate(kind, 1984, hint)
+    cam = s.default_camera(W, H)
+    _setup(renderer, s, cam, W, H)
+    renderer.render(spp=spp, max_depth=20, variant=capi.VARIANT_MEGAKERNEL)
+    want = renderer.read_accum().view(np.uint32).copy()
+    assert renderer.last_variant() == capi.VARIANT_MEGAKERNEL
+    picks = []
+    for _ in range(2):
+        renderer.clear()
+        renderer.reset_counters()
+        renderer.render(spp=spp, max_depth=20, variant=capi.VARIANT_AUTO)
+        got = renderer.read_accum().view(np.uint32)
+        assert (got.view(np.float32)[..., 3] == spp).all()
+        assert renderer.counters().paths == W * H * spp
+        assert np.array_equal(got, want), "the AUTO frame differs from the megakernel's"
+        picks.append(renderer.last_variant())
+    assert picks[0] in (capi.VARIANT_MEGAKERNEL, capi.VARIANT_PIPELINE) and picks[1] == picks[0]
+    # fewer than 16 samples: nothing to measure on, the static rule applies (these scenes have < 256 primitives)
+    renderer.clear()
+    renderer.render(spp=4, max_depth=20, variant=capi.VARIANT_AUTO, spp_begin=0)
+    assert renderer.last_variant() in (picks[0], capi.VARIANT_MEGAKERNEL)
+
+
 @pytest.mark.parametrize("what", ["nan_origin", "nan_direction", "inf_direction"])
 @pytest.mark.parametrize("kind,hint", [(capi.SCENE_RTIOW, 0), (capi.SCENE_GRID_1M, 60)], ids=["staged_tree", "tree_behind_l1"])
 def test_non_finite_rays_terminate_and_the_variants_agree(renderer, kind, hint, what):
