@@ -1511,7 +1511,9 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
             // same bits. So the first samples of the frame are rendered by both, timed, and the rest goes to the winner; the choice
             // is kept while tree, frame size and depth stay what they are. One host synchronisation per such change.
             const bool both = !exact && !count && ctx->scene.n_prims >= 1 && ctx->scene.n_prims <= CRT_PAIR_MAX_PRIMS;
-            if (both && ctx->auto_calibrate) {
+            cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
+            if (both && ctx->auto_calibrate) cudaStreamIsCapturing(ctx->stream, &capturing); // measuring synchronises: not under graph capture
+            if (both && ctx->auto_calibrate && capturing == cudaStreamCaptureStatusNone) {
                 uint64_t key = ctx->nodes_gen * 0x9E3779B97F4A7C15ull;
                 for (uint64_t v : {(uint64_t)A.cover_w, (uint64_t)A.cover_h, (uint64_t)A.max_depth, (uint64_t)p->row_tiles, (uint64_t)A.jitter})
                     key = (key ^ v) * 0x100000001B3ull;
