@@ -18,7 +18,7 @@ SPHERE, XYRECT, XZRECT, YZRECT = 0, 1, 2, 3
 LAMBERTIAN, METAL, DIELECTRIC, DIFFUSELIGHT = 0, 1, 2, 3
 CONSTANT, CHECKER, IMAGE = 0, 1, 2
 STATIC_ACCUM_MAX_PIXELS = 262144  # CRT_STATIC_ACCUM_MAX_PIXELS, include/crt.h
-BUILDER_AUTO, BUILDER_HOST_SAH, BUILDER_GPU_LBVH, BUILDER_GPU_PLOC = 0, 1, 2, 3
+BUILDER_AUTO, BUILDER_HOST_SAH, BUILDER_GPU_LBVH = 0, 1, 2
 VARIANT_AUTO, VARIANT_MEGAKERNEL, VARIANT_WAVEFRONT, VARIANT_PIPELINE = 0, 1, 2, 3
 JITTER_RANDOM, JITTER_CENTER = 0, 1
 FLAG_EXACT_MATH, FLAG_COUNT_TESTS, FLAG_TRUNCATED_GRID = 1, 2, 4

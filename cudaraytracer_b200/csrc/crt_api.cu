@@ -46,7 +46,6 @@ struct crt_context
     int smem_optin = 0, smem_per_sm = 0;
     int smem_budget_override = -1;
     int bvh_builder = CRT_BUILDER_AUTO;      // crt_set_bvh_builder / CRT_BVH_BUILDER
-    int ploc_radius = 16;                   // CRT_PLOC_RADIUS: neighbours searched on each side (lbvh.cuh)
     uint64_t gpu_build_min_prims = 65536;   // AUTO: scenes from this size up are built on the GPU (lbvh.cuh)
     long pipe_prefix_bytes = 24 * 1024; // scene prefix staged by the pipelined kernel when the whole scene does not fit
 
@@ -258,9 +257,7 @@ crt_status crt_context_create(int device, crt_context** out)
     if ((env = getenv("CRT_BVH_BUILDER"))) {
         if (!strcmp(env, "host")) ctx->bvh_builder = CRT_BUILDER_HOST_SAH;
         else if (!strcmp(env, "gpu") || !strcmp(env, "lbvh")) ctx->bvh_builder = CRT_BUILDER_GPU_LBVH;
-        else if (!strcmp(env, "ploc")) ctx->bvh_builder = CRT_BUILDER_GPU_PLOC;
     }
-    if ((env = getenv("CRT_PLOC_RADIUS")) && atoi(env) >= 1) ctx->ploc_radius = std::min(atoi(env), PLOC_MAX_RADIUS);
     if ((env = getenv("CRT_GPU_BUILD_MIN_PRIMS")) && atol(env) >= 2) ctx->gpu_build_min_prims = (uint64_t)atol(env);
     if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&ctx->ev0)) != cudaSuccess || (e = cudaEventCreate(&ctx->ev1)) != cudaSuccess ||
@@ -495,7 +492,7 @@ static crt_status upload_packed(crt_context* ctx, const crt_scene_desc* sd, cons
 // ---- BVH built on the device (lbvh.cuh) ----
 // *outcome: 0 = nothing touched (scene too small for this path), 1 = gave up after the upload (tree too deep; the image
 // textures of `sd` are on the device), 2 = the scene is in use.
-static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, bool keep_images, bool ploc, int* outcome)
+static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, bool keep_images, int* outcome)
 {
     NvtxRange nvtx_range("bvh build: GPU LBVH");
     *outcome = 0;
@@ -523,10 +520,6 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
         cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr,
                                                         (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 64, st);
         if (e != cudaSuccess) return cuda_fail(ctx, e, "cub::DeviceRadixSort::SortPairs (size query)");
-        size_t scan_bytes = 0;
-        e = cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr, (int)n, st);
-        if (e != cudaSuccess) return cuda_fail(ctx, e, "cub::DeviceScan::ExclusiveSum (size query)");
-        tmp_bytes = std::max(tmp_bytes, scan_bytes);
     }
     size_t arena_bytes = 0;
     auto reserve = [&](size_t bytes) { const size_t at = arena_bytes; arena_bytes += (bytes + 255) & ~(size_t)255; return at; };
@@ -535,9 +528,7 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
                  o_act = reserve((size_t)n * 4), o_k0 = reserve((size_t)n * 8), o_k1 = reserve((size_t)n * 8), o_v0 = reserve((size_t)n * 4),
                  o_v1 = reserve((size_t)n * 4), o_code = reserve((size_t)n * 4), o_perm = reserve(nn * 4), o_nodes2 = reserve(nn * 64),
                  o_parent2 = reserve(nn * 4), o_stats = reserve(sizeof(LbvhStats)), o_tmp = reserve(std::max<size_t>(tmp_bytes, 16)),
-                 o_c0 = reserve(ploc ? (size_t)n * sizeof(PlocCluster) : 0), o_c1 = reserve(ploc ? (size_t)n * sizeof(PlocCluster) : 0),
-                 o_nn = reserve(ploc ? (size_t)n * 4 : 0), o_flags = reserve(ploc ? (size_t)n * 8 : 0), o_scan = reserve(ploc ? (size_t)n * 8 : 0),
-                 o_counts = reserve(16);
+                 o_end = reserve(16);
     auto cleanup = [&]() {
         for (unsigned char* p : raw_rgb) cudaFree(p);
     };
@@ -612,33 +603,7 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
     k_lbvh_keys<<<gb, 256, 0, st>>>(R, c0, ie, big_area, d_k0, d_v0);
     CUB_(cub::DeviceRadixSort::SortPairs(d_tmp, tmp_bytes, d_k0, d_k1, d_v0, d_v1, (int)n, 0, 64, st));
     k_lbvh_pack<<<gb, 256, 0, st>>>(R, d_v1, ctx->d_prims, ctx->d_prim_k, ctx->d_mats, ctx->d_prim_id, d_code);
-    bool ploc_done = false;
-    int ploc_steps = 0;
-    if (ploc) { // agglomerative clustering over the sorted leaves; one 8-byte read-back per step tells the host how far it got
-        PlocCluster *c_in = reinterpret_cast<PlocCluster*>(arena + o_c0), *c_out = reinterpret_cast<PlocCluster*>(arena + o_c1);
-        int* d_nn = reinterpret_cast<int*>(arena + o_nn);
-        unsigned long long *d_flags = reinterpret_cast<unsigned long long*>(arena + o_flags), *d_scan = reinterpret_cast<unsigned long long*>(arena + o_scan);
-        unsigned int* d_counts = reinterpret_cast<unsigned int*>(arena + o_counts);
-        k_ploc_init<<<gb, 256, 0, st>>>(R, d_v1, d_code, c_in);
-        int m = (int)n, id_next = (int)n - 1;
-        ploc_done = true;
-        while (m > 1) {
-            const unsigned g = (unsigned)((m + PLOC_BLOCK - 1) / PLOC_BLOCK);
-            k_ploc_nn<<<g, PLOC_BLOCK, 0, st>>>(c_in, m, ctx->ploc_radius, d_nn);
-            k_ploc_flags<<<g, PLOC_BLOCK, 0, st>>>(d_nn, m, d_flags);
-            size_t tb = tmp_bytes;
-            CUB_(cub::DeviceScan::ExclusiveSum(d_tmp, tb, d_flags, d_scan, m, st));
-            k_ploc_emit<<<g, PLOC_BLOCK, 0, st>>>(c_in, d_nn, d_flags, d_scan, m, id_next, c_out, d_nodes2, d_parent2, ctx->d_leaf_ref, d_counts);
-            unsigned int hc[2] = {0, 0};
-            CUB_(cudaMemcpyAsync(hc, d_counts, 8, cudaMemcpyDeviceToHost, st));
-            CUB_(cudaStreamSynchronize(st));
-            if (hc[1] == 0 || (int)hc[0] != m - (int)hc[1] || ++ploc_steps > 1024) { ploc_done = false; break; } // no progress: not expected
-            id_next -= (int)hc[1];
-            m = (int)hc[0];
-            std::swap(c_in, c_out);
-        }
-    }
-    if (!ploc_done) k_lbvh_hierarchy<<<gn, 256, 0, st>>>(d_k1, d_code, (int)n, d_nodes2, d_parent2, ctx->d_leaf_ref);
+    k_lbvh_hierarchy<<<gn, 256, 0, st>>>(d_k1, d_code, (int)n, d_nodes2, d_parent2, ctx->d_leaf_ref);
     CUB_(cudaMemsetAsync(ctx->d_visits, 0, nn * 4, st));
     k_bvh_refit<<<gb, 256, 0, st>>>(d_nodes2, ctx->d_prims, ctx->d_prim_k, d_parent2, ctx->d_leaf_ref, ctx->d_visits, (int)n, abs_pad);
     CUB_(cudaMemsetAsync(d_stats, 0, sizeof(LbvhStats), st));
@@ -690,14 +655,14 @@ static crt_status upload_gpu_built(crt_context* ctx, const crt_scene_desc* sd, b
     ctx->stats.node_bytes = (uint64_t)nn * 64;
     ctx->stats.prim_bytes = (uint64_t)n * (16 + 4 + 32 + 4);
     ctx->stats.h2d_bytes = h2d;
-    ctx->stats.builder = ploc_done ? CRT_BUILDER_GPU_PLOC : CRT_BUILDER_GPU_LBVH;
+    ctx->stats.builder = CRT_BUILDER_GPU_LBVH;
     ctx->scene_h2d_bytes = h2d;
     ctx->have_scene = true;
     *outcome = 2;
     if (getenv("CRT_BVH_TIMING")) {
         auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
-        fprintf(stderr, "[crt] gpu bvh (%s, %d clustering steps): host prepare %.1f ms, free + alloc + enqueue copies %.1f ms, kernels + copies + sync %.1f ms, free + bookkeeping %.1f ms\n",
-                ploc_done ? "PLOC" : "LBVH", ploc_steps, ms(t0, t_prep), ms(t_prep, t_alloc), ms(t_alloc, t_gpu), ms(t_gpu, std::chrono::steady_clock::now()));
+        fprintf(stderr, "[crt] gpu bvh (LBVH): host prepare %.1f ms, free + alloc + enqueue copies %.1f ms, kernels + copies + sync %.1f ms, free + bookkeeping %.1f ms\n",
+                ms(t0, t_prep), ms(t_prep, t_alloc), ms(t_alloc, t_gpu), ms(t_gpu, std::chrono::steady_clock::now()));
     }
     return CRT_OK;
 }
@@ -719,11 +684,11 @@ static crt_status build_and_upload(crt_context* ctx, const crt_scene_desc* sd, b
 static crt_status build_and_upload_tree(crt_context* ctx, const crt_scene_desc* sd, bool keep_images, const char* who)
 {
     uint64_t n_active_bound = sd ? sd->n_hittables : 0;
-    const bool gpu = ctx->bvh_builder == CRT_BUILDER_GPU_LBVH || ctx->bvh_builder == CRT_BUILDER_GPU_PLOC ||
+    const bool gpu = ctx->bvh_builder == CRT_BUILDER_GPU_LBVH ||
                      (ctx->bvh_builder == CRT_BUILDER_AUTO && n_active_bound >= ctx->gpu_build_min_prims);
     if (gpu && sd && sd->hittables) {
         int outcome = 0;
-        crt_status st = upload_gpu_built(ctx, sd, keep_images, ctx->bvh_builder == CRT_BUILDER_GPU_PLOC, &outcome);
+        crt_status st = upload_gpu_built(ctx, sd, keep_images, &outcome);
         if (st != CRT_OK || outcome == 2) return st;
         if (outcome == 1) keep_images = true; // the textures are already on the device
     }
@@ -742,7 +707,7 @@ extern "C" {
 crt_status crt_set_bvh_builder(crt_context* ctx, int32_t builder)
 {
     if (!ctx) return crt_set_error(nullptr, CRT_ERR_INVALID, "crt_set_bvh_builder: ctx is NULL");
-    if (builder < CRT_BUILDER_AUTO || builder > CRT_BUILDER_GPU_PLOC) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_set_bvh_builder: unknown builder");
+    if (builder < CRT_BUILDER_AUTO || builder > CRT_BUILDER_GPU_LBVH) return crt_set_error(ctx, CRT_ERR_INVALID, "crt_set_bvh_builder: unknown builder");
     ctx->bvh_builder = builder;
     return CRT_OK;
 }

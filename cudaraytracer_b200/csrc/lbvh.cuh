@@ -305,99 +305,3 @@ __global__ void k_lbvh_permute_leaf_refs(int* __restrict__ leaf_ref, const int* 
     const int r = leaf_ref[s];
     leaf_ref[s] = 2 * perm[r >> 1] + (r & 1);
 }
-
-// ---- PLOC: parallel locally-ordered clustering (Meister & Bittner 2018) -------------------------------------------------------
-// Bottom-up agglomerative build over the Morton-sorted leaves: every cluster looks at its 2r neighbours in the current order and
-// picks the one whose union with it has the smallest surface area; mutual choices are merged into a new inner node, which
-// takes the place of the lower-positioned partner; the list is compacted and the step repeats until one cluster is left.
-// The order stays a space-filling-curve order, so near neighbours in the list are near in space. Measured on B200 (4K, pipelined
-// kernel): 1 M-sphere grid 4.6 Grays/s (LBVH 5.6, host SAH 5.9), 10 k glass/metal 6.3 (8.4 / 8.3), RTIOW 12.3 (12.4 / 13.8) — on
-// grid-like scenes the LBVH's median splits are hard to beat and its node numbering (subtrees contiguous) is kinder to the
-// caches than ids handed out per clustering step, so AUTO uses the LBVH; PLOC stays selectable for clustered input.
-// Node ids are handed out downwards from n - 2, deterministically (rank among the merges of a step by prefix sum), so the
-// last merge, the root, is node 0 as the kernels expect. Boxes are written afterwards by k_bvh_refit like for every other tree.
-struct PlocCluster
-{
-    float4 lo; // box minimum; w = reference bits (inner node index >= 0, or leaf code < 0)
-    float4 hi; // box maximum
-};
-
-__global__ void k_ploc_init(LbvhRaw R, const uint32_t* __restrict__ sorted, const int* __restrict__ leaf_code, PlocCluster* __restrict__ c)
-{
-    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= R.n) return;
-    const crt_hittable h = R.hittables[R.active[sorted[s]]];
-    float lo[3], hi[3];
-    lbvh_prim_box(h, lo, hi);
-    c[s].lo = make_float4(lo[0], lo[1], lo[2], __int_as_float(leaf_code[s]));
-    c[s].hi = make_float4(hi[0], hi[1], hi[2], 0.f);
-}
-
-#define PLOC_BLOCK 256
-#define PLOC_MAX_RADIUS 32
-
-__global__ void __launch_bounds__(PLOC_BLOCK) k_ploc_nn(const PlocCluster* __restrict__ c, int m, int r, int* __restrict__ nn)
-{
-    __shared__ float4 s_lo[PLOC_BLOCK + 2 * PLOC_MAX_RADIUS], s_hi[PLOC_BLOCK + 2 * PLOC_MAX_RADIUS];
-    const int base = blockIdx.x * PLOC_BLOCK - r;
-    for (int t = threadIdx.x; t < PLOC_BLOCK + 2 * r; t += PLOC_BLOCK) {
-        const int g = base + t;
-        if (g >= 0 && g < m) { s_lo[t] = c[g].lo; s_hi[t] = c[g].hi; }
-    }
-    __syncthreads();
-    const int i = blockIdx.x * PLOC_BLOCK + threadIdx.x;
-    if (i >= m) return;
-    const float4 a0 = s_lo[threadIdx.x + r], a1 = s_hi[threadIdx.x + r];
-    float best = 3.402823466e+38f;
-    int best_j = -1;
-    const int j0 = max(0, i - r), j1 = min(m - 1, i + r);
-    for (int j = j0; j <= j1; j++) {
-        if (j == i) continue;
-        const float4 b0 = s_lo[j - base], b1 = s_hi[j - base];
-        const float dx = fmaxf(a1.x, b1.x) - fminf(a0.x, b0.x), dy = fmaxf(a1.y, b1.y) - fminf(a0.y, b0.y), dz = fmaxf(a1.z, b1.z) - fminf(a0.z, b0.z);
-        const float area = __fmaf_rn(dx, dy, __fmaf_rn(dy, dz, __fmul_rn(dz, dx)));
-        if (area < best || best_j < 0) { best = area; best_j = j; } // the first of equal candidates wins: deterministic
-    }
-    nn[i] = best_j;
-}
-
-// flags for the compaction: low word = the cluster keeps a place in the next list, high word = it leads a merge
-__global__ void k_ploc_flags(const int* __restrict__ nn, int m, unsigned long long* __restrict__ flags)
-{
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
-    const int j = nn[i];
-    const bool mutual = j >= 0 && nn[j] == i;
-    const bool leader = mutual && i < j;
-    const bool stays = !mutual || leader;
-    flags[i] = (stays ? 1ull : 0ull) | (leader ? 1ull << 32 : 0ull);
-}
-
-// scan = exclusive prefix sum of flags. counts[0] = size of the next list, counts[1] = merges of this step.
-__global__ void k_ploc_emit(const PlocCluster* __restrict__ in, const int* __restrict__ nn, const unsigned long long* __restrict__ flags,
-                            const unsigned long long* __restrict__ scan, int m, int id_next, PlocCluster* __restrict__ out, float4* nodes,
-                            int* __restrict__ parent, int* __restrict__ leaf_ref, unsigned int* __restrict__ counts)
-{
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
-    const unsigned long long f = flags[i], sc = scan[i];
-    if (i == m - 1) {
-        counts[0] = (unsigned int)(sc & 0xffffffffu) + (unsigned int)(f & 1u);
-        counts[1] = (unsigned int)(sc >> 32) + (unsigned int)(f >> 32);
-    }
-    if ((f & 1u) == 0u) return; // merged into its partner
-    const int pos = (int)(sc & 0xffffffffu);
-    PlocCluster a = in[i];
-    if (f >> 32) {
-        const int id = id_next - 1 - (int)(sc >> 32);
-        const PlocCluster b = in[nn[i]];
-        const int ra = __float_as_int(a.lo.w), rb = __float_as_int(b.lo.w);
-        nodes[4 * (size_t)id + 3] = make_float4(a.lo.w, b.lo.w, 0.f, 0.f);
-        if (ra >= 0) parent[ra] = 2 * id; else leaf_ref[(~ra) & CRT_LEAF_INDEX_MASK] = 2 * id;
-        if (rb >= 0) parent[rb] = 2 * id + 1; else leaf_ref[(~rb) & CRT_LEAF_INDEX_MASK] = 2 * id + 1;
-        if (id == 0) parent[0] = -1;
-        a.lo = make_float4(fminf(a.lo.x, b.lo.x), fminf(a.lo.y, b.lo.y), fminf(a.lo.z, b.lo.z), __int_as_float(id));
-        a.hi = make_float4(fmaxf(a.hi.x, b.hi.x), fmaxf(a.hi.y, b.hi.y), fmaxf(a.hi.z, b.hi.z), 0.f);
-    }
-    out[pos] = a;
-}

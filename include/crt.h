@@ -136,7 +136,7 @@ typedef struct crt_bvh_stats {
     double build_ms;
     uint64_t node_bytes, prim_bytes;
     uint64_t h2d_bytes; /* bytes copied host -> device by the last scene upload (nodes, primitives, materials, texels) */
-    uint64_t builder;   /* CRT_BUILDER_HOST_SAH, _GPU_LBVH or _GPU_PLOC: which builder made the tree in use */
+    uint64_t builder;   /* CRT_BUILDER_HOST_SAH or _GPU_LBVH: which builder made the tree in use */
     uint64_t cache_hits; /* crt_scene_upload calls since the last real upload that found their scene already on the device
                             (then h2d_bytes is 0 and build_ms is the time of the content hash) */
 } crt_bvh_stats;
@@ -145,12 +145,10 @@ typedef struct crt_bvh_stats {
  * (Hittable.cuh:303-385), which runs on the host at start-up and after every GUI edit (CudaLayer.cpp:247-256,493-494).
  *   HOST_SAH  threaded binned-SAH builder (csrc/scene_pack.cpp): the best trees, 190 ms for 1 M spheres on 16 cores.
  *   GPU_LBVH  Morton-code linear BVH built entirely on the device (csrc/lbvh.cuh): a few ms for 1 M spheres.
- *   GPU_PLOC  locally-ordered agglomerative clustering over the Morton order (Meister & Bittner 2018), also on the device.
- *             On the sphere-grid scenes of BASELINE.json its trees traverse 2-25 % slower than the LBVH ones (whose median
- *             splits suit a grid), so AUTO does not pick it; it is there for clustered scenes.
  *   AUTO      GPU_LBVH from 65536 hittables up (CRT_GPU_BUILD_MIN_PRIMS), HOST_SAH below.
- * The environment variable CRT_BVH_BUILDER=host|lbvh|ploc overrides the default of new contexts. */
-enum { CRT_BUILDER_AUTO = 0, CRT_BUILDER_HOST_SAH = 1, CRT_BUILDER_GPU_LBVH = 2, CRT_BUILDER_GPU_PLOC = 3 };
+ * The environment variable CRT_BVH_BUILDER=host|lbvh overrides the default of new contexts. */
+enum { CRT_BUILDER_AUTO = 0, CRT_BUILDER_HOST_SAH = 1, CRT_BUILDER_GPU_LBVH = 2 };
+/* (a third device builder, PLOC clustering, was measured in rounds 1-2 and removed: DESIGN.md 3.3) */
 
 typedef struct crt_context crt_context;
 

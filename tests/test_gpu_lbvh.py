@@ -1,4 +1,4 @@
-"""GPU tests of the device-side BVH builders (csrc/lbvh.cuh: Morton LBVH and PLOC clustering): the tree is different from the
+"""GPU tests of the device-side BVH builders (csrc/lbvh.cuh: Morton LBVH): the tree is different from the
 host SAH tree, the closest hit is not. Primary-hit IDs bit-exact against the oracle, accumulation buffers bit-identical to the host-built tree's, edits
 (refit and topology change) on a GPU-built tree, fall-back for degenerate scenes. All through the C ABI."""
 import numpy as np
@@ -19,10 +19,10 @@ def _setup(r, scene, cam, W, H):
     r.resize(W, H)
 
 
-GPU_BUILDERS = [capi.BUILDER_GPU_LBVH, capi.BUILDER_GPU_PLOC]
+GPU_BUILDERS = [capi.BUILDER_GPU_LBVH]
 
 
-@pytest.mark.parametrize("builder", GPU_BUILDERS, ids=["lbvh", "ploc"])
+@pytest.mark.parametrize("builder", GPU_BUILDERS, ids=["lbvh"])
 @pytest.mark.parametrize("name,kind,hint,W,H", SCENES)
 def test_gpu_built_tree_same_hits_as_host_tree(name, kind, hint, W, H, builder):
     s = Scene.generate(kind, 1984, hint)
@@ -73,7 +73,7 @@ def test_gpu_built_large_grid_ids_vs_brute_force():
         r.close()
 
 
-@pytest.mark.parametrize("builder", GPU_BUILDERS, ids=["lbvh", "ploc"])
+@pytest.mark.parametrize("builder", GPU_BUILDERS, ids=["lbvh"])
 def test_edits_on_a_gpu_built_tree(builder):
     """Refit (moved / resized spheres, material switch) and a topology change (deactivate, type change) with the GPU builder."""
     s = Scene.generate(capi.SCENE_RTIOW, 1984)
@@ -118,7 +118,7 @@ def test_edits_on_a_gpu_built_tree(builder):
         r.close(); fresh.close()
 
 
-@pytest.mark.parametrize("builder", GPU_BUILDERS, ids=["lbvh", "ploc"])
+@pytest.mark.parametrize("builder", GPU_BUILDERS, ids=["lbvh"])
 def test_degenerate_scenes_fall_back_to_the_host_builder(builder):
     cam = look_camera((0, 0, 5), (0, 0, -1))
     tex = [dict(type=capi.CONSTANT, color=(0.5, 0.5, 0.5))]
