@@ -384,6 +384,19 @@ def test_auto_measures_both_kernels_and_the_frame_does_not_depend_on_the_choice(
         assert np.array_equal(got, want), "the AUTO frame differs from the megakernel's"
         picks.append(renderer.last_variant())
     assert picks[0] in (capi.VARIANT_MEGAKERNEL, capi.VARIANT_PIPELINE) and picks[1] == picks[0]
+    # a sample shard (every third sample from 1: what rank 1 of 3 renders) through AUTO: the measured part must walk the same
+    # strided sample set as the rest of the call
+    renderer.clear()
+    renderer.render(spp=spp, max_depth=20, variant=capi.VARIANT_MEGAKERNEL, spp_begin=1, spp_stride=3)
+    shard = renderer.read_accum().view(np.uint32).copy()
+    renderer.upload(s)  # same description: the tree is kept, so is the choice ...
+    renderer.set_scene_cache(False)
+    renderer.upload(s)  # ... a real re-upload makes AUTO measure again
+    renderer.set_scene_cache(True)
+    renderer.set_camera(cam)
+    renderer.clear()
+    renderer.render(spp=spp, max_depth=20, variant=capi.VARIANT_AUTO, spp_begin=1, spp_stride=3)
+    assert np.array_equal(renderer.read_accum().view(np.uint32), shard), "a strided shard through AUTO differs from the megakernel's"
     # fewer than 16 samples: nothing to measure on, the static rule applies (these scenes have < 256 primitives)
     renderer.clear()
     renderer.render(spp=4, max_depth=20, variant=capi.VARIANT_AUTO, spp_begin=0)
