@@ -192,9 +192,10 @@ template <bool SMEM_ALL> __device__ __forceinline__ uint32_t pipe_mat_bits(const
     return __float_as_uint(__ldg(S.g_mats + 2 * (size_t)i + 1).w);
 }
 
-// One batch of queue q (n <= 32 slots, lane < n holds `slot`): generate, or shade one bounce.
+// One batch of queue q (n <= 32 slots, lane < n holds `slot`): generate, or shade one bounce. Returns whether the lane's slot now
+// holds a ray that waits for its closest-hit query (the caller extends it in place or pushes it into EXT).
 template <bool SMEM_ALL>
-__device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S, const PipePool& P, PipeCtl* ctl, int q, int n, int slot,
+__device__ __forceinline__ bool pipe_batch(const PipeArgs& A, const SceneView& S, const PipePool& P, PipeCtl* ctl, int q, int n, int slot,
                                            unsigned lane, unsigned lt, unsigned int& shard_cursor, bool& exhausted)
 {
     const bool mine = (int)lane < n;
@@ -220,8 +221,7 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
             done += g;
         }
         if (lane == 0 && done < n) atomicSub(&ctl->live, n - done); // no work left: these slots retire
-            pipe_push(P, ctl, PQ_EXT, started, slot, lt);
-        return;
+        return started;
     }
     bool alive = false, ended = false;
     if (mine) {
@@ -247,8 +247,8 @@ __device__ __forceinline__ void pipe_batch(const PipeArgs& A, const SceneView& S
         }
     }
     // (publishing before the atomics, so that the release fence does not wait for them, measured 0.7 % slower)
-    pipe_push(P, ctl, PQ_EXT, alive, slot, lt);
     pipe_push(P, ctl, PQ_GEN, ended, slot, lt);
+    return alive;
 }
 
 // The child-interleaved copy of the packed node table that the global path of k_render_pipe reads (trace.cuh crt_pair_node).
@@ -332,12 +332,23 @@ __global__ void __launch_bounds__(PIPE_THREADS, 1) k_render_pipe(const __grid_co
                 int s2 = -1;
                 const int n = pipe_pop(P, &ctl, q, 32, (int)lane, true, s2);
                 if (n > 0) {
-                    pipe_batch<SMEM_ALL>(A, S, P, &ctl, q, n, s2, lane, lt, shard_cursor, exhausted);
+                    const bool cont = pipe_batch<SMEM_ALL>(A, S, P, &ctl, q, n, s2, lane, lt, shard_cursor, exhausted);
                     worked = true;
+                    // A lane that is idle keeps the ray it has just shaded or generated and extends it itself: no trip through
+                    // EXT (a push, a pop and the hand-over of the ring entry per ray); the other new rays go into the queue.
+                    const bool adopt = cont && cur == CRT_TRAV_DONE;
+                    pipe_push(P, &ctl, PQ_EXT, cont && !adopt, s2, lt);
+                    if (adopt) slot = s2;
                     // Lanes in mid-traversal kept only {slot, cur, sp, t, leaf} across the batch: rebuild the per-ray constants.
                     const int si = max(slot, 0);
                     const float4 a0 = P.a[si], b0 = P.b[si];
                     r = trav_setup<false>(f3(a0.x, a0.y, a0.z), f3(a0.w, b0.x, b0.y));
+                    if (adopt) {
+                        h.t = 3.402823466e+38f;
+                        h.leaf = -1;
+                        cur = trav_begin<false, SMEM_ALL, PAIR, SPH>(S, r, t_min, h);
+                        top = top0;
+                    }
                 }
             }
         }
