@@ -1288,7 +1288,7 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
     // shared memory: [scene prefix][pool of N slots: 56 B of path state + 7 16-bit ring entries]
     const long per_slot = 3 * 16 + 8 + 2 * PQ_COUNT;
     const long budget = (ctx->smem_budget_override >= 0 ? std::min<long>(ctx->smem_budget_override, ctx->smem_optin) : (long)ctx->smem_optin) - 1024;
-    const long node_b = 16 * CRT_SMEM_NODE_F4;
+    const long node_b = 16 * CRT_PAIR_NODE_F4; // a staged prefix slot of the global path (trace.cuh crt_pair_node)
     // whole scene staged: the PAIR layout of trace.cuh, 48-byte nodes + a dummy node, 16-bit references
     const long full = ((long)A.scene.n_nodes + 1) * 16 * CRT_PAIR_NODE_F4 + (long)A.scene.n_prims * 48;
     const bool pair_ok = A.scene.n_prims <= CRT_PAIR_MAX_PRIMS && CRT_PAIR_NODE_F4 * ((long)A.scene.n_nodes + 1) < CRT_PAIR_LEAF;

@@ -173,23 +173,26 @@ __device__ __forceinline__ float2 crt_h2_to_f2(unsigned w)
 #endif
 }
 
-// ---- The child-interleaved 64-byte node of the pipelined kernel's GLOBAL path (scenes that do not fit in shared memory) ----
-// Same content as the packed node of crt_internal.h, reordered so that each 64-bit half of a 128-bit word holds the same
-// quantity of BOTH children ({c0.x, c1.x, c0.y, c1.y} {c0.z, c1.z, h0.x, h1.x} {h0.y, h1.y, h0.z, h1.z} {child0, child1, -, -}):
-// node_visit_pairg then runs the FFMA2 arithmetic of the PAIR path on two LDG.256. The table is made on the device
-// (k_pair_nodes) whenever the packed nodes have changed; the first smem_nodes of it are staged, behind a dummy node.
-__host__ __device__ __forceinline__ void crt_pair_node(const float4& g0, const float4& g1, const float4& g2, const float4& g3, float4& q0,
-                                                       float4& q1, float4& q2, float4& q3)
+// ---- The child-interleaved node of the pipelined kernel's GLOBAL path (scenes that do not fit in shared memory) ----
+// The PAIR node with 32-bit child references (those of crt_internal.h), 44 bytes:
+//   {c0.x, c1.x, c0.y, c1.y} {c0.z, c1.z, half2(h0.x, h1.x), half2(h0.y, h1.y)} {half2(h0.z, h1.z), child0, child1, -}
+// In HBM one record per 64 bytes, fetched by ONE LDG.256 + ONE LDG.128 = 12 wavefronts of the LSU data pipe per warp visit
+// instead of the 16 of two LDG.256 on a binary32 node; staged prefix: 48-byte slots, three LDS.128. That pipe is the bound on
+// these scenes (profiles/r02_y3_pipe_c4scene.txt: l1tex__data_pipe_lsu_wavefronts 90 %, half of it global node loads, issue 56 %).
+// The table is made on the device (k_pair_nodes) whenever the packed nodes have changed; node_visit_pairg reads it.
+__device__ __forceinline__ void crt_pair_node(const float4& g0, const float4& g1, const float4& g2, const float4& g3, float4& q0, float4& q1,
+                                              float4& q2, float4& q3)
 {
+    // packed: {c0.c.xyz, c0.h.x} {c0.h.yz, c1.c.xy} {c1.c.z, c1.h.xyz} {child0, child1}
     q0 = make_float4(g0.x, g1.z, g0.y, g1.w);
-    q1 = make_float4(g0.z, g2.x, g0.w, g2.y);
-    q2 = make_float4(g1.x, g2.z, g1.y, g2.w);
-    q3 = g3;
+    q1 = make_float4(g0.z, g2.x, __uint_as_float(crt_f2h_ru(g0.w) | (crt_f2h_ru(g2.y) << 16)), __uint_as_float(crt_f2h_ru(g1.x) | (crt_f2h_ru(g2.z) << 16)));
+    q2 = make_float4(__uint_as_float(crt_f2h_ru(g1.y) | (crt_f2h_ru(g2.w) << 16)), g3.x, g3.y, 0.f);
+    q3 = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
 // Stages the first smem_* entries of each table into dynamic shared memory. Call from every thread, then __syncthreads().
 // PAIR (needs PAD and the whole tree in shared memory): the 48-byte nodes above, plus a dummy node behind the last one.
-// PAIRG (needs PAD): 80-byte slots holding child-interleaved nodes; slot 0 is the dummy node, node i sits in slot i + 1.
+// PAIRG (needs PAD): 48-byte slots holding the global path's node records; slot 0 is the dummy node, node i sits in slot i + 1.
 template <bool PAD, bool PAIR = false, bool PAIRG = false> __device__ __forceinline__ SceneView stage_scene(const DevScene& D, float4* smem)
 {
     SceneView S;
@@ -198,7 +201,7 @@ template <bool PAD, bool PAIR = false, bool PAIRG = false> __device__ __forceinl
     S.entry = D.entry; S.n_top = D.n_top;
     for (int k = 0; k < CRT_MAX_TOP; k++) { S.top_code[k] = D.top_code[k]; S.top_pair[k] = PAIR ? pair_ref(~D.top_code[k]) : 0; }
     float4* sn = smem;
-    float4* sp = sn + (PAIR ? CRT_PAIR_NODE_F4 * (size_t)(D.smem_nodes + 1) : PAIRG ? CRT_SMEM_NODE_F4 * (size_t)(D.smem_nodes + 1)
+    float4* sp = sn + (PAIR ? CRT_PAIR_NODE_F4 * (size_t)(D.smem_nodes + 1) : PAIRG ? CRT_PAIR_NODE_F4 * (size_t)(D.smem_nodes + 1)
                                                                                     : (PAD ? CRT_SMEM_NODE_F4 : 4) * (size_t)D.smem_nodes);
     float4* sm = sp + D.smem_prims;
     const int tid = threadIdx.x, nt = blockDim.x;
@@ -231,19 +234,18 @@ template <bool PAD, bool PAIR = false, bool PAIRG = false> __device__ __forceinl
     else if (PAIRG) {
         for (int i = tid; i <= D.smem_nodes; i += nt) {
             float4 q0, q1, q2, q3;
-            if (i == 0) { // the dummy node (see above), binary32 here
-                const float inf = __uint_as_float(0x7f800000u);
+            if (i == 0) { // the dummy node (see above) with 32-bit references
+                const float pm = __uint_as_float(0x7c00u | (0xfc00u << 16));
                 q0 = make_float4(0.f, 0.f, 0.f, 0.f);
-                q1 = make_float4(0.f, 0.f, inf, -inf);
-                q2 = make_float4(inf, -inf, inf, -inf);
-                q3 = make_float4(0.f, 0.f, 0.f, 0.f);
+                q1 = make_float4(0.f, 0.f, pm, pm);
+                q2 = make_float4(pm, 0.f, 0.f, 0.f);
             }
             else {
                 const float4* g = D.nodes + 4 * (size_t)(i - 1);
                 crt_pair_node(__ldg(g), __ldg(g + 1), __ldg(g + 2), __ldg(g + 3), q0, q1, q2, q3);
             }
-            float4* d = sn + CRT_SMEM_NODE_F4 * (size_t)i;
-            d[0] = q0; d[1] = q1; d[2] = q2; d[3] = q3;
+            float4* d = sn + CRT_PAIR_NODE_F4 * (size_t)i;
+            d[0] = q0; d[1] = q1; d[2] = q2;
         }
     }
     else
@@ -283,6 +285,12 @@ __device__ __forceinline__ bool sphere_test(float4 sph, float3 o, float3 d, floa
         return false;
     }
     else {
+        // Fast path: the reference's formula (Hittable.cuh:83-88) with fused operations. For a sphere that is small against its
+        // distance its discriminant is noisy (both terms ~ a |oc|^2): rays that pass up to |oc| * 3e-4 outside become grazing
+        // "hits", and the image of such scenes is STATISTICALLY what the reference renders only with this formula (a robust
+        // discriminant moved the mean of the 10 k-sphere scene by 3 % against the oracle: measured, not adopted). Such a phantom hit
+        // can lie outside the leaf box, so whether it is found depends on the boxes on the way: every fast path therefore tests
+        // the SAME boxes (half-extents rounded up to binary16, see slab2).
         float3 oc = o - f3(sph.x, sph.y, sph.z);
         float b = dot3(oc, d);
         float c = fmaf(-sph.w, sph.w, dot3(oc, oc));
@@ -378,9 +386,26 @@ template <bool EXACT> __device__ __forceinline__ TravRay trav_setup(float3 o, fl
 // Slab intervals of the two child boxes of a node (centre / half-extent form): per axis t_mid = c * id - ood and the
 // half-width h * |id|, so near = t_mid - hw, far = t_mid + hw for either sign of the direction: 9 FFMA + 2 three-input
 // min/max per box, instead of 6 FFMA + 10 min/max with lo/hi planes (the ALU pipe that runs min/max was the busiest one).
+// H16: the half-extents are first rounded UP to binary16, which makes the boxes of this visit exactly those of the PAIR nodes
+// (node_visit_pair / node_visit_pairg store them that way). Every fast path sets it, so that all variants cull with the same
+// boxes: the reference's sphere formula admits grazing hits outside the leaf box (sphere_test), and a frame can only be
+// independent of the variant if such a hit is found by all of them or by none. The EXACT paths keep the binary32 boxes.
+__device__ __forceinline__ float crt_h16_up(float x)
+{
+#ifdef CRT_HOST_SIM
+    return crt_h2_to_f2(crt_f2h_ru(x)).x;
+#else
+    return __half2float(__float2half_ru(x));
+#endif
+}
+template <bool H16>
 __device__ __forceinline__ void slab2(const TravRay& r, float4 w0, float4 w1, float4 w2, float t_min, float t_hit, float& tn0, float& tf0,
                                       float& tn1, float& tf1)
 {
+    if (H16) {
+        w0.w = crt_h16_up(w0.w), w1.x = crt_h16_up(w1.x), w1.y = crt_h16_up(w1.y);
+        w2.y = crt_h16_up(w2.y), w2.z = crt_h16_up(w2.z), w2.w = crt_h16_up(w2.w);
+    }
     const float mx0 = fmaf(w0.x, r.id.x, -r.ood.x), my0 = fmaf(w0.y, r.id.y, -r.ood.y), mz0 = fmaf(w0.z, r.id.z, -r.ood.z);
     const float mx1 = fmaf(w1.z, r.id.x, -r.ood.x), my1 = fmaf(w1.w, r.id.y, -r.ood.y), mz1 = fmaf(w2.x, r.id.z, -r.ood.z);
     tn0 = fmaxf(fmaxf(fmaf(-w0.w, r.aid.x, mx0), fmaf(-w1.x, r.aid.y, my0)), fmaxf(fmaf(-w1.y, r.aid.z, mz0), t_min));
@@ -488,40 +513,36 @@ __device__ __forceinline__ void node_visit_pair(const SceneView& S, const TravRa
 
 // The same visit for scenes that do NOT fit in shared memory (stage_scene<true, false, true>): `cur` >= 0 is a node index, the
 // child references are those of crt_internal.h. Nodes below smem_nodes come from the staged prefix (slot i + 1; slot 0 is the
-// dummy node, which lanes that are not at an inner node visit as index -1), the others from the child-interleaved global
-// table with two LDG.256. Everything after the loads is the arithmetic of node_visit_pair in binary32.
+// dummy node, which lanes that are not at an inner node visit as index -1), the others from the global table of crt_pair_node
+// with one LDG.256 and one LDG.128. Everything after the loads is the arithmetic of node_visit_pair.
 __device__ __forceinline__ void node_visit_pairg(const SceneView& S, const TravRay& r, float t_min, float t_hit, int& cur, StackPtr& top)
 {
     const bool at = cur >= 0;
     const int i = at ? cur : -1;
     float4 q0, q1, q2;
-    int2 ch;
     if (i < S.smem_nodes) {
-        const float4* p = S.s_nodes + CRT_SMEM_NODE_F4 * (i + 1);
+        const float4* p = S.s_nodes + CRT_PAIR_NODE_F4 * (i + 1);
         q0 = p[0]; q1 = p[1]; q2 = p[2];
-        ch = *reinterpret_cast<const int2*>(p + 3);
     }
     else {
         const float4* p = S.g_nodes_pair + 4 * (size_t)i;
-        float4 q3;
         ldg256(p, q0, q1);
-        ldg256(p + 2, q2, q3);
-        ch = make_int2(__float_as_int(q3.x), __float_as_int(q3.y));
+        q2 = __ldg(p + 2);
     }
+    const float2 hx = crt_h2_to_f2(__float_as_uint(q1.z)), hy = crt_h2_to_f2(__float_as_uint(q1.w)), hz = crt_h2_to_f2(__float_as_uint(q2.x));
     const float2 mx = fma2ss(make_float2(q0.x, q0.y), r.id.x, -r.ood.x);
     const float2 my = fma2ss(make_float2(q0.z, q0.w), r.id.y, -r.ood.y);
     const float2 mz = fma2ss(make_float2(q1.x, q1.y), r.id.z, -r.ood.z);
-    const float2 nx = fma2s(make_float2(-q1.z, -q1.w), r.aid.x, mx), fx = fma2s(make_float2(q1.z, q1.w), r.aid.x, mx);
-    const float2 ny = fma2s(make_float2(-q2.x, -q2.y), r.aid.y, my), fy = fma2s(make_float2(q2.x, q2.y), r.aid.y, my);
-    const float2 nz = fma2s(make_float2(-q2.z, -q2.w), r.aid.z, mz), fz = fma2s(make_float2(q2.z, q2.w), r.aid.z, mz);
+    const float2 nx = fma2s(make_float2(-hx.x, -hx.y), r.aid.x, mx), fx = fma2s(hx, r.aid.x, mx);
+    const float2 ny = fma2s(make_float2(-hy.x, -hy.y), r.aid.y, my), fy = fma2s(hy, r.aid.y, my);
+    const float2 nz = fma2s(make_float2(-hz.x, -hz.y), r.aid.z, mz), fz = fma2s(hz, r.aid.z, mz);
     const float tn0 = fmaxf(fmaxf(nx.x, ny.x), fmaxf(nz.x, t_min)), tf0 = fminf(fminf(fx.x, fy.x), fminf(fz.x, t_hit));
     const float tn1 = fmaxf(fmaxf(nx.y, ny.y), fmaxf(nz.y, t_min)), tf1 = fminf(fminf(fx.y, fy.y), fminf(fz.y, t_hit));
     const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
     const bool second_first = h1 && (tn1 < tn0 || !h0); // child 1 is the nearer hit child, or the only one
-    const int first = second_first ? ch.y : ch.x, other = second_first ? ch.x : ch.y;
+    const int r0 = __float_as_int(q2.y), r1 = __float_as_int(q2.z);
+    const int first = second_first ? r1 : r0, other = second_first ? r0 : r1;
     int next = first;
-    // `at` on the push: a lane that is not at a node reads the dummy node, whose child 1 can only "hit" if the lane's ray constants
-    // are not finite (NaN drops out of min / max); such a lane must still not move its stack
     stk_visit(top, at && h0 && h1, !(h0 || h1), other, next);
     if (at) cur = next;
 }
@@ -547,7 +568,7 @@ __device__ __forceinline__ void node_step(const SceneView& S, const TravRay& r, 
     int2 ch;
     load_node<SMEM_ALL, PAD>(S, cur, w0, w1, w2, ch);
     float tn0, tf0, tn1, tf1;
-    slab2(r, w0, w1, w2, t_min, t_hit, tn0, tf0, tn1, tf1);
+    slab2<!EXACT>(r, w0, w1, w2, t_min, t_hit, tn0, tf0, tn1, tf1);
     // The boxes are padded on the host (scene_pack.cpp); <= keeps degenerate (flat) boxes alive.
     const bool h0 = tn0 <= tf0;
     const bool h1 = tn1 <= tf1;
@@ -572,7 +593,7 @@ __device__ __forceinline__ void node_step_all(const SceneView& S, const TravRay&
     int2 ch;
     load_node<SMEM_ALL, true>(S, at ? cur : 0, w0, w1, w2, ch);
     float tn0, tf0, tn1, tf1;
-    slab2(r, w0, w1, w2, t_min, t_hit, tn0, tf0, tn1, tf1);
+    slab2<true>(r, w0, w1, w2, t_min, t_hit, tn0, tf0, tn1, tf1);
     const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
     const bool swap = tn1 < tn0;
     const int first = (h0 && !(h1 && swap)) ? ch.x : ch.y; // the nearer hit child (or the only one)

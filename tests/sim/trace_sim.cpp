@@ -170,7 +170,7 @@ void wide_visit(const SceneView& S, const CrtPackedNode* nodes, int node, const 
         float4 w0, w1, w2; int2 ch;
         load_node<false, false>(S, owner, w0, w1, w2, ch);
         float tn0, tf0, tn1, tf1;
-        slab2(r, w0, w1, w2, t_min, h.t, tn0, tf0, tn1, tf1);
+        slab2<true>(r, w0, w1, w2, t_min, h.t, tn0, tf0, tn1, tf1);
         g_wide_boxes++;
         if (c == 0 ? tn0 <= tf0 : tn1 <= tf1) { cand[nc].tn = c == 0 ? tn0 : tn1; cand[nc].ref = nodes[owner].child[c]; nc++; }
     };
@@ -266,7 +266,7 @@ int main(int argc, char** argv)
     }
     D.nodes_pair = pair_tab.data();
     D.smem_nodes = nn / 2; D.smem_prims = 0; D.smem_mats = 0;
-    std::vector<float4> smem4((size_t)(nn / 2 + 1) * CRT_SMEM_NODE_F4 + 16);
+    std::vector<float4> smem4((size_t)(nn / 2 + 1) * CRT_PAIR_NODE_F4 + 16);
     const SceneView Sq = stage_scene<true, false, true>(D, smem4.data());
     D.smem_nodes = nn; D.smem_prims = np; D.smem_mats = np;
     bool spheres_only = true;
