@@ -207,8 +207,32 @@ Hit wide_lane(const SceneView& S, const CrtPackedNode* nodes, const TravRay& r, 
 
 } // namespace
 
+// "half" mode: the host forms of the binary16 helpers (crt_f2h_ru, crt_h2_to_f2, crt_h16_up) on special values and random bit
+// patterns, one line of hex words per value: input, binary16 bits, the decoded low / high halves of (h | h << 16), crt_h16_up.
+static int half_mode(int n)
+{
+    std::vector<uint32_t> in = {0u, 0x00000001u, 0x33000000u, 0x33800000u, 0x33800001u, 0x387fc000u, 0x387fffffu, 0x38800000u, 0x38800001u,
+                                0x3f800000u, 0x3f800001u, 0x3f801fffu, 0x3f802000u, 0x3f802001u, 0x477fe000u, 0x477fe001u, 0x477fffffu, 0x47800000u,
+                                0x7f7fffffu, 0x7f800000u, 0x7fc00000u, 0xbf800001u};
+    uint64_t st = 12345;
+    while ((int)in.size() < n) {
+        st = st * 6364136223846793005ull + 1442695040888963407ull;
+        uint32_t b = (uint32_t)(st >> 32);
+        if (in.size() % 3 == 0) b = (b & 0x807fffffu) | ((uint32_t)(100 + (st >> 20) % 45) << 23); // exponents around binary16's range
+        in.push_back(b);
+    }
+    for (uint32_t b : in) {
+        const float x = __uint_as_float(b);
+        const unsigned h = crt_f2h_ru(x);
+        const float2 f = crt_h2_to_f2(h | (h << 16));
+        printf("%08x %04x %08x %08x %08x\n", b, h, __float_as_uint(f.x), __float_as_uint(f.y), __float_as_uint(crt_h16_up(x)));
+    }
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
+    if (argc > 1 && !strcmp(argv[1], "half")) return half_mode(argc > 2 ? atoi(argv[2]) : 1000);
     const int kind = argc > 1 ? atoi(argv[1]) : CRT_SCENE_RTIOW;
     const uint64_t hint = argc > 2 ? (uint64_t)atoll(argv[2]) : 0;
     const int n_rays = argc > 3 ? atoi(argv[3]) : 20000;

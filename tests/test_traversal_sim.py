@@ -43,3 +43,27 @@ def test_rotated_trees_are_still_trees(trace_sim, kind, hint):
     r = subprocess.run([trace_sim, str(kind), str(hint), "3000", "11"], capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0 and " 0 mismatches" in r.stdout, r.stdout + r.stderr
 
+
+
+def test_binary16_helpers_round_half_extents_up_and_decode_exactly(trace_sim):
+    """crt_f2h_ru must give the SMALLEST binary16 >= |x| (+inf beyond 65504; a box may grow, never shrink) and crt_h2_to_f2 /
+    crt_h16_up must decode it exactly: checked against numpy's float16 on special values and 20 000 random bit patterns. (The
+    device forms are cvt.rp.f16.f32 / cvt.f32.f16; the GPU parity tests pin those through the frames.)"""
+    import numpy as np
+    r = subprocess.run([trace_sim, "half", "20000"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    rows = np.array([[int(w, 16) for w in line.split()] for line in r.stdout.splitlines()], dtype=np.uint64)
+    assert rows.shape == (20000, 5)
+    x = np.abs(rows[:, 0].astype(np.uint32).view(np.float32))
+    h = rows[:, 1].astype(np.uint16)
+    finite = ~np.isnan(x)
+    with np.errstate(over="ignore"):
+        near = x[finite].astype(np.float16)  # round to nearest even ...
+        low = near.astype(np.float32) < x[finite]  # ... then one step up where that fell below x
+        want = np.where(low, np.nextafter(near, np.float16(np.inf)), near)
+    assert np.array_equal(h[finite], want.view(np.uint16))
+    assert np.all(h[~finite] == 0x7c00)  # NaN extent: unbounded side
+    dec = h.view(np.float16).astype(np.float32).view(np.uint32)
+    for col in (2, 3, 4):
+        assert np.array_equal(rows[:, col].astype(np.uint32), dec)
+    assert np.all(dec.view(np.float32)[finite] >= x[finite])
