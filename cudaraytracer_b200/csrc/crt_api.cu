@@ -1341,11 +1341,18 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
     W.inv_pixels = ~0ull / P + 1ull; // pipe_item: division by multiplication (d == 1 is special-cased there)
     W.inv_cover_w = ~0ull / A.cover_w + 1ull;
     W.n_slots = n_slots;
-    W.thresh = ctx->pipe_thresh > 0 ? std::min(ctx->pipe_thresh, 32) : (all ? 14 : 1);
-    // Scene entirely in shared memory: the kernel is issue-bound, lanes are refilled as soon as 18 of 32 are idle (sweep 6..24:
-    // best at 12-14). Scene mostly behind L1: it is latency-bound, idle lanes cost nothing and every refill costs instructions,
-    // so a warp runs its batch of rays to completion (THRESH 1: +9 % on the 1 M-sphere scene, +7 % on the 10 k glass/metal one).
-    W.max_rounds = ctx->pipe_rounds > 0 ? ctx->pipe_rounds : (all ? 16 : 64);
+    // When a warp leaves its traversal loop for a look at the queues (fewer than `thresh` lanes busy, `max_rounds` rounds at the
+    // latest). Scene entirely in shared memory: the kernel is issue-bound and the best pair depends on how long a traversal is.
+    // Shallow trees (RTIOW: depth 12, 9 node visits per ray = three rounds): leave as soon as 13 lanes are idle and after four
+    // rounds, by when most lanes are done - since idle lanes keep the rays they shade, more and shorter visits to the queues
+    // pay: +3.7 % on RTIOW 1080p, +4.4 % at 4 spp, +5.8 % at 400x225. Deeper trees (1601 primitives, depth 14): four rounds end
+    // before the traversals do (-7.8 %), and (14, 16) stays the best pair (profiles/r02_th_refill_sweep.txt: 12..32 x 1..32).
+    // Scene mostly behind L1: latency-bound, idle lanes cost nothing and every refill costs instructions, so a warp runs its batch
+    // of rays to completion (THRESH 1: +9 % on the 1 M-sphere scene, +7 % on the 10 k glass/metal one; re-checked with the
+    // 44-byte nodes: still the best).
+    const bool shallow = all && ctx->stats.max_depth <= 12;
+    W.thresh = ctx->pipe_thresh > 0 ? std::min(ctx->pipe_thresh, 32) : (shallow ? 20 : all ? 14 : 1);
+    W.max_rounds = ctx->pipe_rounds > 0 ? ctx->pipe_rounds : (shallow ? 4 : all ? 16 : 64);
     const uint32_t stride = A.spp_stride ? A.spp_stride : 1u;
     const uint32_t spp_per_pass = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(A.spp_count, 0xF0000000ull / P));
     for (uint32_t done = 0; done < A.spp_count; done += spp_per_pass) {
