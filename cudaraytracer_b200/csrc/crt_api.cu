@@ -60,8 +60,10 @@ struct crt_context
     // kept while the tree, the frame size and the depth stay the same (crt_render)
     uint64_t auto_key = 0;
     int auto_variant = 0, last_variant = 0;
+    int auto_thresh = 0, auto_rounds = 0;    // refill parameters of the pipelined kernel that won the measurement (0 = static)
+    int cal_thresh = 0, cal_rounds = 0;      // ... the pair the NEXT render_pipeline call runs with (set and reset by crt_render)
     bool auto_calibrate = true; // CRT_AUTO_CALIBRATE=0: the static rule (pipeline from 256 primitives up)
-    cudaEvent_t ev_cal[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t ev_cal[4] = {nullptr, nullptr, nullptr, nullptr};
     float4* d_prims = nullptr;
     float* d_prim_k = nullptr;
     float4* d_mats = nullptr;
@@ -291,7 +293,7 @@ void crt_context_destroy(crt_context* ctx)
     cudaFree(ctx->build_arena);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
-    for (int k = 0; k < 3; k++) if (ctx->ev_cal[k]) cudaEventDestroy(ctx->ev_cal[k]);
+    for (int k = 0; k < 4; k++) if (ctx->ev_cal[k]) cudaEventDestroy(ctx->ev_cal[k]);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
@@ -1341,18 +1343,19 @@ static crt_status render_pipeline(crt_context* ctx, RenderArgs A)
     W.inv_pixels = ~0ull / P + 1ull; // pipe_item: division by multiplication (d == 1 is special-cased there)
     W.inv_cover_w = ~0ull / A.cover_w + 1ull;
     W.n_slots = n_slots;
-    // When a warp leaves its traversal loop for a look at the queues (fewer than `thresh` lanes busy, `max_rounds` rounds at the
-    // latest). Scene entirely in shared memory: the kernel is issue-bound and the best pair depends on how long a traversal is.
-    // Shallow trees (RTIOW: depth 12, 9 node visits per ray = three rounds): leave as soon as 13 lanes are idle and after four
-    // rounds, by when most lanes are done - since idle lanes keep the rays they shade, more and shorter visits to the queues
-    // pay: +3.7 % on RTIOW 1080p, +4.4 % at 4 spp, +5.8 % at 400x225. Deeper trees (1601 primitives, depth 14): four rounds end
-    // before the traversals do (-7.8 %), and (14, 16) stays the best pair (profiles/r02_th_refill_sweep.txt: 12..32 x 1..32).
+    // When a warp leaves its traversal loop for a look at the queues: fewer than `thresh` lanes busy, `max_rounds` rounds at the
+    // latest. Scene entirely in shared memory: the kernel is issue-bound and the best pair depends on how long a traversal is
+    // (profiles/r02_th_refill_sweep.txt, 12..32 x 1..32 on nine scenes, after idle lanes began to keep the rays they shade).
+    // RTIOW (nine node visits per ray = three rounds): (20, 4) is +3.7 % over round 1's (14, 16), but costs 4..8 % on glass /
+    // metal grids of ANY size and on diffuse grids from 1 000 spheres up, whose traversals are longer than four rounds. (16, 6)
+    // is the pair that loses nowhere (+0.8 % RTIOW, +2..3 % on 400..800 spheres, -0.2..-0.7 % on 1 000..1 600) and is the static
+    // choice; where crt_render measures (AUTO), it times (20, 4) as well and keeps the faster pair (cal_thresh / cal_rounds).
     // Scene mostly behind L1: latency-bound, idle lanes cost nothing and every refill costs instructions, so a warp runs its batch
     // of rays to completion (THRESH 1: +9 % on the 1 M-sphere scene, +7 % on the 10 k glass/metal one; re-checked with the
     // 44-byte nodes: still the best).
-    const bool shallow = all && ctx->stats.max_depth <= 12;
-    W.thresh = ctx->pipe_thresh > 0 ? std::min(ctx->pipe_thresh, 32) : (shallow ? 20 : all ? 14 : 1);
-    W.max_rounds = ctx->pipe_rounds > 0 ? ctx->pipe_rounds : (shallow ? 4 : all ? 16 : 64);
+    const bool cal = all && ctx->cal_thresh > 0 && ctx->cal_rounds > 0;
+    W.thresh = ctx->pipe_thresh > 0 ? std::min(ctx->pipe_thresh, 32) : cal ? ctx->cal_thresh : (all ? 16 : 1);
+    W.max_rounds = ctx->pipe_rounds > 0 ? ctx->pipe_rounds : cal ? ctx->cal_rounds : (all ? 6 : 64);
     const uint32_t stride = A.spp_stride ? A.spp_stride : 1u;
     const uint32_t spp_per_pass = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(A.spp_count, 0xF0000000ull / P));
     for (uint32_t done = 0; done < A.spp_count; done += spp_per_pass) {
@@ -1476,6 +1479,7 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
         // dominates (RTIOW 486 prims: 13.0 vs 11.5 Grays/s; 10k prims: 7.5 vs 5.4); below a few hundred primitives its
         // queue handling costs more than the divergence it removes (67 prims: 16.4 vs 21.1) and the megakernel is used.
         int variant = p->variant;
+        ctx->cal_thresh = ctx->cal_rounds = 0; // the static refill pair unless the measurement below says otherwise
         if (variant == CRT_VARIANT_AUTO) {
             variant = (exact || count || ctx->scene.n_prims < 256) ? CRT_VARIANT_MEGAKERNEL : CRT_VARIANT_PIPELINE;
             // Where both kernels hold the whole scene in shared memory the better one depends on the scene AND the view (DESIGN.md
@@ -1494,36 +1498,48 @@ crt_status crt_render(crt_context* ctx, const crt_render_params* p)
                 // ... provided they are a launch like the one that follows: on a small frame a few samples measure the fixed cost of a
                 // launch (the pipelined kernel's pool fill and drain), not its rate (400x225: 1 spp 0.14 vs 0.27 ms, 16 spp 1.55 vs 0.46 ms)
                 const bool representative = (uint64_t)A.cover_w * A.cover_h * c >= 1500000ull;
-                if (ctx->auto_key == key) variant = ctx->auto_variant;
+                if (ctx->auto_key == key) {
+                    variant = ctx->auto_variant;
+                    ctx->cal_thresh = ctx->auto_thresh;
+                    ctx->cal_rounds = ctx->auto_rounds;
+                }
                 else if (c >= 1u && representative) {
-                    for (int k = 0; k < 3; k++)
+                    for (int k = 0; k < 4; k++)
                         if (!ctx->ev_cal[k]) CU(cudaEventCreate(&ctx->ev_cal[k]));
-                    RenderArgs W = A; // one untimed sample each first (module load, attribute set-up), then c timed samples each
+                    RenderArgs W = A; // one untimed sample per kernel first (module load, attribute set-up), then c timed samples per candidate
                     uint32_t at = A.spp_begin;
-                    auto part = [&](int v, uint32_t n) -> crt_status {
+                    auto part = [&](int v, uint32_t n, int thresh, int rounds) -> crt_status {
                         W.spp_begin = at; W.spp_count = n;
                         at += n * A.spp_stride;
+                        ctx->cal_thresh = thresh; ctx->cal_rounds = rounds;
                         return v == CRT_VARIANT_MEGAKERNEL ? render_mega(ctx, W, false, false) : render_pipeline(ctx, W);
                     };
                     crt_status cs;
-                    if ((cs = part(CRT_VARIANT_MEGAKERNEL, 1)) != CRT_OK || (cs = part(CRT_VARIANT_PIPELINE, 1)) != CRT_OK) return cs;
+                    if ((cs = part(CRT_VARIANT_MEGAKERNEL, 1, 0, 0)) != CRT_OK || (cs = part(CRT_VARIANT_PIPELINE, 1, 0, 0)) != CRT_OK) return cs;
                     CU(cudaEventRecord(ctx->ev_cal[0], ctx->stream));
-                    if ((cs = part(CRT_VARIANT_MEGAKERNEL, c)) != CRT_OK) return cs;
+                    if ((cs = part(CRT_VARIANT_MEGAKERNEL, c, 0, 0)) != CRT_OK) return cs;
                     CU(cudaEventRecord(ctx->ev_cal[1], ctx->stream));
-                    if ((cs = part(CRT_VARIANT_PIPELINE, c)) != CRT_OK) return cs;
+                    if ((cs = part(CRT_VARIANT_PIPELINE, c, 0, 0)) != CRT_OK) return cs; // the static refill pair
                     CU(cudaEventRecord(ctx->ev_cal[2], ctx->stream));
-                    CU(cudaEventSynchronize(ctx->ev_cal[2]));
-                    float t_mega = 0.f, t_pipe = 0.f;
+                    if ((cs = part(CRT_VARIANT_PIPELINE, c, 20, 4)) != CRT_OK) return cs; // the pair of short traversals (render_pipeline)
+                    CU(cudaEventRecord(ctx->ev_cal[3], ctx->stream));
+                    CU(cudaEventSynchronize(ctx->ev_cal[3]));
+                    float t_mega = 0.f, t_pipe = 0.f, t_pipe_short = 0.f;
                     CU(cudaEventElapsedTime(&t_mega, ctx->ev_cal[0], ctx->ev_cal[1]));
                     CU(cudaEventElapsedTime(&t_pipe, ctx->ev_cal[1], ctx->ev_cal[2]));
-                    variant = t_pipe < t_mega ? CRT_VARIANT_PIPELINE : CRT_VARIANT_MEGAKERNEL;
+                    CU(cudaEventElapsedTime(&t_pipe_short, ctx->ev_cal[2], ctx->ev_cal[3]));
+                    const bool short_wins = t_pipe_short < t_pipe;
+                    variant = std::min(t_pipe, t_pipe_short) < t_mega ? CRT_VARIANT_PIPELINE : CRT_VARIANT_MEGAKERNEL;
                     ctx->auto_key = key;
                     ctx->auto_variant = variant;
+                    ctx->auto_thresh = ctx->cal_thresh = short_wins ? 20 : 0;
+                    ctx->auto_rounds = ctx->cal_rounds = short_wins ? 4 : 0;
                     if (getenv("CRT_VERBOSE"))
-                        fprintf(stderr, "[crt] AUTO: megakernel %.3f ms, pipeline %.3f ms for %u samples of %ux%u -> %s\n", t_mega, t_pipe, c, A.cover_w, A.cover_h,
-                                variant == CRT_VARIANT_PIPELINE ? "pipeline" : "megakernel");
+                        fprintf(stderr, "[crt] AUTO: megakernel %.3f ms, pipeline %.3f ms, pipeline (20, 4) %.3f ms for %u samples of %ux%u -> %s%s\n", t_mega, t_pipe,
+                                t_pipe_short, c, A.cover_w, A.cover_h, variant == CRT_VARIANT_PIPELINE ? "pipeline" : "megakernel",
+                                variant == CRT_VARIANT_PIPELINE && short_wins ? " (20, 4)" : "");
                     A.spp_begin = at;
-                    A.spp_count -= 2u + 2u * c;
+                    A.spp_count -= 2u + 3u * c;
                 }
             }
         }

@@ -277,8 +277,8 @@ crt_status crt_last_render_ms(crt_context* ctx, float* out_ms);
 /* The kernel variant the last crt_render call ran (CRT_VARIANT_MEGAKERNEL / _WAVEFRONT / _PIPELINE; 0 before the first call).
  * With CRT_VARIANT_AUTO on a scene that both the megakernel and the pipelined kernel can stage completely (up to 2048
  * primitives), a call of at least 16 samples on a frame large enough for a few samples to be representative (1.5 M paths in
- * the timed part) renders its first samples with both, times them and gives the rest to the faster
- * one (the variants write identical bits, so the frame does not depend on the choice); the choice is kept until the tree, the
+ * the timed part) renders its first samples with both (the pipelined kernel with each of its two refill-parameter pairs),
+ * times them and gives the rest to the fastest (the variants write identical bits, so the frame does not depend on the choice); the choice is kept until the tree, the
  * frame size or the depth changes. CRT_AUTO_CALIBRATE=0 keeps the static rule (pipeline from 256 primitives up). The reference
  * has one kernel (Kernel.cu:102): no counterpart. */
 int32_t crt_last_variant(crt_context* ctx);
