@@ -74,6 +74,7 @@ Hit brute_force(const SceneView& S, int n_prims, const std::vector<int>& codes, 
 
 // one lane of k_render_pipe's traversal: rounds of three node visits and one leaf visit (pipeline.cuh)
 long g_node_visits = 0, g_leaf_visits = 0; // statistics of the tree, printed at the end
+long g_lane_nodes = 0; // inner nodes the last lane call really visited: every fast form must walk the SAME nodes (one set of boxes)
 
 template <bool SMEM_ALL> Hit pipe_lane(const SceneView& S, const TravRay& r, float t_min, long& visits)
 {
@@ -84,7 +85,7 @@ template <bool SMEM_ALL> Hit pipe_lane(const SceneView& S, const TravRay& r, flo
     int cur = trav_begin<false, SMEM_ALL>(S, r, t_min, h);
     while (cur != CRT_TRAV_DONE) {
         for (int k = 0; k < 3; k++) {
-            if (cur >= 0) g_node_visits++;
+            if (cur >= 0) { g_node_visits++; g_lane_nodes++; }
             node_step_all<SMEM_ALL>(S, r, t_min, h.t, cur, sp, stack);
         }
         if (cur < 0 && cur != CRT_TRAV_DONE) { g_leaf_visits++; leaf_step<false, SMEM_ALL>(S, r, t_min, h, cur, sp, stack); }
@@ -108,6 +109,7 @@ template <bool SPH> Hit pair_lane(const SceneView& S, const TravRay& r, float t_
         for (int k = 0; k < 3; k++) {
             StackPtr before = top;
             const bool at = pair_at_node(cur);
+            g_lane_nodes += at;
             node_visit_pair(S, r, t_min, h.t, cur, top);
             if (!at && top != before) { fprintf(stderr, "the dummy node moved the stack\n"); exit(3); }
         }
@@ -141,6 +143,7 @@ Hit pairg_lane(const SceneView& S, const TravRay& r, float t_min, long& visits)
         for (int k = 0; k < 3; k++) {
             StackPtr before = top;
             const bool at = cur >= 0;
+            g_lane_nodes += at;
             node_visit_pairg(S, r, t_min, h.t, cur, top);
             if (!at && top != before) { fprintf(stderr, "the dummy node moved the stack (global path)\n"); exit(3); }
         }
@@ -327,11 +330,19 @@ int main(int argc, char** argv)
         Hit got[7];
         got[0] = closest_hit<false, false, false>(Sg, o, d, t_min, 3.402823466e+38f, nb, npr); // megakernel form, global tables
         got[1] = closest_hit<false, false, true>(Sw, o, d, t_min, 3.402823466e+38f, nb, npr);  // ... tables in 'shared memory'
-        got[2] = pipe_lane<true>(Sp, r, t_min, visits);
-        got[3] = pipe_lane<false>(Sg, r, t_min, visits); // nodes behind the 'global' pointers (scenes that do not fit)
-        got[4] = pair_ok ? pair_lane<false>(So, r, t_min, visits) : got[2];
-        got[5] = pair_ok && spheres_only ? pair_lane<true>(So, r, t_min, visits) : got[4];
-        got[6] = pairg_lane(Sq, r, t_min, visits);
+        long walked[5];
+        g_lane_nodes = 0; got[2] = pipe_lane<true>(Sp, r, t_min, visits); walked[0] = g_lane_nodes;
+        g_lane_nodes = 0; got[3] = pipe_lane<false>(Sg, r, t_min, visits); walked[1] = g_lane_nodes; // nodes behind the 'global' pointers (scenes that do not fit)
+        g_lane_nodes = 0; got[4] = pair_ok ? pair_lane<false>(So, r, t_min, visits) : got[2]; walked[2] = pair_ok ? g_lane_nodes : walked[0];
+        g_lane_nodes = 0; got[5] = pair_ok && spheres_only ? pair_lane<true>(So, r, t_min, visits) : got[4]; walked[3] = pair_ok && spheres_only ? g_lane_nodes : walked[2];
+        g_lane_nodes = 0; got[6] = pairg_lane(Sq, r, t_min, visits); walked[4] = g_lane_nodes;
+        // Every fast form culls with the binary16-rounded boxes (slab2<H16> / the PAIR tables) and descends near child first:
+        // they must visit the same inner nodes, not merely find the same hit - that is what keeps a grazing phantom hit of the
+        // reference's sphere formula (trace.cuh sphere_test) either in all variants' frames or in none.
+        for (int k = 1; k < 5; k++)
+            if (walked[k] != walked[0]) {
+                if (mism++ < 5) fprintf(stderr, "ray %d: form %d visited %ld inner nodes, the word-major form %ld\n", i, k + 2, walked[k], walked[0]);
+            }
         hits += want.leaf >= 0;
         {
             const Hit w = wide_lane(Sg, P.nodes.data(), r, t_min);

@@ -2,7 +2,10 @@
 -DCRT_HOST_SIM) and run against a brute-force closest hit on the trees the library's own builder packs. No GPU: this checks the
 LOGIC of every traversal form - the megakernel's node_step loop on global and on word-major shared tables, the pipelined
 kernel's node, node, node, leaf rounds with node_step_all (staged or 'global' nodes) and with node_visit_pair (child-interleaved
-staged nodes, FFMA2 emulated with fmaf, sentinel stack, generic and sphere-only leaf visits) - bit for bit; the device arithmetic itself is what the -m gpu parity tests pin."""
+staged nodes, FFMA2 emulated with fmaf, sentinel stack, generic and sphere-only leaf visits) - bit for bit; the device arithmetic itself is what the -m gpu parity tests pin.
+The pipelined forms must also VISIT the same inner nodes per ray (all fast paths cull with the binary16-rounded boxes: with the
+binary32 boxes in one of them, 6 of 3000 rays of the 10 k scene walk different nodes), which is what keeps the variants' frames
+bit-identical although the reference's sphere formula reports grazing hits outside a leaf box."""
 import os
 import subprocess
 
