@@ -268,7 +268,7 @@ __global__ void k_pair_nodes(const float4* __restrict__ nodes, float4* __restric
 // ONE leaf visit serves them all (measured against node, leaf, node, leaf: +7 % on C2, +4 % on the 1 M-sphere scene; two or
 // four node visits per leaf visit are slower, profiles/r02_a_*).
 // Both paths: branch-free node visit on child-interleaved nodes (FFMA2), dummy node for idle lanes, sentinel stack in PTX.
-// Scene larger than shared memory: 64-byte nodes from the child-interleaved global table, a prefix of it staged (node_visit_pairg).
+// Scene larger than shared memory: 44-byte nodes (64-byte records) from the child-interleaved global table, a prefix of it staged in 48-byte slots (node_visit_pairg).
 // SMEM_ALL (the whole scene is staged): the nodes take the PAIR layout of trace.cuh (48-byte nodes: binary16 half-extents,
 // 16-bit references) and node_visit_pair (FFMA2, branch-free, dummy node for idle lanes, sentinel stack pushed / popped in PTX).
 // SPH: the scene holds only spheres (DevScene::spheres_only, chosen by the host): leaf visits without the type dispatch.
